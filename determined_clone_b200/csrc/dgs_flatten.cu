@@ -1,0 +1,229 @@
+// flatten / accumulate / scale / cast: many gradient tensors -> one persistent flat bucket.
+//
+// Takes over autograd's `grad += new` under DDP.no_sync() (reference
+// harness/determined/pytorch/_pytorch_context.py:802-812), DDP's grad/N copy into its buckets
+// (:813-816) and the per-parameter div_(A) of _average_gradients (:818-825).
+//
+// HBM-bound, no reuse: one pass, every warp-level access a contiguous 512 B (fp32) run, 4 independent
+// 16 B accesses per array per thread in flight, grid = min(tiles, 8 CTAs x SMs).
+#include "dgs_common.cuh"
+
+namespace dgs {
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kUnroll = 4;
+constexpr int kMaxSegs = 64;
+
+struct SegDev {
+  const void* src;
+  long long dst_off;
+  long long numel;
+  long long tile_start;  // index of this segment's first tile
+  int vec_ok;            // src is 16-byte aligned
+  int pad_;
+};
+
+struct FlatParams {
+  SegDev seg[kMaxSegs];
+  int n;
+  long long tiles;
+};
+
+template <typename G, typename W, bool READ_ACC, bool WRITE_WIRE>
+struct FlatCfg {
+  // 8 elements per access only when every array in the loop is 16-bit
+  static constexpr int VEC = (is16<G>::value && WRITE_WIRE && !READ_ACC && is16<W>::value) ? 8 : 4;
+  static constexpr int TILE = kThreads * VEC * kUnroll;
+};
+
+template <typename G, typename W, bool READ_ACC, bool WRITE_WIRE>
+__global__ void __launch_bounds__(kThreads)
+flatten_kernel(const __grid_constant__ FlatParams P, float* __restrict__ acc, W* __restrict__ wire,
+               float scale) {
+  using Cfg = FlatCfg<G, W, READ_ACC, WRITE_WIRE>;
+  constexpr int VEC = Cfg::VEC;
+  constexpr int TILE = Cfg::TILE;
+
+  for (long long t = blockIdx.x; t < P.tiles; t += gridDim.x) {
+    // segment lookup: last segment whose tile_start <= t (block-uniform)
+    int lo = 0, hi = P.n - 1;
+    while (lo < hi) {
+      int mid = (lo + hi + 1) >> 1;
+      if (P.seg[mid].tile_start <= t) lo = mid; else hi = mid - 1;
+    }
+    const G* __restrict__ src = static_cast<const G*>(P.seg[lo].src);
+    const long long numel = P.seg[lo].numel;
+    const long long dst0 = P.seg[lo].dst_off;
+    const long long base = (t - P.seg[lo].tile_start) * TILE;
+    const bool vec_ok = P.seg[lo].vec_ok != 0;
+
+    float g[kUnroll][VEC];
+    float a[kUnroll][VEC];
+    long long idx[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      idx[u] = base + (long long)(u * kThreads + threadIdx.x) * VEC;
+      if (idx[u] + VEC <= numel && vec_ok) {
+        load_vec<G, VEC, Cache::Stream>(src + idx[u], g[u]);
+        if constexpr (READ_ACC) load_vec<float, 4>(acc + dst0 + idx[u], a[u]);
+      } else {
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) {
+          const bool in = idx[u] + k < numel;
+          g[u][k] = in ? to_f32(src[idx[u] + k]) : 0.0f;
+          if constexpr (READ_ACC) a[u][k] = in ? acc[dst0 + idx[u] + k] : 0.0f;
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+#pragma unroll
+      for (int k = 0; k < VEC; ++k) {
+        float v = g[u][k];
+        if constexpr (READ_ACC) v += a[u][k];
+        if constexpr (WRITE_WIRE) v *= scale;
+        g[u][k] = v;
+      }
+      if (idx[u] + VEC <= numel) {
+        if constexpr (WRITE_WIRE) store_vec<W, VEC>(wire + dst0 + idx[u], g[u]);
+        else store_vec<float, 4>(acc + dst0 + idx[u], g[u]);
+      } else {
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) {
+          if (idx[u] + k < numel) {
+            if constexpr (WRITE_WIRE) wire[dst0 + idx[u] + k] = from_f32<W>(g[u][k]);
+            else acc[dst0 + idx[u] + k] = g[u][k];
+          }
+        }
+      }
+    }
+  }
+}
+
+template <typename W>
+__global__ void __launch_bounds__(kThreads)
+scale_cast_kernel(const float* __restrict__ acc, W* __restrict__ wire, long long n, float scale) {
+  const long long nvec = n >> 2;
+  const long long stride = (long long)gridDim.x * kThreads;
+  for (long long i = (long long)blockIdx.x * kThreads + threadIdx.x; i < nvec; i += stride) {
+    float v[4];
+    load_vec<float, 4, Cache::Stream>(acc + i * 4, v);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) v[k] *= scale;
+    store_vec<W, 4>(wire + i * 4, v);
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    const long long i = (nvec << 2) + threadIdx.x;
+    wire[i] = from_f32<W>(acc[i] * scale);
+  }
+}
+
+template <typename G, typename W, bool RA, bool WW>
+int launch_flatten(const dgs_seg* segs, int n_segs, float* acc, void* wire, float scale,
+                   cudaStream_t st) {
+  constexpr int TILE = FlatCfg<G, W, RA, WW>::TILE;
+  for (int s0 = 0; s0 < n_segs; s0 += kMaxSegs) {
+    FlatParams P;
+    const int n = (n_segs - s0 < kMaxSegs) ? n_segs - s0 : kMaxSegs;
+    long long tiles = 0;
+    int m = 0;
+    for (int i = 0; i < n; ++i) {
+      const dgs_seg& s = segs[s0 + i];
+      if (s.numel == 0) continue;
+      P.seg[m].src = s.src;
+      P.seg[m].dst_off = s.dst_off;
+      P.seg[m].numel = s.numel;
+      P.seg[m].tile_start = tiles;
+      P.seg[m].vec_ok = aligned16(s.src) ? 1 : 0;
+      P.seg[m].pad_ = 0;
+      tiles += (s.numel + TILE - 1) / TILE;
+      ++m;
+    }
+    if (m == 0) continue;
+    P.n = m;
+    P.tiles = tiles;
+    const long long cap = (long long)sm_count() * 8;
+    const int grid = (int)(tiles < cap ? tiles : cap);
+    flatten_kernel<G, W, RA, WW><<<grid, kThreads, 0, st>>>(P, acc, static_cast<W*>(wire), scale);
+    DGS_LAUNCHED();
+  }
+  return DGS_OK;
+}
+
+template <typename G, typename W>
+int dispatch_mode(int mode, const dgs_seg* segs, int n, float* acc, void* wire, float scale,
+                  cudaStream_t st) {
+  switch (mode) {
+    case 0: return launch_flatten<G, W, false, false>(segs, n, acc, wire, scale, st);
+    case DGS_READ_ACC: return launch_flatten<G, W, true, false>(segs, n, acc, wire, scale, st);
+    case DGS_WRITE_WIRE: return launch_flatten<G, W, false, true>(segs, n, acc, wire, scale, st);
+    default: return launch_flatten<G, W, true, true>(segs, n, acc, wire, scale, st);
+  }
+}
+
+template <typename G>
+int dispatch_wire(int wire_dtype, int mode, const dgs_seg* segs, int n, float* acc, void* wire,
+                  float scale, cudaStream_t st) {
+  switch (wire_dtype) {
+    case DGS_F32: return dispatch_mode<G, float>(mode, segs, n, acc, wire, scale, st);
+    case DGS_BF16: return dispatch_mode<G, __nv_bfloat16>(mode, segs, n, acc, wire, scale, st);
+    case DGS_F16: return dispatch_mode<G, __half>(mode, segs, n, acc, wire, scale, st);
+    default: return fail(DGS_EINVAL, "dgs_flatten_accumulate: bad wire_dtype %d", wire_dtype);
+  }
+}
+
+}  // namespace
+}  // namespace dgs
+
+extern "C" int dgs_flatten_accumulate(const dgs_seg* segs, int n_segs, int grad_dtype, float* acc,
+                                      void* wire, int wire_dtype, int mode, float scale,
+                                      dgs_stream_t stream) {
+  using namespace dgs;
+  DGS_CHECK_ARG(n_segs >= 0, "dgs_flatten_accumulate: n_segs %d < 0", n_segs);
+  if (n_segs == 0) return DGS_OK;
+  DGS_CHECK_ARG(segs != nullptr, "dgs_flatten_accumulate: segs is NULL");
+  DGS_CHECK_ARG((mode & ~(DGS_READ_ACC | DGS_WRITE_WIRE)) == 0, "dgs_flatten_accumulate: bad mode %d",
+                mode);
+  const bool ww = (mode & DGS_WRITE_WIRE) != 0, ra = (mode & DGS_READ_ACC) != 0;
+  DGS_CHECK_ARG(!ww || wire != nullptr, "dgs_flatten_accumulate: DGS_WRITE_WIRE needs a wire buffer");
+  DGS_CHECK_ARG((!ra && ww) || acc != nullptr, "dgs_flatten_accumulate: this mode needs the accumulator");
+  DGS_CHECK_ARG(acc == nullptr || aligned16(acc), "dgs_flatten_accumulate: acc is not 16-byte aligned");
+  DGS_CHECK_ARG(wire == nullptr || aligned16(wire), "dgs_flatten_accumulate: wire is not 16-byte aligned");
+  for (int i = 0; i < n_segs; ++i) {
+    DGS_CHECK_ARG(segs[i].numel >= 0 && segs[i].dst_off >= 0, "dgs_flatten_accumulate: seg %d negative size/offset", i);
+    DGS_CHECK_ARG(segs[i].numel == 0 || segs[i].src != nullptr, "dgs_flatten_accumulate: seg %d src is NULL", i);
+    DGS_CHECK_ARG((segs[i].dst_off & 7) == 0, "dgs_flatten_accumulate: seg %d dst_off %lld is not a multiple of 8",
+                  i, (long long)segs[i].dst_off);
+  }
+  if (!ww) wire_dtype = DGS_F32;  // unused
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (grad_dtype) {
+    case DGS_F32: return dispatch_wire<float>(wire_dtype, mode, segs, n_segs, acc, wire, scale, st);
+    case DGS_BF16: return dispatch_wire<__nv_bfloat16>(wire_dtype, mode, segs, n_segs, acc, wire, scale, st);
+    case DGS_F16: return dispatch_wire<__half>(wire_dtype, mode, segs, n_segs, acc, wire, scale, st);
+    default: return fail(DGS_EINVAL, "dgs_flatten_accumulate: bad grad_dtype %d", grad_dtype);
+  }
+}
+
+extern "C" int dgs_scale_cast(const float* acc, void* wire, int wire_dtype, int64_t n, float scale,
+                              dgs_stream_t stream) {
+  using namespace dgs;
+  DGS_CHECK_ARG(n >= 0, "dgs_scale_cast: n < 0");
+  if (n == 0) return DGS_OK;
+  DGS_CHECK_ARG(acc != nullptr && wire != nullptr, "dgs_scale_cast: NULL buffer");
+  DGS_CHECK_ARG(aligned16(acc) && aligned16(wire), "dgs_scale_cast: buffers must be 16-byte aligned");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const long long nvec = (n + 3) / 4;
+  const long long want = (nvec + kThreads - 1) / kThreads;
+  const long long cap = (long long)sm_count() * 8;
+  const int grid = (int)(want < cap ? want : cap);
+  switch (wire_dtype) {
+    case DGS_F32: scale_cast_kernel<float><<<grid, kThreads, 0, st>>>(acc, (float*)wire, n, scale); break;
+    case DGS_BF16: scale_cast_kernel<__nv_bfloat16><<<grid, kThreads, 0, st>>>(acc, (__nv_bfloat16*)wire, n, scale); break;
+    case DGS_F16: scale_cast_kernel<__half><<<grid, kThreads, 0, st>>>(acc, (__half*)wire, n, scale); break;
+    default: return fail(DGS_EINVAL, "dgs_scale_cast: bad wire_dtype %d", wire_dtype);
+  }
+  DGS_LAUNCHED();
+  return DGS_OK;
+}

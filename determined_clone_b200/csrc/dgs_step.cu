@@ -1,0 +1,338 @@
+// Fused global-norm clip + optimizer step over flat param / state / grad buffers.
+//
+// Takes over clip_grads(parameters) + optimizer.step() + optimizer.zero_grad() of the reference at
+// harness/determined/pytorch/_pytorch_context.py:902-924 for torch.optim.Adam/AdamW and
+// torch.optim.SGD.  Arithmetic follows torch 2.11 torch/optim/adam.py (_multi_tensor_adam) and
+// torch/optim/sgd.py (_multi_tensor_sgd) op by op, in fp32, with one rounding at the store for
+// 16-bit params/state.
+//
+// HBM-bound: AdamW moves 28 B/element in fp32 (read g,p,m,v; write p,m,v), SGD-momentum 20 B.  Each
+// thread keeps kUnroll x 4 independent 16 B loads in flight; every warp access is contiguous; the grid
+// is persistent (resident CTAs per SM x SMs) and strides over tiles.
+#include "dgs_common.cuh"
+
+namespace dgs {
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kUnroll = 2;
+
+// ---- device-side hyper-parameter tables (fp32 constants derived on the host in double) ----------
+struct AdamHp {
+  long long begin, end;
+  float decay;     // decoupled: 1 - lr*wd ; L2: wd
+  float w1;        // 1 - beta1
+  float beta2;
+  float w2;        // 1 - beta2
+  float eps;
+  float neg_step;  // -(lr / bias_correction1)
+  float bc2_sqrt;
+  int flags;
+};
+struct SgdHp {
+  long long begin, end;
+  float wd, momentum, w_g /* 1 - dampening */, neg_lr;
+  int flags;
+  int pad_;
+};
+template <typename Hp>
+struct Table {
+  Hp r[DGS_MAX_RANGES];
+  int n;
+};
+
+__device__ __forceinline__ void adam_update(float& p, float& m, float& v, float g, const AdamHp& h,
+                                            float clip) {
+  g *= clip;
+  if (h.flags & DGS_OPT_MAXIMIZE) g = -g;
+  if (h.flags & DGS_ADAM_DECOUPLED_WD) p *= h.decay;
+  else g = g + h.decay * p;
+  m = m + h.w1 * (g - m);                      // _foreach_lerp_(exp_avg, grad, 1 - beta1)
+  v = v * h.beta2;                             // _foreach_mul_(exp_avg_sq, beta2)
+  v = v + h.w2 * (g * g);                      // _foreach_addcmul_(exp_avg_sq, grad, grad, 1 - beta2)
+  const float denom = sqrtf(v) / h.bc2_sqrt + h.eps;
+  p = p + h.neg_step * (m / denom);            // _foreach_addcdiv_(param, exp_avg, denom, step_size)
+}
+
+__device__ __forceinline__ void sgd_update(float& p, float& b, float g, const SgdHp& h, float clip,
+                                           bool has_buf) {
+  g *= clip;
+  if (h.flags & DGS_OPT_MAXIMIZE) g = -g;
+  if (h.wd != 0.0f) g = g + h.wd * p;
+  if (has_buf) {
+    if (h.flags & DGS_SGD_FIRST_STEP) b = g;   // buf = clone(grad)
+    else b = b * h.momentum + h.w_g * g;       // buf.mul_(momentum).add_(grad, alpha=1-dampening)
+    g = (h.flags & DGS_SGD_NESTEROV) ? g + h.momentum * b : b;
+  }
+  p = p + h.neg_lr * g;
+}
+
+template <typename Hp>
+__device__ __forceinline__ int find_range(const Table<Hp>& T, long long e) {
+  for (int i = 0; i < T.n; ++i)
+    if (e >= T.r[i].begin && e < T.r[i].end) return i;
+  return -1;
+}
+
+template <typename P, typename G>
+struct StepCfg {
+  static constexpr int VEC = (is16<P>::value && is16<G>::value) ? 8 : 4;
+  static constexpr int TILE = kThreads * VEC * kUnroll;
+};
+
+template <typename P, typename G>
+__global__ void __launch_bounds__(kThreads)
+adam_kernel(P* __restrict__ param, P* __restrict__ ea, P* __restrict__ eas, const G* __restrict__ grad,
+            long long n, const __grid_constant__ Table<AdamHp> T,
+            const float* __restrict__ total_norm, float max_norm) {
+  constexpr int VEC = StepCfg<P, G>::VEC;
+  constexpr int TILE = StepCfg<P, G>::TILE;
+  const float clip = clip_coef(total_norm, max_norm);
+  const long long tiles = (n + TILE - 1) / TILE;
+  for (long long t = blockIdx.x; t < tiles; t += gridDim.x) {
+    const long long e0 = t * TILE;
+    // first range that ends after the tile start (ranges are sorted and disjoint)
+    int r = 0;
+    while (r < T.n && T.r[r].end <= e0) ++r;
+    if (r == T.n) break;
+    if (T.r[r].begin <= e0 && e0 + TILE <= T.r[r].end) {
+      const AdamHp h = T.r[r];
+      float g[kUnroll][VEC], p[kUnroll][VEC], m[kUnroll][VEC], v[kUnroll][VEC];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const long long i = e0 + (long long)(u * kThreads + threadIdx.x) * VEC;
+        load_vec<G, VEC, Cache::Stream>(grad + i, g[u]);
+        load_vec<P, VEC>(param + i, p[u]);
+        load_vec<P, VEC>(ea + i, m[u]);
+        load_vec<P, VEC>(eas + i, v[u]);
+      }
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const long long i = e0 + (long long)(u * kThreads + threadIdx.x) * VEC;
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) adam_update(p[u][k], m[u][k], v[u][k], g[u][k], h, clip);
+        store_vec<P, VEC>(param + i, p[u]);
+        store_vec<P, VEC>(ea + i, m[u]);
+        store_vec<P, VEC>(eas + i, v[u]);
+      }
+    } else {
+      // tile straddles a range boundary or the end of the buffer: scalar, per-element lookup
+      const long long e1 = (e0 + TILE < n) ? e0 + TILE : n;
+      for (long long e = e0 + threadIdx.x; e < e1; e += kThreads) {
+        const int q = find_range(T, e);
+        if (q < 0) continue;
+        float p = to_f32(param[e]), m = to_f32(ea[e]), v = to_f32(eas[e]);
+        adam_update(p, m, v, to_f32(grad[e]), T.r[q], clip);
+        param[e] = from_f32<P>(p);
+        ea[e] = from_f32<P>(m);
+        eas[e] = from_f32<P>(v);
+      }
+    }
+  }
+}
+
+template <typename P, typename G, bool HAS_BUF>
+__global__ void __launch_bounds__(kThreads)
+sgd_kernel(P* __restrict__ param, P* __restrict__ buf, const G* __restrict__ grad, long long n,
+           const __grid_constant__ Table<SgdHp> T, const float* __restrict__ total_norm,
+           float max_norm) {
+  constexpr int VEC = StepCfg<P, G>::VEC;
+  constexpr int TILE = StepCfg<P, G>::TILE;
+  const float clip = clip_coef(total_norm, max_norm);
+  const long long tiles = (n + TILE - 1) / TILE;
+  for (long long t = blockIdx.x; t < tiles; t += gridDim.x) {
+    const long long e0 = t * TILE;
+    int r = 0;
+    while (r < T.n && T.r[r].end <= e0) ++r;
+    if (r == T.n) break;
+    if (T.r[r].begin <= e0 && e0 + TILE <= T.r[r].end) {
+      const SgdHp h = T.r[r];
+      const bool read_buf = HAS_BUF && !(h.flags & DGS_SGD_FIRST_STEP);
+      float g[kUnroll][VEC], p[kUnroll][VEC], b[kUnroll][VEC];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const long long i = e0 + (long long)(u * kThreads + threadIdx.x) * VEC;
+        load_vec<G, VEC, Cache::Stream>(grad + i, g[u]);
+        load_vec<P, VEC>(param + i, p[u]);
+        if (read_buf) {
+          load_vec<P, VEC>(buf + i, b[u]);
+        } else {
+#pragma unroll
+          for (int k = 0; k < VEC; ++k) b[u][k] = 0.0f;
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const long long i = e0 + (long long)(u * kThreads + threadIdx.x) * VEC;
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) sgd_update(p[u][k], b[u][k], g[u][k], h, clip, HAS_BUF);
+        store_vec<P, VEC>(param + i, p[u]);
+        if constexpr (HAS_BUF) store_vec<P, VEC>(buf + i, b[u]);
+      }
+    } else {
+      const long long e1 = (e0 + TILE < n) ? e0 + TILE : n;
+      for (long long e = e0 + threadIdx.x; e < e1; e += kThreads) {
+        const int q = find_range(T, e);
+        if (q < 0) continue;
+        float p = to_f32(param[e]);
+        float b = 0.0f;
+        if (HAS_BUF && !(T.r[q].flags & DGS_SGD_FIRST_STEP)) b = to_f32(buf[e]);
+        sgd_update(p, b, to_f32(grad[e]), T.r[q], clip, HAS_BUF);
+        param[e] = from_f32<P>(p);
+        if constexpr (HAS_BUF) buf[e] = from_f32<P>(b);
+      }
+    }
+  }
+}
+
+// resident CTAs per SM for this kernel, probed once per instantiation
+template <auto Kernel>
+int persistent_grid(long long tiles) {
+  static const int per_sm = [] {
+    int v = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, Kernel, kThreads, 0) != cudaSuccess || v < 1) {
+      (void)cudaGetLastError();
+      v = 4;
+    }
+    return v;
+  }();
+  const long long cap = (long long)sm_count() * per_sm;
+  if (tiles < 1) tiles = 1;
+  return (int)(tiles < cap ? tiles : cap);
+}
+
+template <typename Range>
+int check_ranges(const char* who, const Range* ranges, int n_ranges, int64_t n) {
+  DGS_CHECK_ARG(n_ranges >= 0 && n_ranges <= DGS_MAX_RANGES, "%s: n_ranges %d outside [0, %d]", who,
+                n_ranges, DGS_MAX_RANGES);
+  DGS_CHECK_ARG(n_ranges == 0 || ranges != nullptr, "%s: ranges is NULL", who);
+  int64_t prev = 0;
+  for (int i = 0; i < n_ranges; ++i) {
+    DGS_CHECK_ARG(ranges[i].begin >= prev && ranges[i].end >= ranges[i].begin && ranges[i].end <= n,
+                  "%s: range %d [%lld, %lld) is unsorted, overlapping or outside [0, %lld)", who, i,
+                  (long long)ranges[i].begin, (long long)ranges[i].end, (long long)n);
+    DGS_CHECK_ARG((ranges[i].begin & 7) == 0 && ((ranges[i].end & 7) == 0 || ranges[i].end == n),
+                  "%s: range %d bounds must be multiples of 8 elements", who, i);
+    prev = ranges[i].end;
+  }
+  return DGS_OK;
+}
+
+template <typename P, typename G>
+int launch_adam(void* param, void* ea, void* eas, const void* grad, int64_t n, const Table<AdamHp>& T,
+                const float* tn, float max_norm, cudaStream_t st) {
+  const long long tiles = (n + StepCfg<P, G>::TILE - 1) / StepCfg<P, G>::TILE;
+  const int grid = persistent_grid<adam_kernel<P, G>>(tiles);
+  adam_kernel<P, G><<<grid, kThreads, 0, st>>>((P*)param, (P*)ea, (P*)eas, (const G*)grad, n, T, tn, max_norm);
+  DGS_LAUNCHED();
+  return DGS_OK;
+}
+
+template <typename P, typename G>
+int launch_sgd(void* param, void* buf, const void* grad, int64_t n, const Table<SgdHp>& T,
+               const float* tn, float max_norm, cudaStream_t st) {
+  const long long tiles = (n + StepCfg<P, G>::TILE - 1) / StepCfg<P, G>::TILE;
+  if (buf != nullptr) {
+    const int grid = persistent_grid<sgd_kernel<P, G, true>>(tiles);
+    sgd_kernel<P, G, true><<<grid, kThreads, 0, st>>>((P*)param, (P*)buf, (const G*)grad, n, T, tn, max_norm);
+  } else {
+    const int grid = persistent_grid<sgd_kernel<P, G, false>>(tiles);
+    sgd_kernel<P, G, false><<<grid, kThreads, 0, st>>>((P*)param, nullptr, (const G*)grad, n, T, tn, max_norm);
+  }
+  DGS_LAUNCHED();
+  return DGS_OK;
+}
+
+}  // namespace
+}  // namespace dgs
+
+extern "C" int dgs_step_adam(void* param, void* exp_avg, void* exp_avg_sq, int state_dtype,
+                             const void* grad, int grad_dtype, int64_t n,
+                             const dgs_adam_range* ranges, int n_ranges, const float* total_norm,
+                             float max_norm, dgs_stream_t stream) {
+  using namespace dgs;
+  DGS_CHECK_ARG(n >= 0, "dgs_step_adam: n < 0");
+  if (int rc = check_ranges("dgs_step_adam", ranges, n_ranges, n)) return rc;
+  if (n == 0 || n_ranges == 0) return DGS_OK;
+  DGS_CHECK_ARG(param && exp_avg && exp_avg_sq && grad, "dgs_step_adam: NULL buffer");
+  DGS_CHECK_ARG(aligned16(param) && aligned16(exp_avg) && aligned16(exp_avg_sq) && aligned16(grad),
+                "dgs_step_adam: buffers must be 16-byte aligned");
+  Table<AdamHp> T;
+  T.n = n_ranges;
+  for (int i = 0; i < n_ranges; ++i) {
+    const dgs_adam_range& r = ranges[i];
+    AdamHp& h = T.r[i];
+    h.begin = r.begin;
+    h.end = r.end;
+    h.flags = r.flags;
+    if (r.flags & DGS_ADAM_DECOUPLED_WD) h.decay = (float)(1.0 - r.lr * r.weight_decay);
+    else h.decay = (float)r.weight_decay;
+    h.w1 = (float)(1.0 - r.beta1);
+    h.beta2 = (float)r.beta2;
+    h.w2 = (float)(1.0 - r.beta2);
+    h.eps = (float)r.eps;
+    h.neg_step = (float)(-r.step_size);
+    h.bc2_sqrt = (float)r.bias_correction2_sqrt;
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+#define DGS_ADAM_CASE(PD, PT, GD, GT) \
+  if (state_dtype == PD && grad_dtype == GD) \
+    return launch_adam<PT, GT>(param, exp_avg, exp_avg_sq, grad, n, T, total_norm, max_norm, st);
+  DGS_ADAM_CASE(DGS_F32, float, DGS_F32, float)
+  DGS_ADAM_CASE(DGS_F32, float, DGS_BF16, __nv_bfloat16)
+  DGS_ADAM_CASE(DGS_F32, float, DGS_F16, __half)
+  DGS_ADAM_CASE(DGS_BF16, __nv_bfloat16, DGS_F32, float)
+  DGS_ADAM_CASE(DGS_BF16, __nv_bfloat16, DGS_BF16, __nv_bfloat16)
+  DGS_ADAM_CASE(DGS_F16, __half, DGS_F32, float)
+  DGS_ADAM_CASE(DGS_F16, __half, DGS_F16, __half)
+#undef DGS_ADAM_CASE
+  return fail(DGS_EUNSUPPORTED, "dgs_step_adam: state dtype %d with grad dtype %d", state_dtype, grad_dtype);
+}
+
+extern "C" int dgs_step_sgd(void* param, void* momentum_buf, int state_dtype, const void* grad,
+                            int grad_dtype, int64_t n, const dgs_sgd_range* ranges, int n_ranges,
+                            const float* total_norm, float max_norm, dgs_stream_t stream) {
+  using namespace dgs;
+  DGS_CHECK_ARG(n >= 0, "dgs_step_sgd: n < 0");
+  if (int rc = check_ranges("dgs_step_sgd", ranges, n_ranges, n)) return rc;
+  if (n == 0 || n_ranges == 0) return DGS_OK;
+  DGS_CHECK_ARG(param && grad, "dgs_step_sgd: NULL buffer");
+  DGS_CHECK_ARG(aligned16(param) && aligned16(grad) && aligned16(momentum_buf),
+                "dgs_step_sgd: buffers must be 16-byte aligned");
+  Table<SgdHp> T;
+  T.n = n_ranges;
+  for (int i = 0; i < n_ranges; ++i) {
+    const dgs_sgd_range& r = ranges[i];
+    DGS_CHECK_ARG(r.momentum == 0.0 || momentum_buf != nullptr,
+                  "dgs_step_sgd: range %d has momentum but momentum_buf is NULL", i);
+    SgdHp& h = T.r[i];
+    h.begin = r.begin;
+    h.end = r.end;
+    h.flags = r.flags;
+    h.pad_ = 0;
+    h.wd = (float)r.weight_decay;
+    h.momentum = (float)r.momentum;
+    h.w_g = (float)(1.0 - r.dampening);
+    h.neg_lr = (float)(-r.lr);
+  }
+  // a buffer is only touched by ranges with momentum != 0; mixed tables are split by the caller
+  bool any_mom = false, all_mom = true;
+  for (int i = 0; i < n_ranges; ++i) {
+    if (ranges[i].momentum != 0.0) any_mom = true; else all_mom = false;
+  }
+  DGS_CHECK_ARG(!any_mom || all_mom, "dgs_step_sgd: ranges with and without momentum must go in separate calls");
+  void* buf = any_mom ? momentum_buf : nullptr;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+#define DGS_SGD_CASE(PD, PT, GD, GT) \
+  if (state_dtype == PD && grad_dtype == GD) \
+    return launch_sgd<PT, GT>(param, buf, grad, n, T, total_norm, max_norm, st);
+  DGS_SGD_CASE(DGS_F32, float, DGS_F32, float)
+  DGS_SGD_CASE(DGS_F32, float, DGS_BF16, __nv_bfloat16)
+  DGS_SGD_CASE(DGS_F32, float, DGS_F16, __half)
+  DGS_SGD_CASE(DGS_BF16, __nv_bfloat16, DGS_F32, float)
+  DGS_SGD_CASE(DGS_BF16, __nv_bfloat16, DGS_BF16, __nv_bfloat16)
+  DGS_SGD_CASE(DGS_F16, __half, DGS_F32, float)
+  DGS_SGD_CASE(DGS_F16, __half, DGS_F16, __half)
+#undef DGS_SGD_CASE
+  return fail(DGS_EUNSUPPORTED, "dgs_step_sgd: state dtype %d with grad dtype %d", state_dtype, grad_dtype);
+}

@@ -1,0 +1,241 @@
+/*
+ * dgs.h -- C ABI of libdgs.so ("determined grad sync"), the B200 (sm_100a) replacement for the
+ * per-step data-parallel path of Determined's PyTorch harness.
+ *
+ * The reference has no FFI for this path: its hot path is Python calling into torch
+ * (DistributedDataParallel, torch.optim, clip_grad_norm_) -- see SURVEY.md section 8(b).  Each entry
+ * point below therefore cites the reference *call site* (path relative to the reference tree, H/ =
+ * harness/determined/) whose work it takes over.
+ *
+ * Conventions
+ *   - plain C: pointers, sizes, scalars.  No torch / C++ types cross this boundary.
+ *   - every function returns 0 on success, a DGS_E* code otherwise; dgs_last_error() gives the
+ *     thread-local message of the last failure on the calling thread.
+ *   - device pointers are owned by the caller.  Unless a function says otherwise the library never
+ *     allocates or frees device memory; scratch is passed in by the caller.
+ *   - streams are raw cudaStream_t values passed as void*; all work is enqueued asynchronously and
+ *     nothing here blocks the host except dgs_comm_init / dgs_comm_destroy.
+ *   - "flat buffer": one contiguous device array holding every tensor of one optimizer, each tensor
+ *     starting at a multiple of DGS_ALIGN_BYTES bytes (gaps are zero).
+ */
+#ifndef DGS_H_
+#define DGS_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DGS_VERSION 100 /* 0.1.0 */
+#define DGS_ALIGN_BYTES 128
+
+/* status codes */
+#define DGS_OK 0
+#define DGS_EINVAL 1       /* bad argument (null pointer, misaligned buffer, unknown dtype, ...) */
+#define DGS_ECUDA 2        /* a CUDA runtime call failed */
+#define DGS_ENCCL 3        /* an NCCL call failed, or libnccl.so.2 could not be loaded */
+#define DGS_EUNSUPPORTED 4 /* valid request this build does not implement */
+
+/* element types */
+#define DGS_F32 0
+#define DGS_BF16 1
+#define DGS_F16 2
+#define DGS_F64 3
+#define DGS_I64 4
+
+typedef void* dgs_stream_t; /* cudaStream_t */
+
+int dgs_version(void);
+const char* dgs_last_error(void);
+/* Number of CUDA kernels this library has launched in this process (all threads). */
+int64_t dgs_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * 1. flatten / accumulate / scale / cast
+ *
+ * Replaces: autograd's per-parameter `grad += new` under DDP.no_sync()
+ * (H/pytorch/_pytorch_context.py:802-812), DDP's copy of grad/N into its buckets on the boundary
+ * backward (:813-816, torch Reducer), and the per-parameter `p.grad.data.div_(A)` loop of
+ * _average_gradients (:818-825).
+ *
+ * One launch handles every gradient tensor of one bucket: tensor i has `numel` elements of
+ * `grad_dtype` at `src` and lands at element offset `dst_off` of the bucket.
+ *   mode 0                          acc[dst]  = g                      (first micro-batch)
+ *   mode DGS_READ_ACC               acc[dst] += g                      (middle micro-batches)
+ *   mode DGS_WRITE_WIRE             wire[dst] = cast(g * scale)        (boundary, A == 1)
+ *   mode DGS_READ_ACC|DGS_WRITE_WIRE wire[dst] = cast((acc[dst]+g)*scale)  (boundary, A > 1)
+ * `acc` is fp32 and may be NULL when it is neither read nor written; `wire` (of `wire_dtype`:
+ * F32/BF16/F16) may be NULL when DGS_WRITE_WIRE is not set.  scale is 1/(N*A) for averaged
+ * gradients, 1/N when average_aggregated_gradients is false.  `segs` is a HOST array; dst_off must be
+ * a multiple of 8 elements, src should be 16-byte aligned (unaligned sources take a scalar path).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct dgs_seg {
+  const void* src;
+  int64_t dst_off;
+  int64_t numel;
+} dgs_seg;
+
+#define DGS_READ_ACC 1
+#define DGS_WRITE_WIRE 2
+
+int dgs_flatten_accumulate(const dgs_seg* segs, int n_segs, int grad_dtype, float* acc, void* wire,
+                           int wire_dtype, int mode, float scale, dgs_stream_t stream);
+
+/* wire[i] = cast(acc[i] * scale) for i in [0, n): finishes a bucket whose last gradient never
+ * arrived through a hook (same reference lines as above). */
+int dgs_scale_cast(const float* acc, void* wire, int wire_dtype, int64_t n, float scale,
+                   dgs_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * 2. global L2 norm, two passes, no host synchronisation
+ *
+ * Replaces: the user's clip_grads callable == torch.nn.utils.clip_grad_norm_(params, max_norm)
+ * invoked at H/pytorch/_pytorch_context.py:902 (torch: _foreach_norm + vector_norm of the stack).
+ *
+ * pass 1: dgs_l2norm_partial writes dgs_l2norm_grid(n) per-block sums of squares (fp32) to
+ *         `partials` (warp-shuffle + shared-memory block reduction).
+ * pass 2: dgs_l2norm_final reduces `n_partials` values in double and writes sqrt(sum) to
+ *         out_norm[0] (device fp32), which the step kernels read.
+ * Several flat buffers can share one pass 2 by writing their partials side by side.
+ * ---------------------------------------------------------------------------------------------- */
+#define DGS_NORM_MAX_PARTIALS 2368 /* 148 SMs x 16 */
+
+int dgs_l2norm_grid(int64_t n);
+int dgs_l2norm_partial(const void* x, int dtype, int64_t n, float* partials, dgs_stream_t stream);
+int dgs_l2norm_final(const float* partials, int n_partials, float* out_norm, dgs_stream_t stream);
+/* both passes; `partials` must hold dgs_l2norm_grid(n) floats */
+int dgs_l2norm(const void* x, int dtype, int64_t n, float* partials, float* out_norm,
+               dgs_stream_t stream);
+
+/* g[i] *= min(max_norm / (total_norm[0] + 1e-6), 1) -- the unfused tail of clip_grad_norm_, used
+ * only when the optimizer step itself stays in torch (optimizers other than SGD/Adam/AdamW). */
+int dgs_clip_scale(void* g, int dtype, int64_t n, const float* total_norm, float max_norm,
+                   dgs_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * 3. fused clip + optimizer step
+ *
+ * Replaces: clip_grads(parameters) + optimizer.step() + optimizer.zero_grad() at
+ * H/pytorch/_pytorch_context.py:902-924, for torch.optim.AdamW / Adam (amsgrad=False) and
+ * torch.optim.SGD.  Formulas follow torch 2.11 torch/optim/adamw.py, adam.py
+ * (_single_tensor_adam) and sgd.py (_single_tensor_sgd).
+ *
+ * param / state / grad are flat buffers with the same element layout.  Hyper-parameters are
+ * per range (a run of tensors of one param group with the same step count); elements outside
+ * every range are left untouched (parameters that received no gradient).  Range bounds must be
+ * multiples of 8 elements (the last `end` may be n).  At most DGS_MAX_RANGES per call.
+ * If total_norm != NULL every gradient is first multiplied by
+ * min(max_norm / (total_norm[0] + 1e-6), 1)  (torch/nn/utils/clip_grad.py).
+ * The accumulator needs no zeroing: the next window's first micro-batch overwrites it.
+ * ---------------------------------------------------------------------------------------------- */
+#define DGS_MAX_RANGES 24
+
+#define DGS_OPT_MAXIMIZE 1
+#define DGS_ADAM_DECOUPLED_WD 2 /* AdamW: p *= 1 - lr*wd ; otherwise Adam: g += wd*p */
+#define DGS_SGD_NESTEROV 4
+#define DGS_SGD_FIRST_STEP 8 /* momentum buffer does not exist yet: buf = g */
+
+/* Hyper-parameters are doubles, exactly the Python floats torch.optim holds in param_groups; the
+ * kernels derive their fp32 constants from them the way torch does (double arithmetic, then one
+ * rounding to fp32). */
+typedef struct dgs_adam_range {
+  int64_t begin, end;
+  double lr, beta1, beta2, eps, weight_decay;
+  double step_size;             /* lr / (1 - beta1^t) */
+  double bias_correction2_sqrt; /* sqrt(1 - beta2^t) */
+  int32_t flags;
+  int32_t _pad;
+} dgs_adam_range;
+
+typedef struct dgs_sgd_range {
+  int64_t begin, end;
+  double lr, momentum, dampening, weight_decay;
+  int32_t flags;
+  int32_t _pad;
+} dgs_sgd_range;
+
+int dgs_step_adam(void* param, void* exp_avg, void* exp_avg_sq, int state_dtype, const void* grad,
+                  int grad_dtype, int64_t n, const dgs_adam_range* ranges, int n_ranges,
+                  const float* total_norm, float max_norm, dgs_stream_t stream);
+
+/* momentum_buf may be NULL when every range has momentum == 0 */
+int dgs_step_sgd(void* param, void* momentum_buf, int state_dtype, const void* grad, int grad_dtype,
+                 int64_t n, const dgs_sgd_range* ranges, int n_ranges, const float* total_norm,
+                 float max_norm, dgs_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * 4. metric reducer
+ *
+ * Replaces: the per-batch `metric.cpu().detach().numpy()` at H/pytorch/_pytorch_trial.py:920-927,
+ * _average_training_metrics (H/pytorch/_metric_utils.py:29-60), the batch mean of
+ * util.make_metrics (H/util.py:171-196) and _simple_reduce_metrics (H/pytorch/_reducer.py:28-46).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct dgs_scalar_ref {
+  const void* ptr; /* device scalar, or NULL for "this batch has no value" (Python None) */
+  int32_t dtype;
+  int32_t _pad;
+} dgs_scalar_ref;
+
+#define DGS_MAX_METRICS 64
+
+/* row[j] = (double)*refs[j].ptr, valid[j] = (refs[j].ptr != NULL); no host sync. refs is a HOST array. */
+int dgs_metric_pack(const dgs_scalar_ref* refs, int m, double* row, uint8_t* valid,
+                    dgs_stream_t stream);
+
+/* gathered [N][B][M] doubles with validity bytes [N][B][M], num_batches [N] (device int64).
+ * Ranks with num_batches == 0 are ignored.  per_batch[b][j] = mean over ranks of the valid values
+ * (per_batch_valid 0 if none); avg[j] = mean over b of the valid per_batch values; count[j] = how
+ * many batches contributed (int64, exact). */
+int dgs_metric_average(const double* gathered, const uint8_t* valid, const int64_t* num_batches,
+                       int n_ranks, int b, int m, double* per_batch, uint8_t* per_batch_valid,
+                       double* avg, int64_t* count, dgs_stream_t stream);
+
+/* Reducer enum values of H/pytorch/_reducer.py:9-25 */
+#define DGS_REDUCE_AVG 1
+#define DGS_REDUCE_SUM 2
+#define DGS_REDUCE_MAX 3
+#define DGS_REDUCE_MIN 4
+
+/* values [n][m] (device doubles), weights [n] device int64 or NULL (AVG only: np.average weights).
+ * out[j] = reduce over n of values[.][j]. */
+int dgs_metric_reduce(const double* values, const int64_t* weights, int n, int m, int op,
+                      double* out, dgs_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * 5. communicator: NCCL over NVLink on a side stream
+ *
+ * Replaces: dist.init_process_group (H/pytorch/_pytorch_trial.py:296-300), DDP's bucket allreduce
+ * and constructor / per-forward broadcasts (H/pytorch/_pytorch_context.py:296), hvd.broadcast_*
+ * (H/pytorch/_pytorch_trial.py:617-620) and the tensor payload of DistributedContext.gather /
+ * allgather (H/core/_distributed.py:287-356).
+ *
+ * libnccl.so.2 is resolved at run time with dlopen (the copy torch already loaded, if any).
+ * The 128-byte unique id travels between ranks through the caller's control plane.
+ * Collectives run on a high-priority stream owned by the communicator: each *_async call makes
+ * that stream wait for everything enqueued so far on `compute`; dgs_comm_wait makes `compute`
+ * wait for everything issued so far on the side stream.  Neither blocks the host.
+ * One owner thread per communicator.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct dgs_comm dgs_comm;
+
+int dgs_comm_unique_id(void* out128);
+int dgs_comm_init(const void* id128, int rank, int nranks, int device, dgs_comm** out);
+int dgs_comm_destroy(dgs_comm* comm);
+int dgs_comm_rank(const dgs_comm* comm, int* rank, int* nranks);
+/* in-place sum over ranks of buf[0..count) */
+int dgs_comm_allreduce_async(dgs_comm* comm, void* buf, int64_t count, int dtype,
+                             dgs_stream_t compute);
+int dgs_comm_broadcast_async(dgs_comm* comm, void* buf, int64_t bytes, int root,
+                             dgs_stream_t compute);
+/* recv holds nranks * bytes_per_rank bytes, ordered by rank */
+int dgs_comm_allgather_async(dgs_comm* comm, const void* send, void* recv, int64_t bytes_per_rank,
+                             dgs_stream_t compute);
+int dgs_comm_wait(dgs_comm* comm, dgs_stream_t compute);
+int dgs_nccl_version(int* version);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DGS_H_ */
