@@ -1,0 +1,81 @@
+"""Load the golden fixtures recorded from the reference harness (tests/golden/make_golden.py)."""
+import pathlib
+import sys
+from typing import Any, Dict, List
+
+import numpy as np
+
+GOLDEN = pathlib.Path(__file__).resolve().parent / "golden"
+sys.path.insert(0, str(GOLDEN))
+sys.path.insert(0, str(GOLDEN.parent.parent))
+
+from golden_model import SCENARIOS  # noqa: E402
+
+N_PARAMS = 6  # fc1.weight, fc1.bias, norm.weight, norm.bias, fc2.weight, fc2.bias
+# torch optimizer param order produced by golden_model.param_groups: decay group (ndim >= 2) first
+GROUP_OF = [0, 1, 1, 1, 0, 1]
+# clip_grads sees the parameters in optimizer order (param_groups flattened); model index of each
+OPT_ORDER = [0, 4, 1, 2, 3, 5]
+
+
+class Golden:
+    def __init__(self, name: str) -> None:
+        self.name = name
+        self.sc = SCENARIOS[name]
+        self.hp: Dict[str, Any] = self.sc["hp"]
+        self.slots, self.agg, self.steps = self.sc["slots"], self.sc["agg"], self.sc["steps"]
+        self.dtype: str = self.sc["dtype"]
+        self.clip = self.sc["clip"]
+        with np.load(GOLDEN / f"{name}.npz") as z:
+            self.z = {k: z[k] for k in z.files}
+
+    def init_params(self) -> List[np.ndarray]:
+        return [self.z[f"init_params/{i}"] for i in range(N_PARAMS)]
+
+    def raw(self, step: int) -> List[List[List[np.ndarray]]]:
+        """raw[r][m][i] for optimizer step `step`."""
+        return [
+            [[self.z[f"rank{r}/raw_grads/{step * self.agg + m}/{i}"] for i in range(N_PARAMS)] for m in range(self.agg)]
+            for r in range(self.slots)
+        ]
+
+    def per_step(self, key: str, step: int) -> List[np.ndarray]:
+        """Per-parameter arrays of optimizer step `step`, always returned in MODEL order."""
+        vals = [self.z[f"{key}/{step}/{i}"] for i in range(N_PARAMS)]
+        if key in ("avg_grads", "clipped_grads"):  # recorded in optimizer order
+            out: List[Any] = [None] * N_PARAMS
+            for j, i in enumerate(OPT_ORDER):
+                out[i] = vals[j]
+            return out
+        return vals
+
+    def state(self, step: int, i: int, key: str) -> np.ndarray:
+        return self.z[f"state/{step}/{i}/{key}"]
+
+    def loss(self, rank: int) -> np.ndarray:
+        return self.z[f"rank{rank}/loss"]
+
+    def groups(self) -> List[Dict[str, Any]]:
+        hp = self.hp
+        base = {k: hp[k] for k in ("lr", "momentum", "dampening", "nesterov", "betas", "eps") if k in hp}
+        return [dict(base, weight_decay=hp.get("weight_decay", 0.0)), dict(base, weight_decay=0.0)]
+
+
+def tolerances(dtype: str) -> Dict[str, float]:
+    # north_star: rel 1e-5 fp32 / 1e-2 bf16 for gradients, norms, parameters and averaged metrics
+    if dtype == "float32":
+        return dict(rtol=1e-5, atol=1e-7)
+    return dict(rtol=1e-2, atol=2e-4)
+
+
+def assert_close(actual: Any, desired: Any, dtype: str, what: str = "", scale: Any = None) -> None:
+    """rel 1e-5 (fp32) / 1e-2 (bf16), relative to each element or -- for elements that are the
+    result of cancellation -- to the magnitude of the operands (`scale`, default max |desired|):
+    a bf16 sum of two gradients of size 0.03 carries an absolute error of about one ulp of 0.03
+    however small the sum is."""
+    actual = np.asarray(actual, dtype=np.float64)
+    desired = np.asarray(desired, dtype=np.float64)
+    rtol = 1e-5 if dtype == "float32" else 1e-2
+    if scale is None:
+        scale = float(np.max(np.abs(desired))) if desired.size else 0.0
+    np.testing.assert_allclose(actual, desired, rtol=rtol, atol=rtol * float(scale) + 1e-30, err_msg=what)
