@@ -17,7 +17,7 @@ REDUCE_AVG, REDUCE_SUM, REDUCE_MAX, REDUCE_MIN = 1, 2, 3, 4
 MAX_RANGES = 24
 MAX_METRICS = 64
 ALIGN_BYTES = 128
-NORM_MAX_PARTIALS = 2368
+NORM_MAX_PARTIALS = 9472
 
 
 class Seg(ctypes.Structure):

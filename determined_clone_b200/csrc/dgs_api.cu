@@ -3,6 +3,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 
 namespace dgs {
 
@@ -36,6 +37,17 @@ int sm_count() {
     }
     cache[dev].store(v, std::memory_order_relaxed);
   }
+  return v;
+}
+
+int grid_mult() {
+  static const int v = [] {
+    const char* e = getenv("DGS_GRID_MULT");
+    int m = e ? atoi(e) : 0;
+    // Measured on B200 (gpurun_out/sweep_grid.txt): one tile per CTA beats a persistent grid-stride loop
+    // by 5-15% on mixed read/write streams (CTAs stay in address order, so DRAM pages stay open).
+    return m > 0 ? m : 4096;
+  }();
   return v;
 }
 

@@ -16,6 +16,8 @@ namespace dgs {
 int fail(int code, const char* fmt, ...);
 extern std::atomic<int64_t> g_launches;
 int sm_count();  // SMs of the current device (148 on B200), cached per device
+// Upper bound on the grid of a streaming kernel, in CTAs per SM (env DGS_GRID_MULT overrides, for tuning).
+int grid_mult();
 
 #define DGS_CHECK_ARG(cond, ...)                     \
   do {                                               \

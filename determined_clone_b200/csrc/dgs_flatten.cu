@@ -5,7 +5,7 @@
 // (:813-816) and the per-parameter div_(A) of _average_gradients (:818-825).
 //
 // HBM-bound, no reuse: one pass, every warp-level access a contiguous 512 B (fp32) run, 4 independent
-// 16 B accesses per array per thread in flight, grid = min(tiles, 8 CTAs x SMs).
+// 16 B accesses per array per thread in flight, one tile per CTA (see grid_mult() in dgs_api.cu).
 #include "dgs_common.cuh"
 
 namespace dgs {
@@ -143,7 +143,7 @@ int launch_flatten(const dgs_seg* segs, int n_segs, float* acc, void* wire, floa
     if (m == 0) continue;
     P.n = m;
     P.tiles = tiles;
-    const long long cap = (long long)sm_count() * 8;
+    const long long cap = (long long)sm_count() * grid_mult();
     const int grid = (int)(tiles < cap ? tiles : cap);
     flatten_kernel<G, W, RA, WW><<<grid, kThreads, 0, st>>>(P, acc, static_cast<W*>(wire), scale);
     DGS_LAUNCHED();
@@ -216,7 +216,7 @@ extern "C" int dgs_scale_cast(const float* acc, void* wire, int wire_dtype, int6
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const long long nvec = (n + 3) / 4;
   const long long want = (nvec + kThreads - 1) / kThreads;
-  const long long cap = (long long)sm_count() * 8;
+  const long long cap = (long long)sm_count() * grid_mult();
   const int grid = (int)(want < cap ? want : cap);
   switch (wire_dtype) {
     case DGS_F32: scale_cast_kernel<float><<<grid, kThreads, 0, st>>>(acc, (float*)wire, n, scale); break;

@@ -78,12 +78,10 @@ clip_scale_kernel(T* __restrict__ g, long long n, const float* __restrict__ tota
 }
 
 int grid_for(int64_t n) {
-  // one CTA per 16 Ki elements, capped at 16 CTAs per SM's worth of partials
+  // one CTA per 16 Ki elements, capped by the size of the partials scratch
   long long want = (n + 16383) / 16384;
   if (want < 1) want = 1;
-  long long cap = (long long)sm_count() * 16;
-  if (cap > DGS_NORM_MAX_PARTIALS) cap = DGS_NORM_MAX_PARTIALS;
-  return (int)(want < cap ? want : cap);
+  return (int)(want < DGS_NORM_MAX_PARTIALS ? want : DGS_NORM_MAX_PARTIALS);
 }
 
 }  // namespace
@@ -137,7 +135,7 @@ extern "C" int dgs_clip_scale(void* g, int dtype, int64_t n, const float* total_
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   long long want = (n / 4 + kThreads - 1) / kThreads;
   if (want < 1) want = 1;
-  const long long cap = (long long)sm_count() * 8;
+  const long long cap = (long long)sm_count() * grid_mult();
   const int grid = (int)(want < cap ? want : cap);
   switch (dtype) {
     case DGS_F32: clip_scale_kernel<float><<<grid, kThreads, 0, st>>>((float*)g, n, total_norm, max_norm); break;

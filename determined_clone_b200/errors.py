@@ -1,0 +1,10 @@
+"""Exception types of the reference harness used on the grad-sync path
+(reference harness/determined/errors.py; raised at harness/determined/pytorch/_pytorch_context.py:289,347,351,715,869)."""
+
+
+class InternalException(Exception):
+    """The harness itself is in an unexpected state."""
+
+
+class InvalidExperimentException(Exception):
+    """The user's experiment or trial code misuses the API."""

@@ -100,7 +100,7 @@ int dgs_scale_cast(const float* acc, void* wire, int wire_dtype, int64_t n, floa
  *         out_norm[0] (device fp32), which the step kernels read.
  * Several flat buffers can share one pass 2 by writing their partials side by side.
  * ---------------------------------------------------------------------------------------------- */
-#define DGS_NORM_MAX_PARTIALS 2368 /* 148 SMs x 16 */
+#define DGS_NORM_MAX_PARTIALS 9472 /* 148 SMs x 64 */
 
 int dgs_l2norm_grid(int64_t n);
 int dgs_l2norm_partial(const void* x, int dtype, int64_t n, float* partials, dgs_stream_t stream);
