@@ -1,0 +1,20 @@
+"""B200-native replacement for the per-step data-parallel path of Determined's PyTorch harness.
+
+    import determined_clone_b200 as det
+    from determined_clone_b200 import pytorch, core
+
+`pytorch` and `core` expose the same names the reference's determined.pytorch / determined.core expose
+on this path (PyTorchTrial, PyTorchTrialContext, MetricReducer, DistributedContext, ...).  The compute
+lives in csrc/libdgs.so (hand-written sm_100a kernels + NCCL); see include/dgs.h and DESIGN.md.
+"""
+from determined_clone_b200 import errors, util  # noqa: F401
+
+__version__ = "0.1.0"
+
+
+def __getattr__(name: str):  # lazy: importing the package must not import torch
+    if name in ("pytorch", "core"):
+        import importlib
+
+        return importlib.import_module(f"determined_clone_b200.{name}")
+    raise AttributeError(name)

@@ -1,0 +1,475 @@
+"""PyTorchTrialContext: the object a PyTorchTrial talks to.
+
+Drop-in for the per-step surface of the reference's context
+(reference harness/determined/pytorch/_pytorch_context.py): wrap_model :284-311, wrap_optimizer
+:313-378, _should_communicate_and_update :711-716, backward :718-816, _average_gradients :818-825,
+step_optimizer :827-924, plus the reducer API it inherits (:36, _reducer.py:273-518).  Same
+signatures, same exceptions and texts, same gating on aggregation_frequency -- but no torch DDP and no
+Horovod underneath: gradients go through GradSyncEngine (libdgs.so kernels + NCCL side stream).
+
+Differences a user can observe, all documented in DESIGN.md:
+  * wrap_model returns the model itself on the device (no DistributedDataParallel wrapper, so
+    state_dict keys carry no "module." prefix); parameters become views of one flat buffer.
+  * between batches p.grad is None (as after zero_grad(set_to_none=True)); inside a clip_grads
+    callable p.grad are views of the synchronized, averaged gradient buffer.
+  * 16-bit gradients are accumulated in fp32 across micro-batches and rounded once.
+"""
+import contextlib
+import logging
+from typing import Any, Callable, Dict, Iterator, List, Optional, Set, Type, Union
+
+import torch
+from torch import nn
+
+from determined_clone_b200 import _lib, core, errors, util
+from determined_clone_b200.pytorch import _gradsync
+from determined_clone_b200.pytorch._comm import Comm
+from determined_clone_b200.pytorch._reducer import _PyTorchReducerContext
+
+logger = logging.getLogger("determined.pytorch")
+
+
+class PyTorchExperimentalContext:
+    def __init__(self, parent: Any) -> None:
+        self._parent = parent
+        self._auto_amp = False
+        self._auto_to_device = True
+
+    def disable_auto_to_device(self) -> None:
+        self._auto_to_device = False
+
+
+class _BufferSync:
+    """DDP's broadcast_buffers=True: before every training forward, rank 0's module buffers (batch-norm
+    running statistics, ...) overwrite every other rank's.  Buffers of one dtype live in one flat
+    tensor so that this is one NCCL broadcast per dtype."""
+
+    def __init__(self, model: nn.Module, comm: Comm) -> None:
+        self.comm = comm
+        self.flats: List[torch.Tensor] = []
+        by_dtype: Dict[torch.dtype, List[Any]] = {}
+        seen: Set[int] = set()
+        for mod in model.modules():
+            for name, buf in list(mod._buffers.items()):
+                if buf is None or id(buf) in seen or not buf.is_cuda:
+                    continue
+                seen.add(id(buf))
+                by_dtype.setdefault(buf.dtype, []).append((mod, name, buf))
+        for dtype, items in by_dtype.items():
+            total = sum(b.numel() for _, _, b in items)
+            flat = torch.empty(total, dtype=dtype, device=items[0][2].device)
+            off = 0
+            for mod, name, buf in items:
+                view = flat[off:off + buf.numel()].view(buf.shape)
+                view.copy_(buf)
+                mod._buffers[name] = view
+                off += buf.numel()
+            self.flats.append(flat)
+        if self.flats:
+            self.sync()
+            model.register_forward_pre_hook(self._pre_forward)
+
+    def sync(self) -> None:
+        for flat in self.flats:
+            self.comm.broadcast(flat, 0)
+        self.comm.wait()
+
+    def _pre_forward(self, module: nn.Module, args: Any) -> None:
+        if module.training and torch.is_grad_enabled():
+            self.sync()
+
+
+class PyTorchTrialContext(_PyTorchReducerContext):
+    """Runtime context of one PyTorchTrial.
+
+    Constructor arguments follow the reference (core_context, trial_seed, hparams, slots_per_trial,
+    num_gpus, exp_conf, aggregation_frequency, steps_completed, managed_training, debug_enabled,
+    enable_tensorboard_logging).  `core_context` only needs a `.distributed` attribute; a bare
+    DistributedContext can be given instead through `distributed=`.
+    """
+
+    def __init__(
+        self,
+        core_context: Any = None,
+        trial_seed: Optional[int] = None,
+        hparams: Optional[Dict] = None,
+        slots_per_trial: int = 1,
+        num_gpus: int = 1,
+        exp_conf: Optional[Dict[str, Any]] = None,
+        aggregation_frequency: int = 1,
+        steps_completed: int = 0,
+        managed_training: bool = True,
+        debug_enabled: bool = False,
+        enable_tensorboard_logging: bool = False,
+        distributed: Optional[core.DistributedContext] = None,
+        device: Optional[torch.device] = None,
+    ) -> None:
+        self._core = core_context
+        if distributed is None:
+            distributed = getattr(core_context, "distributed", None) or core.DummyDistributedContext()
+        self.distributed = distributed
+        _PyTorchReducerContext.__init__(self, self.distributed.allgather)
+        self._per_slot_batch_size, self._global_batch_size = (
+            util.calculate_batch_sizes(hparams=hparams, slots_per_trial=slots_per_trial, trialname="PyTorchTrial")
+            if hparams and hparams.get("global_batch_size", None)
+            else (None, None)
+        )
+        self._hparams = hparams
+        self._num_gpus = num_gpus
+        self._debug_enabled = debug_enabled
+        self._exp_conf = exp_conf
+        self._trial_seed = trial_seed
+        self._steps_completed = steps_completed
+        self.device = device if device is not None else self._init_device()
+        self._to_device_warned_types: Set[Type] = set()
+
+        self.models: List[nn.Module] = []
+        self.optimizers: List[torch.optim.Optimizer] = []
+        self.profiler: Any = None
+        self.lr_schedulers: List[Any] = []
+        self._epoch_len: Optional[int] = None
+        self._wrapped_models: Dict[nn.Module, nn.Module] = {}
+        self._optimizer_configs: Dict[Any, Any] = {}
+        self._main_model = nn.Module()
+        self._scaler: Any = None
+        self._use_apex = False
+        self._loss_ids: Dict[torch.Tensor, int] = {}
+        self._last_backward_batch_idx: Optional[int] = None
+        self._current_batch_idx: Optional[int] = None
+
+        self.experimental = PyTorchExperimentalContext(self)
+        self._managed_training = managed_training
+        self._aggregation_frequency = aggregation_frequency
+        self._fp16_compression_default = False
+        self._average_aggregated_gradients_default = True
+        self._is_pre_trainer = False
+
+        # grad-sync state
+        self._engines: Dict[torch.optim.Optimizer, _gradsync.GradSyncEngine] = {}
+        self._buffer_syncs: List[_BufferSync] = []
+        self._backward_calls = 0
+        self._backward_calls_batch: Optional[int] = None
+        self._comm: Optional[Comm] = None
+
+    # ---- device / communicator ----------------------------------------------------------------
+    def _init_device(self) -> torch.device:
+        if not torch.cuda.is_available():
+            # the reference falls back to CPU here (_pytorch_context.py:481-494); the grad-sync path
+            # does not exist on CPU, so model code may run but wrap_optimizer() will refuse.
+            return torch.device("cpu")
+        index = self.distributed.local_rank if self.distributed.size > 1 else torch.cuda.current_device()
+        torch.cuda.set_device(index)
+        return torch.device("cuda", index)
+
+    def _get_comm(self) -> Optional[Comm]:
+        if self.distributed.size < 2:
+            return None
+        if self._comm is None:
+            self._comm = self.distributed.attach_comm(lambda d: Comm.from_distributed(d, self.device))
+        return self._comm
+
+    def _set_default_gradient_compression(self, gradient_compression: bool) -> None:
+        self._fp16_compression_default = gradient_compression
+
+    def _set_default_average_aggregated_gradients(self, average_aggregated_gradients: bool) -> None:
+        self._average_aggregated_gradients_default = average_aggregated_gradients
+
+    # ---- trial-facing helpers -------------------------------------------------------------------
+    def get_hparams(self) -> Dict[str, Any]:
+        return self._hparams or {}
+
+    def get_hparam(self, name: str) -> Any:
+        if name not in self.get_hparams():
+            raise ValueError(
+                f"Could not find name '{name}' in experiment hyperparameters. Please check your "
+                "experiment configuration 'hyperparameters' section."
+            )
+        return self.get_hparams()[name]
+
+    def get_per_slot_batch_size(self) -> int:
+        if self._per_slot_batch_size is None:
+            raise ValueError("global_batch_size not specified in the hyperparameters")
+        return self._per_slot_batch_size
+
+    def get_global_batch_size(self) -> int:
+        if self._global_batch_size is None:
+            raise ValueError("global_batch_size not specified in the hyperparameters")
+        return self._global_batch_size
+
+    def current_train_batch(self) -> int:
+        if self._current_batch_idx is None:
+            raise errors.InternalException("Training hasn't started.")
+        return self._current_batch_idx
+
+    def to_device(self, data: Any) -> Any:
+        """Move a (nested) batch to this trial's device with non-blocking copies."""
+        if isinstance(data, torch.Tensor):
+            return data.to(self.device, non_blocking=True)
+        if isinstance(data, dict):
+            return {k: self.to_device(v) for k, v in data.items()}
+        if isinstance(data, (list, tuple)):
+            return type(data)(self.to_device(v) for v in data)
+        if type(data) not in self._to_device_warned_types:
+            self._to_device_warned_types.add(type(data))
+            logger.warning(f"Was not able to move data item of type '{type(data).__name__}' to device.")
+        return data
+
+    # ---- wrapping ---------------------------------------------------------------------------------
+    def wrap_model(self, model: nn.Module) -> nn.Module:
+        """Returns a wrapped model."""
+        if self._managed_training:
+            if self._use_apex:
+                raise errors.InvalidExperimentException("Must call wrap_model() before configure_apex_amp.")
+            model = model.to(self.device)
+            comm = self._get_comm()
+            if comm is not None:
+                # stands in for DistributedDataParallel(model): parameters are broadcast when the
+                # optimizer is wrapped (they are flattened there), buffers before every forward
+                self._buffer_syncs.append(_BufferSync(model, comm))
+            self._wrapped_models[model] = model
+        model_id = len(self.models)
+        self._main_model.__setattr__(f"model_{model_id}", model)
+        self.models.append(model)
+        return model
+
+    def wrap_optimizer(
+        self,
+        optimizer: torch.optim.Optimizer,
+        backward_passes_per_step: int = 1,
+        fp16_compression: Optional[bool] = None,
+        average_aggregated_gradients: Optional[bool] = None,
+    ) -> torch.optim.Optimizer:
+        """Returns a wrapped optimizer (the same object: its parameters and state now live in flat
+        buffers managed by the grad-sync engine)."""
+        if self._managed_training:
+            if self._use_apex:
+                raise errors.InvalidExperimentException("Must call wrap_optimizer() before configure_apex_amp.")
+            if backward_passes_per_step < 1:
+                raise errors.InvalidExperimentException(
+                    "backward_passes_per_step for local gradient aggregation must be >= 1; "
+                    f"got {backward_passes_per_step}."
+                )
+        if fp16_compression is None:
+            fp16_compression = self._fp16_compression_default
+        if average_aggregated_gradients is None:
+            average_aggregated_gradients = self._average_aggregated_gradients_default
+        self._optimizer_configs[optimizer] = {"average_aggregated_gradients": average_aggregated_gradients}
+        if self._managed_training:
+            self._engines[optimizer] = _gradsync.GradSyncEngine(
+                optimizer,
+                device=self.device,
+                comm=self._get_comm(),
+                aggregation_frequency=self._aggregation_frequency,
+                average_aggregated_gradients=bool(average_aggregated_gradients),
+                backward_passes_per_step=backward_passes_per_step,
+                fp16_compression=bool(fp16_compression) and self.distributed.size > 1,
+            )
+        self.optimizers.append(optimizer)
+        return optimizer
+
+    def wrap_lr_scheduler(self, lr_scheduler: Any, step_mode: Any = None, frequency: int = 1) -> Any:
+        from determined_clone_b200.pytorch._lr_scheduler import LRScheduler
+
+        opt = getattr(lr_scheduler, "optimizer", None)
+        if opt is not None and opt not in self.optimizers:
+            raise errors.InvalidExperimentException("Must use an optimizer that is returned by wrap_optimizer()")
+        wrapped = LRScheduler(lr_scheduler, step_mode if step_mode is not None else LRScheduler.StepMode.STEP_EVERY_BATCH, frequency)
+        self.lr_schedulers.append(wrapped)
+        return lr_scheduler
+
+    def wrap_scaler(self, scaler: Any) -> Any:
+        self._scaler = scaler
+        return scaler
+
+    # ---- gating -------------------------------------------------------------------------------------
+    @contextlib.contextmanager
+    def _no_sync(self) -> Iterator[None]:
+        # DDP's no_sync has nothing to switch off here: whether a backward pass communicates is
+        # decided per pass in backward().
+        yield
+
+    def _should_communicate_and_update(self) -> bool:
+        if not self._managed_training:
+            return True
+        if self._current_batch_idx is None:
+            raise errors.InternalException("Training hasn't started.")
+        return (self._current_batch_idx + 1) % self._aggregation_frequency == 0
+
+    # ---- backward ---------------------------------------------------------------------------------
+    def backward(
+        self,
+        loss: torch.Tensor,
+        gradient: Optional[torch.Tensor] = None,
+        retain_graph: bool = False,
+        create_graph: bool = False,
+    ) -> None:
+        """Compute the gradient of `loss` w.r.t. graph leaves (arguments as torch.Tensor.backward).
+
+        On micro-batches that are not an aggregation boundary the gradients are only accumulated into
+        the engines' fp32 buckets.  On the boundary pass each bucket is scaled by 1/(N*A), cast and
+        all-reduced as soon as it is complete, while autograd keeps running.
+        """
+        if self._scaler and self.experimental._auto_amp:
+            loss = self._scaler.scale(loss)
+        if self._backward_calls_batch != self._current_batch_idx:
+            self._backward_calls_batch, self._backward_calls = self._current_batch_idx, 0
+        self._backward_calls += 1
+        boundary = self._should_communicate_and_update() if self._engines else False
+        for eng in self._engines.values():
+            eng.begin_pass(final=boundary and self._backward_calls >= eng.bpps)
+        try:
+            loss.backward(gradient=gradient, retain_graph=retain_graph, create_graph=create_graph)  # type: ignore
+        finally:
+            for eng in self._engines.values():
+                eng.end_pass()
+
+    @staticmethod
+    def _average_gradients(parameters: Any, divisor: int) -> None:
+        """Reference semantics on explicit .grad tensors (kept for callers that use it directly; the
+        engine folds this division into the scale factor of its flatten kernel)."""
+        if divisor == 1:
+            return
+        divisor_value = float(divisor)
+        for p in parameters:
+            if p.grad is not None:
+                p.grad.data.div_(divisor_value)
+
+    # ---- optimizer step -----------------------------------------------------------------------------
+    def step_optimizer(
+        self,
+        optimizer: torch.optim.Optimizer,
+        clip_grads: Optional[Callable[[Iterator], None]] = None,
+        auto_zero_grads: bool = True,
+        scaler: Optional[Any] = None,
+    ) -> None:
+        """Perform a single optimization step: synchronize, average, clip, step, zero.
+
+        A no-op on batches that are not an aggregation boundary.  `clip_grads` receives the list of
+        parameters; if it calls torch.nn.utils.clip_grad_norm_ on them the norm comes from the L2-norm
+        kernels and the clipping is fused into the optimizer kernel; anything else it does to the
+        p.grad views is honoured as is.
+        """
+        if self._aggregation_frequency > 1 and not auto_zero_grads:
+            raise errors.InvalidExperimentException(
+                "if optimizations.aggregation_frequency is larger than 1, "
+                "auto_zero_grads must be set to true. ",
+            )
+        if not self._should_communicate_and_update():
+            return
+        eng = self._engines.get(optimizer)
+        if eng is None:
+            raise errors.InvalidExperimentException("step_optimizer() needs an optimizer returned by wrap_optimizer()")
+
+        present = eng.finish_window()
+        parameters = [p for group in optimizer.param_groups for p in group.get("params", [])]
+        if scaler is None and self.experimental._auto_amp:
+            scaler = self._scaler
+        aliased = all(fs.wire_dtype == fs.dtype for fs in eng.sets)
+        fused = eng.can_fuse() and scaler is None and (aliased or clip_grads is None)
+
+        clip_req: Optional[_gradsync.ClipRequest] = None
+        materialized = False
+        if clip_grads is not None or not fused or not auto_zero_grads:
+            eng.materialize_grads(present)
+            materialized = True
+        if clip_grads is not None:
+            if self._scaler and self.experimental._auto_amp:
+                self._scaler.unscale_(optimizer)
+            clip_req = _run_clip(eng, clip_grads, parameters, defer=fused and aliased)
+            if aliased:
+                _fold_back_replaced_grads(eng, present)
+
+        if fused:
+            eng.fused_step(present, clip_req)
+        elif scaler:
+            scaler.step(optimizer)
+        else:
+            optimizer.step()
+
+        if auto_zero_grads:
+            if materialized:
+                eng.clear_grads()
+        eng.reset_window()
+
+    # ---- epoch helpers the controller maintains ---------------------------------------------------
+    def is_epoch_start(self) -> bool:
+        if self._current_batch_idx is None:
+            raise errors.InternalException("Training hasn't started.")
+        if self._epoch_len is None:
+            raise errors.InternalException("Training DataLoader uninitialized.")
+        return self._current_batch_idx % self._epoch_len == 0
+
+    def is_epoch_end(self) -> bool:
+        if self._current_batch_idx is None:
+            raise errors.InternalException("Training hasn't started.")
+        if self._epoch_len is None:
+            raise errors.InternalException("Training DataLoader uninitialized.")
+        return self._current_batch_idx % self._epoch_len == self._epoch_len - 1
+
+    def current_train_epoch(self) -> int:
+        if self._current_batch_idx is None:
+            raise errors.InternalException("Training hasn't started.")
+        if self._epoch_len is None:
+            raise errors.InternalException("Training DataLoader uninitialized.")
+        return self._current_batch_idx // self._epoch_len
+
+    def close(self) -> None:
+        for eng in self._engines.values():
+            eng.close()
+
+
+def _fold_back_replaced_grads(eng: _gradsync.GradSyncEngine, present: List[List[bool]]) -> None:
+    """A clip function may assign a new tensor to p.grad instead of modifying it in place; copy such
+    tensors back into the wire buffer the optimizer kernel reads."""
+    for fs, have in zip(eng.sets, present):
+        for t, view, ok in zip(fs.tensors, fs.grad_views, have):
+            g = t.param.grad
+            if ok and g is not view and g is not None:
+                view.copy_(g)
+                t.param.grad = view
+
+
+def _run_clip(eng: _gradsync.GradSyncEngine, clip_grads: Callable, parameters: List[Any], defer: bool) -> _gradsync.ClipRequest:
+    """Run the user's clip function with torch's clip_grad_norm_ internals redirected to the kernels.
+
+    torch.nn.utils.clip_grad_norm_ computes `_get_total_norm(grads, ...)` then
+    `_clip_grads_with_norm_(parameters, max_norm, total_norm, ...)`, both looked up in its module at
+    call time -- so redirecting those two names catches every way a user may have imported
+    clip_grad_norm_.  Calls that are not "L2 norm over exactly this optimizer's gradients" fall
+    through to torch untouched.
+    """
+    from torch.nn.utils import clip_grad as tcg
+
+    req = _gradsync.ClipRequest()
+    ours = [v for fs in eng.sets for t, v in zip(fs.tensors, fs.grad_views) if t.param.grad is v]
+    aliased = len(ours) > 0
+    real_norm, real_clip = tcg._get_total_norm, tcg._clip_grads_with_norm_
+    issued: List[torch.Tensor] = []
+
+    def total_norm(tensors: Any, norm_type: float = 2.0, error_if_nonfinite: bool = False, foreach: Any = None) -> torch.Tensor:
+        ts = [tensors] if isinstance(tensors, torch.Tensor) else list(tensors)
+        if aliased and float(norm_type) == 2.0 and not error_if_nonfinite and len(ts) == len(ours) and all(a is b for a, b in zip(ts, ours)):
+            out = eng.total_norm().clone()  # the caller may keep it; the engine's scalar is reused every step
+            issued.append(out)
+            return out
+        return real_norm(ts, norm_type, error_if_nonfinite, foreach)
+
+    def clip_with_norm(params: Any, max_norm: float, total: torch.Tensor, foreach: Any = None) -> None:
+        if issued and total is issued[-1] and req.max_norm is None:
+            if defer:
+                req.max_norm = float(max_norm)  # fused into the optimizer kernel
+            else:
+                for fs in eng.sets:
+                    _lib.calls.dgs_clip_scale(
+                        _gradsync._ptr(fs.wire), _lib.dtype_code(fs.wire_dtype), fs.total, _gradsync._ptr(eng._norm),
+                        float(max_norm), _gradsync._stream(),
+                    )
+            return
+        real_clip(params, max_norm, total, foreach)
+
+    tcg._get_total_norm, tcg._clip_grads_with_norm_ = total_norm, clip_with_norm  # type: ignore
+    try:
+        clip_grads(parameters)
+    finally:
+        tcg._get_total_norm, tcg._clip_grads_with_norm_ = real_norm, real_clip
+    return req

