@@ -44,7 +44,16 @@ def _align(n: int) -> int:
     return (n + ALIGN_ELEMS - 1) // ALIGN_ELEMS * ALIGN_ELEMS
 
 
+try:
+    _raw_stream = torch._C._cuda_getCurrentRawStream  # ~0.2 us; torch.cuda.current_stream() costs ~5 us
+except AttributeError:  # pragma: no cover
+    _raw_stream = None
+
+
 def _stream() -> ctypes.c_void_p:
+    """cudaStream_t of torch's current stream on the current device."""
+    if _raw_stream is not None:
+        return ctypes.c_void_p(_raw_stream(torch.cuda.current_device()))
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
@@ -68,12 +77,10 @@ class _Tensor:
 
 
 class _Bucket:
-    __slots__ = ("begin", "end", "tensors", "arrived", "grads", "flushed", "reduced")
+    __slots__ = ("begin", "end", "tensors", "flushed", "reduced")
 
     def __init__(self, begin: int, end: int, tensors: List[int]) -> None:
         self.begin, self.end, self.tensors = begin, end, tensors
-        self.arrived = 0
-        self.grads: Dict[int, torch.Tensor] = {}
         self.flushed = False  # wire produced for this window
         self.reduced = False  # allreduce issued for this window
 
@@ -96,6 +103,10 @@ class _FlatSet:
         self.in_window: List[bool] = []  # tensor has contributed to the accumulator in this window
         self.in_wire: List[bool] = []  # tensor's wire slice is final for this window
         self.next_reduce = 0
+        self.dtype_code = self.wire_code = 0
+        self.group_runs: Optional[List[Tuple[int, int, int, List[_Tensor]]]] = None
+        self.steady = False  # last step covered every parameter and left every state tensor as our view
+        self.uniform_step: Optional[int] = None  # Adam: the common step count while all parameters move together
 
 
 class GradSyncEngine:
@@ -128,6 +139,9 @@ class GradSyncEngine:
         self.sets: List[_FlatSet] = []
         self._where: Dict[int, Tuple[int, int]] = {}  # id(param) -> (set index, tensor index)
         self._hooks: List[Any] = []
+        self._sentinels: Optional[Dict[int, Tuple[int, int]]] = None  # id(param) -> (set, bucket); None = not learnt
+        self._order: List[Tuple[int, int]] = []
+        self._learn_tries = 0
         self._final_pass = False
         self._in_pass = False
         self._norm = torch.zeros(1, dtype=torch.float32, device=device)
@@ -136,6 +150,7 @@ class GradSyncEngine:
         self._step_views: List[torch.Tensor] = []
         self._fused_kind = self._classify(optimizer)
         self.last_total_norm: Optional[torch.Tensor] = None
+        self._timing: Optional[List[Tuple[torch.cuda.Event, torch.cuda.Event]]] = None
         self._build()
 
     # ---- construction ---------------------------------------------------------------------------
@@ -192,8 +207,7 @@ class GradSyncEngine:
             fs.in_window = [False] * len(fs.tensors)
             fs.in_wire = [False] * len(fs.tensors)
             self._cut_buckets(fs)
-            for t in fs.tensors:
-                self._hooks.append(t.param.register_post_accumulate_grad_hook(self._on_grad))
+            fs.dtype_code, fs.wire_code = _lib.dtype_code(fs.dtype), _lib.dtype_code(fs.wire_dtype)
         n_partials = sum(_lib.calls.dgs_l2norm_grid(fs.total) for fs in self.sets)
         self._partials = torch.zeros(max(n_partials, 1), dtype=torch.float32, device=self.device)
         if self.comm is not None:
@@ -230,10 +244,15 @@ class GradSyncEngine:
         return [t.param for fs in self.sets for t in fs.tensors]
 
     # ---- backward ---------------------------------------------------------------------------------
+    # Gradients are left where autograd puts them (p.grad) and picked up per bucket:
+    #   * single GPU: after loss.backward() returns (end_pass) -- there is nothing to overlap with, and
+    #     no Python runs per parameter during backward;
+    #   * several GPUs: a hook on ONE parameter per bucket (the one whose gradient is produced last,
+    #     learnt from the first backward pass, as torch DDP rebuilds its buckets after the first
+    #     iteration) flushes the bucket and starts its allreduce while backward continues.
     def begin_pass(self, final: bool) -> None:
         """Called right before loss.backward().  `final`: this pass completes the window, so finished
-        buckets are scaled, cast and all-reduced straight from the hooks."""
-        self._in_pass, self._final_pass = True, final
+        buckets are scaled, cast and all-reduced as soon as they are complete."""
         for fs in self.sets:
             for b in fs.buckets:
                 if b.flushed:
@@ -242,67 +261,108 @@ class GradSyncEngine:
                         "already synchronized; pass the number of backward calls per batch as "
                         "backward_passes_per_step to wrap_optimizer()"
                     )
+        self._in_pass, self._final_pass = True, final
+        if self.comm is not None and self._sentinels is None and not self._hooks:
+            self._order = []
+            for fs in self.sets:
+                for t in fs.tensors:
+                    self._hooks.append(t.param.register_post_accumulate_grad_hook(self._learn_order))
 
     def end_pass(self) -> None:
-        """Called right after loss.backward(): flush buckets that only partly filled in this pass."""
+        """Called right after loss.backward(): flatten whatever the hooks have not taken yet."""
         for si, fs in enumerate(self.sets):
             for bi, b in enumerate(fs.buckets):
-                if b.grads:
-                    self._flush_bucket(si, bi, self._final_pass and b.arrived == len(b.tensors))
+                grads = self._collect(fs, b)
+                if grads:
+                    self._flush_bucket(si, bi, grads, self._final_pass and len(grads) == len(b.tensors))
+        if self._sentinels is None and self._hooks:
+            self._finish_learning()
         self._in_pass = self._final_pass = False
 
-    def _on_grad(self, p: torch.nn.Parameter) -> None:
-        g = p.grad
-        if g is None:
+    def _learn_order(self, p: torch.nn.Parameter) -> None:
+        self._order.append(self._where[id(p)])
+
+    def _finish_learning(self) -> None:
+        """After a backward pass in which every parameter produced exactly one gradient: keep a hook only
+        on the last-arriving parameter of each bucket."""
+        n = sum(len(fs.tensors) for fs in self.sets)
+        self._learn_tries += 1
+        complete = len(self._order) == n and len(set(self._order)) == n
+        if not complete and self._learn_tries < 3:
             return
-        p.grad = None  # the kernel consumes it; autograd must not keep accumulating into it
-        si, ti = self._where[id(p)]
+        for h in self._hooks:
+            h.remove()
+        self._hooks = []
+        self._sentinels = {}
+        if not complete:
+            return  # irregular graphs: no overlap, buckets are flushed at the end of backward
+        last: Dict[Tuple[int, int], int] = {}
+        for pos, (si, ti) in enumerate(self._order):
+            last[(si, self.sets[si].tensors[ti].bucket)] = pos
+        for (si, bi), pos in last.items():
+            _, ti = self._order[pos]
+            param = self.sets[si].tensors[ti].param
+            self._sentinels[id(param)] = (si, bi)
+            self._hooks.append(param.register_post_accumulate_grad_hook(self._on_sentinel))
+
+    def _on_sentinel(self, p: torch.nn.Parameter) -> None:
+        if not self._final_pass:
+            return  # nothing to communicate on this pass; end_pass() flattens everything at once
+        si, bi = self._sentinels[id(p)]  # type: ignore
         fs = self.sets[si]
-        b = fs.buckets[fs.tensors[ti].bucket]
-        if b.flushed:
+        b = fs.buckets[bi]
+        for ti in b.tensors:
+            if fs.tensors[ti].param.grad is None:
+                return  # arrival order changed: leave the bucket to end_pass()
+        self._flush_bucket(si, bi, self._collect(fs, b), True)
+
+    def _collect(self, fs: _FlatSet, b: _Bucket) -> Dict[int, torch.Tensor]:
+        """Take the gradients autograd has produced for this bucket (p.grad -> None)."""
+        out: Dict[int, torch.Tensor] = {}
+        tensors = fs.tensors
+        for ti in b.tensors:
+            p = tensors[ti].param
+            g = p.grad
+            if g is None:
+                continue
+            p.grad = None  # the kernel consumes it; autograd must not accumulate into it again
+            if g.is_sparse:
+                raise _lib.DgsError("sparse gradients are not supported by the grad-sync kernels")
+            if g.dtype != fs.dtype or not g.is_contiguous():
+                g = g.to(fs.dtype).contiguous()
+            out[ti] = g
+        if out and b.flushed:
             raise errors.InvalidExperimentException(
                 "a gradient arrived after this batch's gradients were already synchronized (more "
                 "backward passes than backward_passes_per_step declared)"
             )
-        if g.is_sparse:
-            raise _lib.DgsError("sparse gradients are not supported by the grad-sync kernels")
-        if g.dtype != fs.dtype or not g.is_contiguous():
-            g = g.to(fs.dtype).contiguous()
-        if ti in b.grads:  # second gradient for the same tensor within one pass: fold on arrival
-            b.grads[ti] = b.grads[ti] + g
-            return
-        b.grads[ti] = g
-        b.arrived += 1
-        if b.arrived == len(b.tensors):
-            self._flush_bucket(si, fs.tensors[ti].bucket, self._final_pass)
+        return out
 
-    def _flush_bucket(self, si: int, bi: int, to_wire: bool) -> None:
-        """Launch the flatten kernel over the gradients this bucket has collected in this pass."""
+    def _flush_bucket(self, si: int, bi: int, grads: Dict[int, torch.Tensor], to_wire: bool) -> None:
+        """Launch the flatten kernel over the gradients collected for this bucket in this pass."""
         fs = self.sets[si]
         b = fs.buckets[bi]
         if not to_wire and fs.acc is None:
             # more passes than configured: grow an accumulator on demand
             fs.acc = torch.zeros(fs.total, dtype=torch.float32, device=self.device)
+        stream = _stream()
         for read_acc in (False, True):
-            idxs = [ti for ti in b.grads if fs.in_window[ti] == read_acc]
+            idxs = [ti for ti in grads if fs.in_window[ti] == read_acc]
             if not idxs:
                 continue
             segs = (_lib.Seg * len(idxs))()
             for k, ti in enumerate(idxs):
                 t = fs.tensors[ti]
-                segs[k].src, segs[k].dst_off, segs[k].numel = b.grads[ti].data_ptr(), t.off, t.numel
+                seg = segs[k]
+                seg.src, seg.dst_off, seg.numel = grads[ti].data_ptr(), t.off, t.numel
             mode = (_lib.READ_ACC if read_acc else 0) | (_lib.WRITE_WIRE if to_wire else 0)
             _lib.calls.dgs_flatten_accumulate(
-                segs, len(idxs), _lib.dtype_code(fs.dtype), _ptr(fs.acc), _ptr(fs.wire),
-                _lib.dtype_code(fs.wire_dtype), mode, self.scale, _stream(),
+                segs, len(idxs), fs.dtype_code, _ptr(fs.acc), _ptr(fs.wire), fs.wire_code, mode, self.scale, stream,
             )
-        for ti in b.grads:
-            if to_wire:
-                fs.in_wire[ti] = True
-            else:
-                fs.in_window[ti] = True
-        b.grads = {}  # stream-ordered allocator: safe to release after the launch
-        b.arrived = 0
+        flags = fs.in_wire if to_wire else fs.in_window
+        for ti in grads:
+            flags[ti] = True
+        # the gradient tensors can be released now: the allocator is stream-ordered
         if to_wire:
             b.flushed = True
             self._reduce_ready(fs)
@@ -325,8 +385,9 @@ class GradSyncEngine:
         present: List[List[bool]] = []
         for si, fs in enumerate(self.sets):
             for bi, b in enumerate(fs.buckets):
-                if b.grads:  # gradients produced outside context.backward()
-                    self._flush_bucket(si, bi, False)
+                grads = self._collect(fs, b)  # gradients produced outside context.backward()
+                if grads:
+                    self._flush_bucket(si, bi, grads, False)
             have = [fs.in_wire[i] or fs.in_window[i] for i in range(len(fs.tensors))]
             for bi, b in enumerate(fs.buckets):
                 if b.flushed:
@@ -398,8 +459,6 @@ class GradSyncEngine:
                 fs.in_window[i] = fs.in_wire[i] = False
             for b in fs.buckets:
                 b.flushed = b.reduced = False
-                b.arrived = 0
-                b.grads = {}
 
     # -- fused step -----------------------------------------------------------------------------------
     def can_fuse(self) -> bool:
@@ -411,10 +470,11 @@ class GradSyncEngine:
             buf = fs.state[key] = torch.zeros(fs.total, dtype=fs.dtype, device=self.device)
         return buf
 
-    def _adopt_state(self, fs: _FlatSet, key: str) -> torch.Tensor:
+    def _adopt_state(self, fs: _FlatSet, key: str) -> Tuple[torch.Tensor, bool]:
         """Flat buffer for optimizer.state[p][key].  State tensors that are not (any more) views of it --
         the user called optimizer.load_state_dict() -- are copied in and replaced by views.  The check
-        is by identity on the first and last tensor, so the steady state costs two dict lookups."""
+        is by identity on the first and last tensor, so the steady state costs two dict lookups; the
+        second result says whether that check passed (every state tensor already was our view)."""
         buf = self._state_buffer(fs, key)
         views = fs.state_views.get(key)
         if views is None:
@@ -422,7 +482,7 @@ class GradSyncEngine:
         state = self.optimizer.state
         probes = (fs.tensors[0], fs.tensors[-1])
         if all(state.get(t.param, {}).get(key) is views[t.index] for t in probes):
-            return buf
+            return buf, True
         for t in fs.tensors:
             st = state.get(t.param)
             if st is None or st.get(key) is None:
@@ -430,7 +490,7 @@ class GradSyncEngine:
             if st[key] is not views[t.index]:
                 views[t.index].copy_(st[key])
                 st[key] = views[t.index]
-        return buf
+        return buf, False
 
     def _ranges(self, fs: _FlatSet, have: Sequence[bool], key_fn: Callable[[_Tensor], Any]) -> List[Tuple[int, int, Any, List[_Tensor]]]:
         """Maximal runs of present tensors with equal key -> (begin, end, key, tensors)."""
@@ -447,9 +507,36 @@ class GradSyncEngine:
                 runs.append((t.off, end, k, [t]))
         return runs
 
+    # -- measurement: CUDA events around the optimizer kernel, on the stream it is launched on ----------
+    def enable_step_timing(self, on: bool = True) -> None:
+        self._timing = [] if on else None
+
+    def step_timings_ms(self) -> List[float]:
+        """Durations of the fused step launches since enable_step_timing(); synchronizes."""
+        if not self._timing:
+            return []
+        self._timing[-1][1].synchronize()
+        return [a.elapsed_time(b) for a, b in self._timing]
+
     def fused_step(self, present: List[List[bool]], clip: Optional[ClipRequest]) -> None:
         """clip + optimizer.step() in one kernel per flat set (several if there are > 24 ranges)."""
         assert self._fused_kind is not None
+        self._fused_step(present, clip)
+
+    def _launch_step(self, fn: Any, *args: Any) -> None:
+        """Launch one optimizer kernel; with timing on, CUDA events are recorded immediately around the
+        launch call on the launching stream."""
+        if self._timing is None:
+            fn(*args)
+            return
+        st = torch.cuda.current_stream()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(st)
+        fn(*args)
+        b.record(st)
+        self._timing.append((a, b))
+
+    def _fused_step(self, present: List[List[bool]], clip: Optional[ClipRequest]) -> None:
         norm_ptr, max_norm = None, 0.0
         if clip is not None and clip.max_norm is not None:
             if self.last_total_norm is None:
@@ -461,43 +548,58 @@ class GradSyncEngine:
         else:
             self._fused_adam(present, groups, norm_ptr, max_norm)
         self.last_total_norm = None
+        self.optimizer._opt_called = True  # type: ignore  # what torch LR schedulers look at before warning
+
+    def _group_runs(self, fs: _FlatSet) -> List[Tuple[int, int, int, List[_Tensor]]]:
+        """One (begin, end, group, tensors) per run of adjacent tensors of one param group: the range table
+        of a step in which every parameter has a gradient."""
+        if fs.group_runs is None:
+            fs.group_runs = [(b, e, k, ts) for b, e, k, ts in self._ranges(fs, [True] * len(fs.tensors), lambda t: t.group)]
+        return fs.group_runs
 
     def _fused_sgd(self, present: List[List[bool]], groups: List[Dict[str, Any]], norm_ptr: Any, max_norm: float) -> None:
+        stream = _stream()
         for fs, have in zip(self.sets, present):
             any_momentum = any(g["momentum"] != 0 for g in groups)
-            buf = self._adopt_state(fs, "momentum_buffer") if any_momentum else None
+            buf, intact = self._adopt_state(fs, "momentum_buffer") if any_momentum else (None, True)
+            everyone = all(have)
+            if everyone and intact and (fs.steady or not any_momentum):
+                # steady state: every parameter has a gradient and a momentum buffer that is our view
+                runs = [(b, e, (gi, False), ts) for b, e, gi, ts in self._group_runs(fs)]
+            else:
+                state = self.optimizer.state
 
-            def key(t: _Tensor) -> Any:
-                st = self.optimizer.state.get(t.param)
-                first = st is None or st.get("momentum_buffer") is None
-                return (t.group, first)
+                def key(t: _Tensor) -> Any:
+                    st = state.get(t.param)
+                    return (t.group, st is None or st.get("momentum_buffer") is None)
 
-            runs = self._ranges(fs, have, key)
+                runs = self._ranges(fs, have, key)
             for with_momentum in (True, False):
                 sel = [r for r in runs if (groups[r[2][0]]["momentum"] != 0) == with_momentum]
                 for i in range(0, len(sel), _lib.MAX_RANGES):
                     chunk = sel[i:i + _lib.MAX_RANGES]
                     arr = (_lib.SgdRange * len(chunk))()
                     for k, (b, e, (gi, first), _) in enumerate(chunk):
-                        g = groups[gi]
-                        arr[k].begin, arr[k].end = b, e
-                        arr[k].lr, arr[k].momentum = float(g["lr"]), float(g["momentum"])
-                        arr[k].dampening, arr[k].weight_decay = float(g["dampening"]), float(g["weight_decay"])
-                        arr[k].flags = (
+                        g, r = groups[gi], arr[k]
+                        r.begin, r.end = b, e
+                        r.lr, r.momentum = float(g["lr"]), float(g["momentum"])
+                        r.dampening, r.weight_decay = float(g["dampening"]), float(g["weight_decay"])
+                        r.flags = (
                             (_lib.SGD_NESTEROV if g["nesterov"] else 0)
                             | (_lib.SGD_FIRST_STEP if first else 0)
                             | (_lib.OPT_MAXIMIZE if g.get("maximize") else 0)
                         )
-                    _lib.calls.dgs_step_sgd(
-                        _ptr(fs.param), _ptr(buf) if with_momentum else None, _lib.dtype_code(fs.dtype), _ptr(fs.wire),
-                        _lib.dtype_code(fs.wire_dtype), fs.total, arr, len(chunk), norm_ptr, max_norm, _stream(),
+                    self._launch_step(
+                        _lib.calls.dgs_step_sgd, _ptr(fs.param), _ptr(buf) if with_momentum else None, fs.dtype_code, _ptr(fs.wire),
+                        fs.wire_code, fs.total, arr, len(chunk), norm_ptr, max_norm, stream,
                     )
             if buf is not None:
+                views = fs.state_views["momentum_buffer"]
                 for b, e, (gi, first), ts in runs:
                     if first and groups[gi]["momentum"] != 0:
-                        views = fs.state_views["momentum_buffer"]
                         for t in ts:
                             self.optimizer.state[t.param]["momentum_buffer"] = views[t.index]
+                fs.steady = everyone
 
     def _ensure_steps(self) -> torch.Tensor:
         n = sum(len(fs.tensors) for fs in self.sets)
@@ -508,49 +610,56 @@ class GradSyncEngine:
 
     def _fused_adam(self, present: List[List[bool]], groups: List[Dict[str, Any]], norm_ptr: Any, max_norm: float) -> None:
         steps = self._ensure_steps()
+        stream = _stream()
         base = 0
         decoupled = self._fused_kind == "adamw"
         for fs, have in zip(self.sets, present):
-            m = self._adopt_state(fs, "exp_avg")
-            v = self._adopt_state(fs, "exp_avg_sq")
-            # per-parameter step counters live in one host tensor; optimizer.state[p]["step"] are views
-            for t, ok in zip(fs.tensors, have):
-                st = self.optimizer.state[t.param]
-                cur = st.get("step")
-                mine = self._step_views[base + t.index]
-                if cur is not mine:
-                    if cur is not None:
-                        mine.fill_(float(cur))
-                    st["step"] = mine
+            m, intact_m = self._adopt_state(fs, "exp_avg")
+            v, intact_v = self._adopt_state(fs, "exp_avg_sq")
+            n_t = len(fs.tensors)
+            everyone = all(have)
+            if everyone and intact_m and intact_v and fs.steady and fs.uniform_step is not None:
+                # steady state: all parameters in lock-step; one host add advances every `step` view
+                steps[base:base + n_t] += 1.0
+                fs.uniform_step += 1
+                runs = [(b, e, (gi, fs.uniform_step), ts) for b, e, gi, ts in self._group_runs(fs)]
+            else:
+                # per-parameter step counters live in one host tensor; optimizer.state[p]["step"] are views
+                state = self.optimizer.state
+                for t in fs.tensors:
+                    st = state[t.param]
+                    cur = st.get("step")
+                    mine = self._step_views[base + t.index]
+                    if cur is not mine:
+                        if cur is not None:
+                            mine.fill_(float(cur))
+                        st["step"] = mine
                     if "exp_avg" not in st:
                         st["exp_avg"] = fs.state_views["exp_avg"][t.index]
                         st["exp_avg_sq"] = fs.state_views["exp_avg_sq"][t.index]
-            mask = torch.tensor(have, dtype=torch.float32)
-            steps[base:base + len(fs.tensors)] += mask
-            counts = steps[base:base + len(fs.tensors)].tolist()
-
-            def key(t: _Tensor) -> Any:
-                return (t.group, int(counts[t.index]))
-
-            runs = self._ranges(fs, have, key)
+                steps[base:base + n_t] += torch.tensor(have, dtype=torch.float32)
+                counts = [int(c) for c in steps[base:base + n_t].tolist()]
+                runs = self._ranges(fs, have, lambda t: (t.group, counts[t.index]))
+                fs.steady = everyone
+                fs.uniform_step = counts[0] if everyone and len(set(counts)) == 1 else None
             for i in range(0, len(runs), _lib.MAX_RANGES):
                 chunk = runs[i:i + _lib.MAX_RANGES]
                 arr = (_lib.AdamRange * len(chunk))()
                 for k, (b, e, (gi, step), _) in enumerate(chunk):
-                    g = groups[gi]
+                    g, r = groups[gi], arr[k]
                     b1, b2 = (float(x) for x in g["betas"])
                     lr = float(g["lr"])
-                    arr[k].begin, arr[k].end = b, e
-                    arr[k].lr, arr[k].beta1, arr[k].beta2 = lr, b1, b2
-                    arr[k].eps, arr[k].weight_decay = float(g["eps"]), float(g["weight_decay"])
-                    arr[k].step_size = lr / (1 - b1 ** step)
-                    arr[k].bias_correction2_sqrt = (1 - b2 ** step) ** 0.5
+                    r.begin, r.end = b, e
+                    r.lr, r.beta1, r.beta2 = lr, b1, b2
+                    r.eps, r.weight_decay = float(g["eps"]), float(g["weight_decay"])
+                    r.step_size = lr / (1 - b1 ** step)
+                    r.bias_correction2_sqrt = (1 - b2 ** step) ** 0.5
                     use_decoupled = decoupled or bool(g.get("decoupled_weight_decay"))
-                    arr[k].flags = (_lib.ADAM_DECOUPLED_WD if use_decoupled else 0) | (_lib.OPT_MAXIMIZE if g.get("maximize") else 0)
+                    r.flags = (_lib.ADAM_DECOUPLED_WD if use_decoupled else 0) | (_lib.OPT_MAXIMIZE if g.get("maximize") else 0)
                     if g["weight_decay"] == 0:
-                        arr[k].flags |= _lib.ADAM_DECOUPLED_WD  # p *= 1 exactly; skips the L2 add
-                _lib.calls.dgs_step_adam(
-                    _ptr(fs.param), _ptr(m), _ptr(v), _lib.dtype_code(fs.dtype), _ptr(fs.wire), _lib.dtype_code(fs.wire_dtype),
-                    fs.total, arr, len(chunk), norm_ptr, max_norm, _stream(),
+                        r.flags |= _lib.ADAM_DECOUPLED_WD  # p *= 1 exactly; skips the L2 add
+                self._launch_step(
+                    _lib.calls.dgs_step_adam, _ptr(fs.param), _ptr(m), _ptr(v), fs.dtype_code, _ptr(fs.wire), fs.wire_code,
+                    fs.total, arr, len(chunk), norm_ptr, max_norm, stream,
                 )
-            base += len(fs.tensors)
+            base += n_t

@@ -236,17 +236,19 @@ class DeviceMetricBuffer:
             comm.wait()
         else:
             all_ring, all_valid, all_nb = ring, valid, nb
-        # [per_batch (b*m) | avg (m)] doubles, then counts / validity, in one host-visible block
-        out = torch.empty(b * m + m, dtype=torch.float64, device=self.device)
-        out_valid = torch.empty(b * m, dtype=torch.uint8, device=self.device)
-        count = torch.empty(m, dtype=torch.int64, device=self.device)
+        # one result block -> one device->host copy: [per_batch b*m f64 | avg m f64 | count m i64 | valid b*m u8]
+        n_f64 = b * m + m
+        block = torch.empty(8 * n_f64 + 8 * m + b * m, dtype=torch.uint8, device=self.device)
+        base = block.data_ptr()
         _lib.calls.dgs_metric_average(
-            _p(all_ring), _p(all_valid), _p(all_nb), n, b, m, _p(out), _p(out_valid),
-            ctypes.c_void_p(out.data_ptr() + 8 * b * m), _p(count), _stream(),
+            _p(all_ring), _p(all_valid), _p(all_nb), n, b, m,
+            ctypes.c_void_p(base), ctypes.c_void_p(base + 8 * n_f64 + 8 * m),
+            ctypes.c_void_p(base + 8 * b * m), ctypes.c_void_p(base + 8 * n_f64), _stream(),
         )
-        host = out.cpu().numpy()
-        host_valid = out_valid.cpu().numpy().reshape(b, m).astype(bool)
-        counts = count.cpu().numpy().tolist()
+        raw = block.cpu().numpy()
+        host = raw[: 8 * n_f64].view(np.float64)
+        counts = raw[8 * n_f64: 8 * n_f64 + 8 * m].view(np.int64).tolist()
+        host_valid = raw[8 * n_f64 + 8 * m:].reshape(b, m).astype(bool)
         per_batch_vals = host[: b * m].reshape(b, m)
         per_batch: List[Dict[str, Any]] = []
         for i in range(b):
