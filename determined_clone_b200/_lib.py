@@ -18,6 +18,8 @@ MAX_RANGES = 24
 MAX_METRICS = 64
 ALIGN_BYTES = 128
 NORM_MAX_PARTIALS = 9472
+NOALLOC_MAX_PARTIALS = 4096
+NOALLOC_MAX_ELEMS = 4096 * 16384
 
 
 class Seg(ctypes.Structure):
@@ -70,6 +72,7 @@ SIGNATURES = {
     "dgs_l2norm_partial": [_vp, _i, _i64, _vp, _vp],
     "dgs_l2norm_final": [_vp, _i, _vp, _vp],
     "dgs_l2norm": [_vp, _i, _i64, _vp, _vp, _vp],
+    "dgs_l2norm_noalloc": [_vp, _i, _i64, _vp, _vp],
     "dgs_clip_scale": [_vp, _i, _i64, _vp, _f, _vp],
     "dgs_step_adam": [_vp, _vp, _vp, _i, _vp, _i, _i64, ctypes.POINTER(AdamRange), _i, _vp, _f, _vp],
     "dgs_step_sgd": [_vp, _vp, _i, _vp, _i, _i64, ctypes.POINTER(SgdRange), _i, _vp, _f, _vp],

@@ -109,6 +109,20 @@ int dgs_l2norm_final(const float* partials, int n_partials, float* out_norm, dgs
 int dgs_l2norm(const void* x, int dtype, int64_t n, float* partials, float* out_norm,
                dgs_stream_t stream);
 
+/* The same two-pass norm for callers that cannot allocate device memory at all (a cgo / JNI / ctypes
+ * plugin host that owns no device allocator; a trainer whose caching allocator has reserved all of HBM so
+ * that a raw cudaMalloc for scratch would fail; step loops under a no-allocation rule): the partials go to
+ * a __device__ array built into the library (DGS_NOALLOC_MAX_PARTIALS floats = 16 KiB, resident on every
+ * GPU that loads the library until exit) instead of caller scratch.  Accepts n <= DGS_NOALLOC_MAX_ELEMS
+ * and refuses larger inputs with DGS_EINVAL.  Calls no cudaMalloc/cudaFree or other allocating routine.
+ * The first call on a device resolves the array's device address (do it during set-up, before any stream
+ * capture on that device).  One array per device is shared by all calls: calls whose kernels overlap on
+ * the GPU race; it keeps the previous call's contents and needs no clearing (pass 1 overwrites every slot
+ * pass 2 reads).  This entry point has no counterpart in the reference. */
+#define DGS_NOALLOC_MAX_PARTIALS 4096
+#define DGS_NOALLOC_MAX_ELEMS (4096LL * 16384LL) /* 2^26 elements */
+int dgs_l2norm_noalloc(const void* x, int dtype, int64_t n, float* out_norm, dgs_stream_t stream);
+
 /* g[i] *= min(max_norm / (total_norm[0] + 1e-6), 1) -- the unfused tail of clip_grad_norm_, used
  * only when the optimizer step itself stays in torch (optimizers other than SGD/Adam/AdamW). */
 int dgs_clip_scale(void* g, int dtype, int64_t n, const float* total_norm, float max_norm,
