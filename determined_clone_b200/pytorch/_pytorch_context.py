@@ -257,7 +257,9 @@ class PyTorchTrialContext(_PyTorchReducerContext):
         if average_aggregated_gradients is None:
             average_aggregated_gradients = self._average_aggregated_gradients_default
         self._optimizer_configs[optimizer] = {"average_aggregated_gradients": average_aggregated_gradients}
-        if self._managed_training:
+        if optimizer in self._engines:
+            raise errors.InvalidExperimentException("wrap_optimizer() was called twice on the same optimizer")
+        if True:  # managed or not (Trainer / Core API use): the same engine carries the step
             self._engines[optimizer] = _gradsync.GradSyncEngine(
                 optimizer,
                 device=self.device,
