@@ -52,6 +52,8 @@ def parse() -> argparse.Namespace:
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-microbench", action="store_true")
     ap.add_argument("--micro-mb", type=int, default=256)
+    ap.add_argument("--workload", default="cifar_resnet18", choices=["cifar_resnet18", "resnet50", "gpt2_medium"],
+                    help="cifar_resnet18 = BASELINE.json configs[1] (the default the driver runs); the others are configs[2]/[3]")
     return ap.parse_args()
 
 
@@ -122,17 +124,20 @@ class ClockSampler:
 
 
 # ---- reference arm / cpu baseline -----------------------------------------------------------------
-def run_cpu_port(steps: int, warmup: int, budget_s: float) -> Dict[str, Any]:
+def run_cpu_port(steps: int, warmup: int, budget_s: float, workload: str = "cifar_resnet18") -> Dict[str, Any]:
     """The reference's per-batch path as it runs on CPU (oracle/torch_port.py), all host threads."""
     import torch
 
     from oracle import torch_port
-    from workloads.trials import CifarResNetTrial
+    from workloads.trials import WORKLOADS
+
+    CifarResNetTrial = WORKLOADS[workload]
+    PER_SLOT_BATCH = CifarResNetTrial.PER_SLOT_BATCH
 
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     torch.set_num_threads(cores)
     torch.manual_seed(17)
-    ctx = torch_port.RefContext(aggregation_frequency=1, device="cpu")
+    ctx = torch_port.RefContext(aggregation_frequency=CifarResNetTrial.AGG, device="cpu")
     trial = CifarResNetTrial(ctx)
     gen = torch.Generator().manual_seed(1234)
     batches = [CifarResNetTrial.synthetic_batch(PER_SLOT_BATCH, gen) for _ in range(4)]
@@ -157,13 +162,17 @@ def run_cpu_port(steps: int, warmup: int, budget_s: float) -> Dict[str, Any]:
 def run_reference(args: argparse.Namespace) -> None:
     if int(os.environ.get("RANK", "0")) != 0:
         return  # the CPU path is timed once, on rank 0
-    r = run_cpu_port(args.steps, args.warmup, budget_s=150.0)
+    from workloads.trials import WORKLOADS
+
+    W = WORKLOADS[args.workload]
+    PER_SLOT_BATCH = W.PER_SLOT_BATCH
+    r = run_cpu_port(args.steps, args.warmup, budget_s=150.0, workload=args.workload)
     line = {
         "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": r["steps"],
         "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "cifar10_resnet18_pytorchtrial", "per_slot_batch": PER_SLOT_BATCH, "global_batch": PER_SLOT_BATCH,
-                   "optimizer": "sgd_momentum", "aggregation_frequency": 1, "parallelism": "cpu, 1 process"},
+        "dtype": W.DTYPE, "data": "synthetic",
+        "config": {"workload": W.NAME, "per_slot_batch": PER_SLOT_BATCH, "global_batch": PER_SLOT_BATCH,
+                   "optimizer": W.OPTIMIZER, "aggregation_frequency": W.AGG, "parallelism": "cpu, 1 process"},
         "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
         "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -184,19 +193,22 @@ def gradsync_microbench(ctx: Any, mb: int, steps: int, peak_gbs: float) -> Dict[
 
     from determined_clone_b200 import pytorch
 
-    n = mb * (1 << 20) // 4
+    pieces = 64  # the flat bucket is made of 64 equal tensors, as a model's would be of many
+    n_piece = mb * (1 << 20) // 4 // pieces
+    n = n_piece * pieces
     world = ctx.distributed.size
-    p = torch.nn.Parameter((torch.randn(n, device=ctx.device) * 0.02))
-    opt = torch.optim.AdamW([p], lr=3e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
+    params = [torch.nn.Parameter(torch.randn(n_piece, device=ctx.device) * 0.02) for _ in range(pieces)]
+    opt = torch.optim.AdamW(params, lr=3e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
     eng = pytorch.GradSyncEngine(opt, ctx.device, ctx._get_comm(), aggregation_frequency=1, average_aggregated_gradients=True)
-    grads = [torch.randn(n, device=ctx.device) * 1e-2 for _ in range(2)]
+    grads = [[torch.randn(n_piece, device=ctx.device) * 1e-2 for _ in range(pieces)] for _ in range(2)]
     clip = pytorch._gradsync.ClipRequest()
     clip.max_norm = 1.0
     st = torch.cuda.current_stream()
 
     def step(i: int) -> None:
         eng.begin_pass(final=True)
-        p.grad = grads[i % 2]  # what autograd leaves behind when backward produces this gradient
+        for p, g in zip(params, grads[i % 2]):
+            p.grad = g  # what autograd leaves behind when backward produces this gradient
         eng.end_pass()
         present = eng.finish_window()
         eng.total_norm()
@@ -232,8 +244,11 @@ def run_ours(args: argparse.Namespace) -> None:
     import torch
 
     from determined_clone_b200 import _build, _lib, core, pytorch
-    from workloads.trials import CifarResNetTrial
+    from workloads.trials import WORKLOADS
 
+    CifarResNetTrial = WORKLOADS[args.workload]  # the trial class of the selected workload
+    PER_SLOT_BATCH = CifarResNetTrial.PER_SLOT_BATCH
+    AGG = CifarResNetTrial.AGG
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -263,7 +278,7 @@ def run_ours(args: argparse.Namespace) -> None:
 
     pytorch._PyTorchTrialController.pre_execute_hook(17)
     ctx = pytorch.PyTorchTrialContext(distributed=dctx, hparams={"global_batch_size": PER_SLOT_BATCH * world}, slots_per_trial=world,
-                                      aggregation_frequency=1, trial_seed=17, device=device)
+                                      aggregation_frequency=AGG, trial_seed=17, device=device)
 
     class BenchTrial(CifarResNetTrial):
         loader: Any = None
@@ -325,6 +340,8 @@ def run_ours(args: argparse.Namespace) -> None:
         orig = ctx.step_optimizer
 
         def timed_step_optimizer(*a: Any, **k: Any) -> None:
+            if not ctx._should_communicate_and_update():
+                return orig(*a, **k)  # not an optimizer step: nothing to time
             a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a0.record(stream)
             orig(*a, **k)
@@ -332,7 +349,7 @@ def run_ours(args: argparse.Namespace) -> None:
             ev.append((a0, a1))
 
         ctx.step_optimizer = timed_step_optimizer  # type: ignore
-        for i in range(10):
+        for i in range(2 * AGG + 8 - (8 % AGG if AGG > 1 else 0)):
             one_step(args.warmup + args.steps + i)
         torch.cuda.synchronize()
         ctx.step_optimizer = orig  # type: ignore
@@ -353,10 +370,10 @@ def run_ours(args: argparse.Namespace) -> None:
 
     trial.loader = HostLoader()
     reports: List[Any] = []
-    base = args.warmup + args.steps + 10
-    warm = pytorch._PyTorchTrialController(trial, ctx, max_length=base + 3, reporting_period=1, steps_completed=base)
+    base = (args.warmup + args.steps + 4 * AGG + 16) // AGG * AGG  # resume on an aggregation boundary
+    warm = pytorch._PyTorchTrialController(trial, ctx, max_length=base + AGG, reporting_period=1, steps_completed=base)
     warm.run()
-    ctl = pytorch._PyTorchTrialController(trial, ctx, max_length=base + 3 + e2e_steps, reporting_period=1, steps_completed=base + 3,
+    ctl = pytorch._PyTorchTrialController(trial, ctx, max_length=base + AGG + e2e_steps, reporting_period=1, steps_completed=base + AGG,
                                           on_report=lambda n, r: reports.append(r))
     barrier()
     t0 = time.perf_counter()
@@ -375,14 +392,15 @@ def run_ours(args: argparse.Namespace) -> None:
     # ---- roofline of the dominant kernel of the path (fused SGD step) --------------------------------
     peak, peak_src = measured_peaks()
     k_ms = sorted(step_kernel_ms)[len(step_kernel_ms) // 2] if step_kernel_ms else None
-    bytes_per_elem = 20  # read g,p,buf + write p,buf, fp32 (kernel table)
+    bytes_per_elem = CifarResNetTrial.STEP_BYTES_PER_ELEM  # DESIGN.md, kernel table
     roofline = None
     if k_ms:
         achieved = bytes_per_elem * p_total / (k_ms * 1e-3) / 1e9
-        roofline = {"bound": "hbm", "kernel": "dgs::sgd_kernel<float,float,true>", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                    "frac": achieved / peak, "traffic": NCU_TRAFFIC_BYTES, "peak_source": peak_src, "elements": p_total,
+        roofline = {"bound": "hbm", "kernel": CifarResNetTrial.STEP_KERNEL, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                    "frac": achieved / peak, "traffic": NCU_TRAFFIC_BYTES if args.workload == "cifar_resnet18" else None, "peak_source": peak_src, "elements": p_total,
                     "algorithmic_bytes_per_element": bytes_per_elem, "us_per_launch": k_ms * 1e3,
-                    "note": "44.7 MB fp32 model: the wire bucket was just written by the flatten kernels and partly sits in L2"}
+                    "note": "events recorded immediately around the launch; for models smaller than L2 the wire bucket just written by "
+                            "the flatten kernels is partly still cached"}
 
     micro = None
     if not args.no_microbench:
@@ -390,16 +408,17 @@ def run_ours(args: argparse.Namespace) -> None:
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
-        r = run_cpu_port(steps=20, warmup=1, budget_s=20.0)
+        r = run_cpu_port(steps=20, warmup=1, budget_s=20.0, workload=args.workload)
         cpu = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
 
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": CifarResNetTrial.DTYPE,
             "data": "synthetic",
             "config": {"workload": CifarResNetTrial.NAME, "per_slot_batch": PER_SLOT_BATCH, "global_batch": PER_SLOT_BATCH * world,
-                       "optimizer": "sgd_momentum lr 0.1 m 0.9 wd 5e-4", "aggregation_frequency": 1, "parallelism": f"dp{world}",
+                       "optimizer": CifarResNetTrial.OPTIMIZER, "aggregation_frequency": AGG, "parallelism": f"dp{world}",
                        "l2": "8 distinct input batches cycled; forward/backward activations between optimizer steps exceed L2",
                        "param_elements": p_total},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks.summary(),
@@ -419,8 +438,10 @@ def run_torch_gpu(args: argparse.Namespace) -> None:
     import torch
 
     from oracle import torch_port
-    from workloads.trials import CifarResNetTrial
+    from workloads.trials import WORKLOADS
 
+    CifarResNetTrial = WORKLOADS[args.workload]
+    PER_SLOT_BATCH = CifarResNetTrial.PER_SLOT_BATCH
     rank, world, local_rank = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
     torch.cuda.set_device(local_rank)
     device = torch.device("cuda", local_rank)
@@ -439,7 +460,7 @@ def run_torch_gpu(args: argparse.Namespace) -> None:
             self.models.append(model)
             return model
 
-    ctx = Ctx(aggregation_frequency=1, device=str(device))
+    ctx = Ctx(aggregation_frequency=CifarResNetTrial.AGG, device=str(device))
     trial = CifarResNetTrial(ctx)
     gen = torch.Generator().manual_seed(1234 + rank)
     batches = [tuple(t.to(device) for t in CifarResNetTrial.synthetic_batch(PER_SLOT_BATCH, gen)) for _ in range(8)]

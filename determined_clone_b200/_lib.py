@@ -86,6 +86,7 @@ SIGNATURES = {
     "dgs_comm_allreduce_async": [_vp, _vp, _i64, _i, _vp],
     "dgs_comm_broadcast_async": [_vp, _vp, _i64, _i, _vp],
     "dgs_comm_allgather_async": [_vp, _vp, _vp, _i64, _vp],
+    "dgs_comm_l2norm_partial_async": [_vp, _vp, _i, _i64, _vp],
     "dgs_comm_wait": [_vp, _vp],
     "dgs_nccl_version": [ctypes.POINTER(_i)],
 }

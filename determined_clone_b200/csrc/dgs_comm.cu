@@ -20,10 +20,14 @@
 struct dgs_comm {
   ncclComm_t comm = nullptr;
   int rank = 0, nranks = 1, device = 0;
-  cudaStream_t side = nullptr;
+  cudaStream_t side = nullptr;       // collectives
+  cudaStream_t aux = nullptr;        // kernels that consume a collective's result (norm pass 1), so that they
+                                     // do not delay the next collective on `side`
   cudaEvent_t ev_compute = nullptr;  // "everything enqueued so far on the compute stream"
   cudaEvent_t ev_side = nullptr;     // "everything issued so far on the side stream"
+  cudaEvent_t ev_aux = nullptr;      // "everything issued so far on the aux stream"
   bool pending = false;
+  bool aux_pending = false;
 };
 
 namespace dgs {
@@ -149,8 +153,10 @@ extern "C" int dgs_comm_init(const void* id128, int rank, int nranks, int device
   int lo = 0, hi = 0;
   DGS_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));  // hi = numerically lowest = highest priority
   DGS_CUDA(cudaStreamCreateWithPriority(&c->side, cudaStreamNonBlocking, hi));
+  DGS_CUDA(cudaStreamCreateWithPriority(&c->aux, cudaStreamNonBlocking, hi));
   DGS_CUDA(cudaEventCreateWithFlags(&c->ev_compute, cudaEventDisableTiming));
   DGS_CUDA(cudaEventCreateWithFlags(&c->ev_side, cudaEventDisableTiming));
+  DGS_CUDA(cudaEventCreateWithFlags(&c->ev_aux, cudaEventDisableTiming));
   ncclUniqueId id;
   memcpy(&id, id128, sizeof(id));
   DGS_NCCL(api, nullptr, api->CommInitRank(&c->comm, nranks, id, rank));
@@ -163,10 +169,13 @@ extern "C" int dgs_comm_destroy(dgs_comm* c) {
   if (!c) return DGS_OK;
   NcclApi* api = nccl();
   if (c->side) (void)cudaStreamSynchronize(c->side);
+  if (c->aux) (void)cudaStreamSynchronize(c->aux);
   if (api && c->comm) (void)api->CommDestroy(c->comm);
   if (c->ev_compute) (void)cudaEventDestroy(c->ev_compute);
   if (c->ev_side) (void)cudaEventDestroy(c->ev_side);
+  if (c->ev_aux) (void)cudaEventDestroy(c->ev_aux);
   if (c->side) (void)cudaStreamDestroy(c->side);
+  if (c->aux) (void)cudaStreamDestroy(c->aux);
   delete c;
   return DGS_OK;
 }
@@ -218,11 +227,27 @@ extern "C" int dgs_comm_allgather_async(dgs_comm* c, const void* send, void* rec
   return mark_out(c);
 }
 
+extern "C" int dgs_comm_l2norm_partial_async(dgs_comm* c, const void* x, int dtype, int64_t n, float* partials) {
+  using namespace dgs;
+  DGS_CHECK_ARG(c != nullptr, "dgs_comm_l2norm_partial_async: NULL communicator");
+  // aux waits for the collectives issued so far (ev_side was recorded behind the last one), then reads
+  DGS_CUDA(cudaStreamWaitEvent(c->aux, c->ev_side, 0));  // no-op if nothing was ever issued
+  if (int rc = dgs_l2norm_partial(x, dtype, n, partials, c->aux)) return rc;
+  DGS_CUDA(cudaEventRecord(c->ev_aux, c->aux));
+  c->aux_pending = true;
+  return DGS_OK;
+}
+
 extern "C" int dgs_comm_wait(dgs_comm* c, dgs_stream_t compute) {
   using namespace dgs;
   DGS_CHECK_ARG(c != nullptr, "dgs_comm_wait: NULL communicator");
-  if (!c->pending) return DGS_OK;
-  DGS_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(compute), c->ev_side, 0));
-  c->pending = false;
+  if (c->pending) {
+    DGS_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(compute), c->ev_side, 0));
+    c->pending = false;
+  }
+  if (c->aux_pending) {
+    DGS_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(compute), c->ev_aux, 0));
+    c->aux_pending = false;
+  }
   return DGS_OK;
 }

@@ -4,15 +4,16 @@
 // harness/determined/pytorch/_pytorch_context.py:802-812), DDP's grad/N copy into its buckets
 // (:813-816) and the per-parameter div_(A) of _average_gradients (:818-825).
 //
-// HBM-bound, no reuse: one pass, every warp-level access a contiguous 512 B (fp32) run, 4 independent
+// HBM-bound, no reuse: one pass, every warp-level access a contiguous 512 B (fp32) run, 2 independent
 // 16 B accesses per array per thread in flight, one tile per CTA (see grid_mult() in dgs_api.cu).
 #include "dgs_common.cuh"
+
+#include <cstdlib>
 
 namespace dgs {
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kUnroll = 4;
 constexpr int kMaxSegs = 64;
 
 struct SegDev {
@@ -30,18 +31,18 @@ struct FlatParams {
   long long tiles;
 };
 
-template <typename G, typename W, bool READ_ACC, bool WRITE_WIRE>
+template <typename G, typename W, bool READ_ACC, bool WRITE_WIRE, int kUnroll>
 struct FlatCfg {
   // 8 elements per access only when every array in the loop is 16-bit
   static constexpr int VEC = (is16<G>::value && WRITE_WIRE && !READ_ACC && is16<W>::value) ? 8 : 4;
   static constexpr int TILE = kThreads * VEC * kUnroll;
 };
 
-template <typename G, typename W, bool READ_ACC, bool WRITE_WIRE>
+template <typename G, typename W, bool READ_ACC, bool WRITE_WIRE, int kUnroll>
 __global__ void __launch_bounds__(kThreads)
 flatten_kernel(const __grid_constant__ FlatParams P, float* __restrict__ acc, W* __restrict__ wire,
                float scale) {
-  using Cfg = FlatCfg<G, W, READ_ACC, WRITE_WIRE>;
+  using Cfg = FlatCfg<G, W, READ_ACC, WRITE_WIRE, kUnroll>;
   constexpr int VEC = Cfg::VEC;
   constexpr int TILE = Cfg::TILE;
 
@@ -119,10 +120,10 @@ scale_cast_kernel(const float* __restrict__ acc, W* __restrict__ wire, long long
   }
 }
 
-template <typename G, typename W, bool RA, bool WW>
-int launch_flatten(const dgs_seg* segs, int n_segs, float* acc, void* wire, float scale,
+template <typename G, typename W, bool RA, bool WW, int kUnroll>
+int launch_flatten_u(const dgs_seg* segs, int n_segs, float* acc, void* wire, float scale,
                    cudaStream_t st) {
-  constexpr int TILE = FlatCfg<G, W, RA, WW>::TILE;
+  constexpr int TILE = FlatCfg<G, W, RA, WW, kUnroll>::TILE;
   for (int s0 = 0; s0 < n_segs; s0 += kMaxSegs) {
     FlatParams P;
     const int n = (n_segs - s0 < kMaxSegs) ? n_segs - s0 : kMaxSegs;
@@ -145,10 +146,28 @@ int launch_flatten(const dgs_seg* segs, int n_segs, float* acc, void* wire, floa
     P.tiles = tiles;
     const long long cap = (long long)sm_count() * grid_mult();
     const int grid = (int)(tiles < cap ? tiles : cap);
-    flatten_kernel<G, W, RA, WW><<<grid, kThreads, 0, st>>>(P, acc, static_cast<W*>(wire), scale);
+    flatten_kernel<G, W, RA, WW, kUnroll><<<grid, kThreads, 0, st>>>(P, acc, static_cast<W*>(wire), scale);
     DGS_LAUNCHED();
   }
   return DGS_OK;
+}
+
+inline int flat_unroll() {
+  static const int v = [] {
+    const char* e = getenv("DGS_FLAT_UNROLL");
+    return e ? atoi(e) : 0;
+  }();
+  return v;
+}
+
+template <typename G, typename W, bool RA, bool WW>
+int launch_flatten(const dgs_seg* segs, int n_segs, float* acc, void* wire, float scale, cudaStream_t st) {
+  // 2 vectors per thread per array measured best on B200 for every dtype mix (gpurun_out/sweep_unroll*.txt:
+  // bf16->bf16 0.78 -> 1.00 of the copy peak against 4); DGS_FLAT_UNROLL=1|4 re-runs the sweep.
+  const int u = flat_unroll();
+  if (u == 4) return launch_flatten_u<G, W, RA, WW, 4>(segs, n_segs, acc, wire, scale, st);
+  if (u == 1) return launch_flatten_u<G, W, RA, WW, 1>(segs, n_segs, acc, wire, scale, st);
+  return launch_flatten_u<G, W, RA, WW, 2>(segs, n_segs, acc, wire, scale, st);
 }
 
 template <typename G, typename W>

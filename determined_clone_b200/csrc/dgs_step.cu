@@ -7,15 +7,16 @@
 // 16-bit params/state.
 //
 // HBM-bound: AdamW moves 28 B/element in fp32 (read g,p,m,v; write p,m,v), SGD-momentum 20 B.  Each
-// thread keeps kUnroll x 4 independent 16 B loads in flight; every warp access is contiguous; one tile per
+// thread keeps 3-4 independent 16 B loads in flight (one per array); every warp access is contiguous; one tile per
 // CTA (measured faster on B200 than a persistent grid-stride loop, see grid_mult() in dgs_api.cu).
 #include "dgs_common.cuh"
+
+#include <cstdlib>
 
 namespace dgs {
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kUnroll = 2;
 
 // ---- device-side hyper-parameter tables (fp32 constants derived on the host in double) ----------
 struct AdamHp {
@@ -82,19 +83,27 @@ __device__ __forceinline__ int find_range(const Table<Hp>& T, long long e) {
   return -1;
 }
 
-template <typename P, typename G>
+template <typename P, typename G, int kUnroll>
 struct StepCfg {
   static constexpr int VEC = (is16<P>::value && is16<G>::value) ? 8 : 4;
   static constexpr int TILE = kThreads * VEC * kUnroll;
 };
 
-template <typename P, typename G>
+inline int step_unroll() {
+  static const int v = [] {
+    const char* e = getenv("DGS_STEP_UNROLL");
+    return e ? atoi(e) : 0;
+  }();
+  return v;
+}
+
+template <typename P, typename G, int kUnroll>
 __global__ void __launch_bounds__(kThreads)
 adam_kernel(P* __restrict__ param, P* __restrict__ ea, P* __restrict__ eas, const G* __restrict__ grad,
             long long n, const __grid_constant__ Table<AdamHp> T,
             const float* __restrict__ total_norm, float max_norm) {
-  constexpr int VEC = StepCfg<P, G>::VEC;
-  constexpr int TILE = StepCfg<P, G>::TILE;
+  constexpr int VEC = StepCfg<P, G, kUnroll>::VEC;
+  constexpr int TILE = StepCfg<P, G, kUnroll>::TILE;
   const float clip = clip_coef(total_norm, max_norm);
   const long long tiles = (n + TILE - 1) / TILE;
   for (long long t = blockIdx.x; t < tiles; t += gridDim.x) {
@@ -139,13 +148,13 @@ adam_kernel(P* __restrict__ param, P* __restrict__ ea, P* __restrict__ eas, cons
   }
 }
 
-template <typename P, typename G, bool HAS_BUF>
+template <typename P, typename G, bool HAS_BUF, int kUnroll>
 __global__ void __launch_bounds__(kThreads)
 sgd_kernel(P* __restrict__ param, P* __restrict__ buf, const G* __restrict__ grad, long long n,
            const __grid_constant__ Table<SgdHp> T, const float* __restrict__ total_norm,
            float max_norm) {
-  constexpr int VEC = StepCfg<P, G>::VEC;
-  constexpr int TILE = StepCfg<P, G>::TILE;
+  constexpr int VEC = StepCfg<P, G, kUnroll>::VEC;
+  constexpr int TILE = StepCfg<P, G, kUnroll>::TILE;
   const float clip = clip_coef(total_norm, max_norm);
   const long long tiles = (n + TILE - 1) / TILE;
   for (long long t = blockIdx.x; t < tiles; t += gridDim.x) {
@@ -216,12 +225,35 @@ int check_ranges(const char* who, const Range* ranges, int n_ranges, int64_t n) 
   return DGS_OK;
 }
 
+template <typename P, typename G, int U>
+int launch_adam_u(void* param, void* ea, void* eas, const void* grad, int64_t n, const Table<AdamHp>& T,
+                  const float* tn, float max_norm, cudaStream_t st) {
+  const long long tiles = (n + StepCfg<P, G, U>::TILE - 1) / StepCfg<P, G, U>::TILE;
+  const int grid = tile_grid(tiles);
+  adam_kernel<P, G, U><<<grid, kThreads, 0, st>>>((P*)param, (P*)ea, (P*)eas, (const G*)grad, n, T, tn, max_norm);
+  DGS_LAUNCHED();
+  return DGS_OK;
+}
+
 template <typename P, typename G>
 int launch_adam(void* param, void* ea, void* eas, const void* grad, int64_t n, const Table<AdamHp>& T,
                 const float* tn, float max_norm, cudaStream_t st) {
-  const long long tiles = (n + StepCfg<P, G>::TILE - 1) / StepCfg<P, G>::TILE;
+  // one vector per array per thread (4 loads in flight) measured best; DGS_STEP_UNROLL=2|4 re-runs the sweep
+  if (step_unroll() == 2) return launch_adam_u<P, G, 2>(param, ea, eas, grad, n, T, tn, max_norm, st);
+  if (step_unroll() == 4) return launch_adam_u<P, G, 4>(param, ea, eas, grad, n, T, tn, max_norm, st);
+  return launch_adam_u<P, G, 1>(param, ea, eas, grad, n, T, tn, max_norm, st);
+}
+
+template <typename P, typename G, int U>
+int launch_sgd_u(void* param, void* buf, const void* grad, int64_t n, const Table<SgdHp>& T,
+                 const float* tn, float max_norm, cudaStream_t st) {
+  const long long tiles = (n + StepCfg<P, G, U>::TILE - 1) / StepCfg<P, G, U>::TILE;
   const int grid = tile_grid(tiles);
-  adam_kernel<P, G><<<grid, kThreads, 0, st>>>((P*)param, (P*)ea, (P*)eas, (const G*)grad, n, T, tn, max_norm);
+  if (buf != nullptr) {
+    sgd_kernel<P, G, true, U><<<grid, kThreads, 0, st>>>((P*)param, (P*)buf, (const G*)grad, n, T, tn, max_norm);
+  } else {
+    sgd_kernel<P, G, false, U><<<grid, kThreads, 0, st>>>((P*)param, nullptr, (const G*)grad, n, T, tn, max_norm);
+  }
   DGS_LAUNCHED();
   return DGS_OK;
 }
@@ -229,16 +261,9 @@ int launch_adam(void* param, void* ea, void* eas, const void* grad, int64_t n, c
 template <typename P, typename G>
 int launch_sgd(void* param, void* buf, const void* grad, int64_t n, const Table<SgdHp>& T,
                const float* tn, float max_norm, cudaStream_t st) {
-  const long long tiles = (n + StepCfg<P, G>::TILE - 1) / StepCfg<P, G>::TILE;
-  if (buf != nullptr) {
-    const int grid = tile_grid(tiles);
-    sgd_kernel<P, G, true><<<grid, kThreads, 0, st>>>((P*)param, (P*)buf, (const G*)grad, n, T, tn, max_norm);
-  } else {
-    const int grid = tile_grid(tiles);
-    sgd_kernel<P, G, false><<<grid, kThreads, 0, st>>>((P*)param, nullptr, (const G*)grad, n, T, tn, max_norm);
-  }
-  DGS_LAUNCHED();
-  return DGS_OK;
+  if (step_unroll() == 2) return launch_sgd_u<P, G, 2>(param, buf, grad, n, T, tn, max_norm, st);
+  if (step_unroll() == 4) return launch_sgd_u<P, G, 4>(param, buf, grad, n, T, tn, max_norm, st);
+  return launch_sgd_u<P, G, 1>(param, buf, grad, n, T, tn, max_norm, st);
 }
 
 }  // namespace

@@ -62,6 +62,10 @@ class Comm:
             self._handle(), ctypes.c_void_p(send.data_ptr()), ctypes.c_void_p(recv.data_ptr()), nbytes, _stream()
         )
 
+    def l2norm_partial(self, ptr: int, dtype_code: int, n: int, partials_ptr: int) -> None:
+        """Norm pass 1 over a slice, on the side stream behind the collectives issued so far."""
+        _lib.calls.dgs_comm_l2norm_partial_async(self._handle(), ctypes.c_void_p(ptr), dtype_code, n, ctypes.c_void_p(partials_ptr))
+
     def wait(self) -> None:
         """Make the current stream wait for every collective issued so far (no host block)."""
         _lib.calls.dgs_comm_wait(self._handle(), _stream())

@@ -38,7 +38,7 @@ from determined_clone_b200.pytorch._comm import Comm
 _SKIP_ALLREDUCE = "allreduce" in __import__("os").environ.get("DGS_DEBUG_SKIP", "")  # measurement aid only
 ALIGN_ELEMS = 64  # 128 bytes of bf16, 256 bytes of fp32: every tensor starts vector-aligned
 FIRST_BUCKET_BYTES = 1 << 20
-BUCKET_BYTES = 25 << 20
+BUCKET_BYTES = int(__import__("os").environ.get("DGS_BUCKET_MB", "25")) << 20  # torch DDP's default; env for tuning
 
 
 def _align(n: int) -> int:
@@ -78,10 +78,13 @@ class _Tensor:
 
 
 class _Bucket:
-    __slots__ = ("begin", "end", "tensors", "flushed", "reduced")
+    __slots__ = ("begin", "end", "tensors", "flushed", "reduced", "norm_off", "norm_n", "norm_done", "segs")
 
     def __init__(self, begin: int, end: int, tensors: List[int]) -> None:
         self.begin, self.end, self.tensors = begin, end, tensors
+        self.norm_off = self.norm_n = 0  # this bucket's slots in the engine's norm partials
+        self.norm_done = False  # pass 1 of the norm already ran on this bucket in this window
+        self.segs: Any = None  # prebuilt dgs_seg[len(tensors)] (dst_off, numel fixed; src set per flush)
         self.flushed = False  # wire produced for this window
         self.reduced = False  # allreduce issued for this window
 
@@ -105,6 +108,8 @@ class _FlatSet:
         self.in_wire: List[bool] = []  # tensor's wire slice is final for this window
         self.next_reduce = 0
         self.dtype_code = self.wire_code = 0
+        self.acc_ptr: Any = None
+        self.wire_ptr: Any = None
         self.group_runs: Optional[List[Tuple[int, int, int, List[_Tensor]]]] = None
         self.steady = False  # last step covered every parameter and left every state tensor as our view
         self.uniform_step: Optional[int] = None  # Adam: the common step count while all parameters move together
@@ -152,6 +157,13 @@ class GradSyncEngine:
         self._fused_kind = self._classify(optimizer)
         self.last_total_norm: Optional[torch.Tensor] = None
         self._timing: Optional[List[Tuple[torch.cuda.Event, torch.cuda.Event]]] = None
+        # Several GPUs: norm pass 1 is run per bucket right behind the bucket's allreduce (aux stream, bucket still
+        # in L2) once a clip_grad_norm_ request has been seen; switched off again if nobody asks for the norm.
+        # One GPU: a single pass over the whole buffer at step time (fewer launches, nothing to hide behind).
+        self._eager_norm = False
+        self._eager_unused = 0
+        self._norm_slots_valid = True
+        self._norm_requested = False
         self._build()
 
     # ---- construction ---------------------------------------------------------------------------
@@ -209,7 +221,14 @@ class GradSyncEngine:
             fs.in_wire = [False] * len(fs.tensors)
             self._cut_buckets(fs)
             fs.dtype_code, fs.wire_code = _lib.dtype_code(fs.dtype), _lib.dtype_code(fs.wire_dtype)
+            fs.acc_ptr, fs.wire_ptr = _ptr(fs.acc), _ptr(fs.wire)
+        # norm scratch: [whole-buffer partials of every set | per-bucket partials of every set]
         n_partials = sum(_lib.calls.dgs_l2norm_grid(fs.total) for fs in self.sets)
+        self._bucket_partials_base = n_partials
+        for fs in self.sets:
+            for b in fs.buckets:
+                b.norm_off, b.norm_n = n_partials, _lib.calls.dgs_l2norm_grid(b.end - b.begin)
+                n_partials += b.norm_n
         self._partials = torch.zeros(max(n_partials, 1), dtype=torch.float32, device=self.device)
         if self.comm is not None:
             # what DDP's constructor does: every replica starts from rank 0's parameters
@@ -232,8 +251,11 @@ class GradSyncEngine:
         if cur:
             fs.buckets.append(_Bucket(0, end, cur))
         for bi, b in enumerate(fs.buckets):
-            for ti in b.tensors:
-                fs.tensors[ti].bucket = bi
+            b.segs = (_lib.Seg * len(b.tensors))()
+            for k, ti in enumerate(b.tensors):
+                t = fs.tensors[ti]
+                t.bucket = bi
+                b.segs[k].dst_off, b.segs[k].numel = t.off, t.numel
 
     def close(self) -> None:
         for h in self._hooks:
@@ -346,20 +368,33 @@ class GradSyncEngine:
         if not to_wire and fs.acc is None:
             # more passes than configured: grow an accumulator on demand
             fs.acc = torch.zeros(fs.total, dtype=torch.float32, device=self.device)
+            fs.acc_ptr = _ptr(fs.acc)
         stream = _stream()
-        for read_acc in (False, True):
-            idxs = [ti for ti in grads if fs.in_window[ti] == read_acc]
-            if not idxs:
-                continue
-            segs = (_lib.Seg * len(idxs))()
-            for k, ti in enumerate(idxs):
-                t = fs.tensors[ti]
-                seg = segs[k]
-                seg.src, seg.dst_off, seg.numel = grads[ti].data_ptr(), t.off, t.numel
-            mode = (_lib.READ_ACC if read_acc else 0) | (_lib.WRITE_WIRE if to_wire else 0)
+        in_window = fs.in_window
+        first_state = in_window[b.tensors[0]]
+        if len(grads) == len(b.tensors) and all(in_window[ti] == first_state for ti in b.tensors):
+            # the usual case: the whole bucket, all tensors in the same accumulation state -> prebuilt table
+            segs = b.segs
+            for k, ti in enumerate(b.tensors):
+                segs[k].src = grads[ti].data_ptr()
+            mode = (_lib.READ_ACC if first_state else 0) | (_lib.WRITE_WIRE if to_wire else 0)
             _lib.calls.dgs_flatten_accumulate(
-                segs, len(idxs), fs.dtype_code, _ptr(fs.acc), _ptr(fs.wire), fs.wire_code, mode, self.scale, stream,
+                segs, len(b.tensors), fs.dtype_code, fs.acc_ptr, fs.wire_ptr, fs.wire_code, mode, self.scale, stream,
             )
+        else:
+            for read_acc in (False, True):
+                idxs = [ti for ti in grads if in_window[ti] == read_acc]
+                if not idxs:
+                    continue
+                segs = (_lib.Seg * len(idxs))()
+                for k, ti in enumerate(idxs):
+                    t = fs.tensors[ti]
+                    seg = segs[k]
+                    seg.src, seg.dst_off, seg.numel = grads[ti].data_ptr(), t.off, t.numel
+                mode = (_lib.READ_ACC if read_acc else 0) | (_lib.WRITE_WIRE if to_wire else 0)
+                _lib.calls.dgs_flatten_accumulate(
+                    segs, len(idxs), fs.dtype_code, fs.acc_ptr, fs.wire_ptr, fs.wire_code, mode, self.scale, stream,
+                )
         flags = fs.in_wire if to_wire else fs.in_window
         for ti in grads:
             flags[ti] = True
@@ -372,9 +407,14 @@ class GradSyncEngine:
         """Issue allreduces strictly in bucket order so that every rank issues the same sequence."""
         while fs.next_reduce < len(fs.buckets) and fs.buckets[fs.next_reduce].flushed:
             b = fs.buckets[fs.next_reduce]
+            itemsize = fs.wire.element_size()
             if self.comm is not None and not b.reduced and not _SKIP_ALLREDUCE:
-                itemsize = fs.wire.element_size()
-                self.comm.allreduce_raw(fs.wire.data_ptr() + b.begin * itemsize, b.end - b.begin, _lib.dtype_code(fs.wire_dtype))
+                self.comm.allreduce_raw(fs.wire.data_ptr() + b.begin * itemsize, b.end - b.begin, fs.wire_code)
+            if self._eager_norm and self.comm is not None and not b.norm_done:
+                # behind this bucket's allreduce, on the communicator's aux stream, while the bucket is in L2
+                self.comm.l2norm_partial(fs.wire.data_ptr() + b.begin * itemsize, fs.wire_code, b.end - b.begin,
+                                         self._partials.data_ptr() + 4 * b.norm_off)
+                b.norm_done = True
             b.reduced = True
             fs.next_reduce += 1
 
@@ -418,6 +458,7 @@ class GradSyncEngine:
                     for ti in missing:  # absent gradients must not leak stale values into the norm
                         t = fs.tensors[ti]
                         fs.wire[t.off:t.off + t.numel].zero_()
+                    self._norm_slots_valid = False
                 b.flushed = True
             self._reduce_ready(fs)
             present.append(have)
@@ -426,13 +467,21 @@ class GradSyncEngine:
         return present
 
     def total_norm(self) -> torch.Tensor:
-        """Global L2 norm of the synchronized gradients, left on the device (fp32 scalar)."""
-        off = 0
-        for fs in self.sets:
-            n = _lib.calls.dgs_l2norm_grid(fs.total)
-            _lib.calls.dgs_l2norm_partial(_ptr(fs.wire), _lib.dtype_code(fs.wire_dtype), fs.total, _ptr(self._partials, 4 * off), _stream())
-            off += n
-        _lib.calls.dgs_l2norm_final(_ptr(self._partials), off, _ptr(self._norm), _stream())
+        """Global L2 norm of the synchronized gradients, left on the device (fp32 scalar).  Call after
+        finish_window()."""
+        stream = _stream()
+        if self.comm is not None and self._eager_norm and self._norm_slots_valid and all(b.norm_done for fs in self.sets for b in fs.buckets):
+            # pass 1 already ran bucket by bucket behind the allreduces: only the final reduction is left
+            n = self._partials.numel() - self._bucket_partials_base
+            _lib.calls.dgs_l2norm_final(_ptr(self._partials, 4 * self._bucket_partials_base), n, _ptr(self._norm), stream)
+        else:
+            off = 0
+            for fs in self.sets:
+                n = _lib.calls.dgs_l2norm_grid(fs.total)
+                _lib.calls.dgs_l2norm_partial(_ptr(fs.wire), fs.wire_code, fs.total, _ptr(self._partials, 4 * off), stream)
+                off += n
+            _lib.calls.dgs_l2norm_final(_ptr(self._partials), off, _ptr(self._norm), stream)
+        self._eager_norm, self._eager_unused, self._norm_requested = True, 0, True
         self.last_total_norm = self._norm[0]
         return self.last_total_norm
 
@@ -454,12 +503,17 @@ class GradSyncEngine:
                 t.param.grad = None
 
     def reset_window(self) -> None:
+        if self._eager_norm and not self._norm_requested:
+            self._eager_unused += 1
+            if self._eager_unused >= 3:
+                self._eager_norm = False  # nobody clips by norm any more
+        self._norm_slots_valid, self._norm_requested = True, False
         for fs in self.sets:
             fs.next_reduce = 0
             for i in range(len(fs.tensors)):
                 fs.in_window[i] = fs.in_wire[i] = False
             for b in fs.buckets:
-                b.flushed = b.reduced = False
+                b.flushed = b.reduced = b.norm_done = False
 
     # -- fused step -----------------------------------------------------------------------------------
     def can_fuse(self) -> bool:

@@ -246,6 +246,11 @@ int dgs_comm_broadcast_async(dgs_comm* comm, void* buf, int64_t bytes, int root,
 /* recv holds nranks * bytes_per_rank bytes, ordered by rank */
 int dgs_comm_allgather_async(dgs_comm* comm, const void* send, void* recv, int64_t bytes_per_rank,
                              dgs_stream_t compute);
+/* Pass 1 of the L2 norm (dgs_l2norm_partial) over x[0..n), enqueued on the communicator's side stream
+ * behind the collectives issued so far -- typically right behind the allreduce of the same bucket, while
+ * the bucket is still in L2 and the compute stream is busy with backward.  Takes the norm's read of the
+ * gradients (H/pytorch/_pytorch_context.py:902) off the critical tail of step_optimizer. */
+int dgs_comm_l2norm_partial_async(dgs_comm* comm, const void* x, int dtype, int64_t n, float* partials);
 int dgs_comm_wait(dgs_comm* comm, dgs_stream_t compute);
 int dgs_nccl_version(int* version);
 

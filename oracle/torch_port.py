@@ -54,7 +54,17 @@ class RefContext:
         return (self._current_batch_idx + 1) % self._aggregation_frequency == 0
 
     def backward(self, loss: torch.Tensor) -> None:
-        loss.backward()
+        ddp = [m for m in self.models if isinstance(m, torch.nn.parallel.DistributedDataParallel)]
+        if ddp and not self._should_communicate_and_update():
+            # DDP all-reduces on every backward unless told otherwise (_pytorch_context.py:802-812)
+            import contextlib
+
+            with contextlib.ExitStack() as stack:
+                for m in ddp:
+                    stack.enter_context(m.no_sync())
+                loss.backward()
+        else:
+            loss.backward()
 
     @staticmethod
     def _average_gradients(parameters: Any, divisor: int) -> None:

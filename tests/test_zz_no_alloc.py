@@ -45,8 +45,8 @@ def _reference_norm(x):
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_noalloc_norm_matches_existing_entry_point_twice_in_a_row(lib, dtype):
     gen = torch.Generator(device="cuda").manual_seed(11)
-    first = (torch.randn(3_000_003, device="cuda", generator=gen) * 0.3).to(dtype)   # 184 partials
-    second = (torch.randn(70_001, device="cuda", generator=gen) * 5.0).to(dtype)     # 5 partials; 179 stale ones stay behind
+    first = (torch.randn(3_000_003, device="cuda", generator=gen) * 0.3).to(dtype)   # 92 partials
+    second = (torch.randn(70_001, device="cuda", generator=gen) * 5.0).to(dtype)     # 3 partials; 89 stale ones stay behind
     for x in (first, second):
         out = torch.full((1,), -1.0, device="cuda")
         before = torch.cuda.memory_allocated()
