@@ -38,7 +38,13 @@ from determined_clone_b200.pytorch._comm import Comm
 _SKIP_ALLREDUCE = "allreduce" in __import__("os").environ.get("DGS_DEBUG_SKIP", "")  # measurement aid only
 ALIGN_ELEMS = 64  # 128 bytes of bf16, 256 bytes of fp32: every tensor starts vector-aligned
 FIRST_BUCKET_BYTES = 1 << 20
-BUCKET_BYTES = int(__import__("os").environ.get("DGS_BUCKET_MB", "25")) << 20  # torch DDP's default; env for tuning
+# Bucket cap: NCCL's allreduce over NVSwitch needs large messages (measured at 8 x B200, gpurun_out/
+# nccl_probe_n8.jsonl: bus bandwidth 331 GB/s at 25 MiB, 418 at 64, 590 at 128, 728 at 1 GiB), small models
+# want several buckets to overlap with backward.  Default: 1/8 of the gradient bytes clamped to
+# [25 MiB (torch DDP's size), 128 MiB]; DGS_BUCKET_MB fixes it for tuning.
+_BUCKET_MB_ENV = __import__("os").environ.get("DGS_BUCKET_MB")
+BUCKET_BYTES = (int(_BUCKET_MB_ENV) << 20) if _BUCKET_MB_ENV else 0  # 0 = adaptive
+MIN_BUCKET_BYTES, MAX_BUCKET_BYTES = 25 << 20, 128 << 20
 
 
 def _align(n: int) -> int:
@@ -106,7 +112,6 @@ class _FlatSet:
         self.grad_views: List[torch.Tensor] = []
         self.in_window: List[bool] = []  # tensor has contributed to the accumulator in this window
         self.in_wire: List[bool] = []  # tensor's wire slice is final for this window
-        self.next_reduce = 0
         self.dtype_code = self.wire_code = 0
         self.acc_ptr: Any = None
         self.wire_ptr: Any = None
@@ -164,6 +169,9 @@ class GradSyncEngine:
         self._eager_unused = 0
         self._norm_slots_valid = True
         self._norm_requested = False
+        self._launch_order: List[Tuple[int, int]] = []
+        self._pending_order: Optional[List[Tuple[int, int]]] = None
+        self._next_launch = 0
         self._build()
 
     # ---- construction ---------------------------------------------------------------------------
@@ -230,6 +238,7 @@ class GradSyncEngine:
                 b.norm_off, b.norm_n = n_partials, _lib.calls.dgs_l2norm_grid(b.end - b.begin)
                 n_partials += b.norm_n
         self._partials = torch.zeros(max(n_partials, 1), dtype=torch.float32, device=self.device)
+        self._launch_order = [(si, bi) for si, fs in enumerate(self.sets) for bi in range(len(fs.buckets))]
         if self.comm is not None:
             # what DDP's constructor does: every replica starts from rank 0's parameters
             for fs in self.sets:
@@ -238,6 +247,7 @@ class GradSyncEngine:
 
     def _cut_buckets(self, fs: _FlatSet) -> None:
         itemsize = torch.empty(0, dtype=fs.wire_dtype).element_size()
+        cap = self.bucket_bytes or min(max(fs.total * itemsize // 8, MIN_BUCKET_BYTES), MAX_BUCKET_BYTES)
         limit = self.first_bucket_bytes
         cur: List[int] = []
         cur_bytes = 0
@@ -247,7 +257,7 @@ class GradSyncEngine:
             cur_bytes += t.numel * itemsize
             if cur_bytes >= limit:
                 fs.buckets.append(_Bucket(t.off, end, cur))
-                end, cur, cur_bytes, limit = t.off, [], 0, self.bucket_bytes
+                end, cur, cur_bytes, limit = t.off, [], 0, cap
         if cur:
             fs.buckets.append(_Bucket(0, end, cur))
         for bi, b in enumerate(fs.buckets):
@@ -322,6 +332,17 @@ class GradSyncEngine:
         last: Dict[Tuple[int, int], int] = {}
         for pos, (si, ti) in enumerate(self._order):
             last[(si, self.sets[si].tensors[ti].bucket)] = pos
+        # buckets are all-reduced in the order in which they complete (a param group that collects every
+        # layer's 1-D parameters completes last wherever it sits in the buffer); rank 0's order is adopted
+        # by everyone so that the NCCL sequences cannot differ
+        order = sorted(last, key=lambda k: last[k])
+        if len(order) == len(self._launch_order):
+            flat = torch.tensor([x for sb in order for x in sb], dtype=torch.int64, device=self.device)
+            self.comm.broadcast(flat, 0)  # type: ignore
+            self.comm.wait()  # type: ignore
+            got = flat.tolist()
+            # adopted at the next window boundary: this window may already be part-way through the old order
+            self._pending_order = [(got[i], got[i + 1]) for i in range(0, len(got), 2)]
         for (si, bi), pos in last.items():
             _, ti = self._order[pos]
             param = self.sets[si].tensors[ti].param
@@ -403,10 +424,17 @@ class GradSyncEngine:
             b.flushed = True
             self._reduce_ready(fs)
 
-    def _reduce_ready(self, fs: _FlatSet) -> None:
-        """Issue allreduces strictly in bucket order so that every rank issues the same sequence."""
-        while fs.next_reduce < len(fs.buckets) and fs.buckets[fs.next_reduce].flushed:
-            b = fs.buckets[fs.next_reduce]
+    def _reduce_ready(self, fs: Optional[_FlatSet] = None) -> None:
+        """Issue allreduces strictly in `_launch_order`, so that every rank issues the same NCCL sequence.
+        The order starts as (set, bucket index) and is replaced after the first backward pass by the order
+        in which the buckets actually complete (rank 0's, broadcast to all ranks)."""
+        order = self._launch_order
+        while self._next_launch < len(order):
+            si, bi = order[self._next_launch]
+            fs = self.sets[si]
+            b = fs.buckets[bi]
+            if not b.flushed:
+                return
             itemsize = fs.wire.element_size()
             if self.comm is not None and not b.reduced and not _SKIP_ALLREDUCE:
                 self.comm.allreduce_raw(fs.wire.data_ptr() + b.begin * itemsize, b.end - b.begin, fs.wire_code)
@@ -416,7 +444,7 @@ class GradSyncEngine:
                                          self._partials.data_ptr() + 4 * b.norm_off)
                 b.norm_done = True
             b.reduced = True
-            fs.next_reduce += 1
+            self._next_launch += 1
 
     # ---- step ---------------------------------------------------------------------------------------
     def finish_window(self) -> List[List[bool]]:
@@ -508,8 +536,10 @@ class GradSyncEngine:
             if self._eager_unused >= 3:
                 self._eager_norm = False  # nobody clips by norm any more
         self._norm_slots_valid, self._norm_requested = True, False
+        self._next_launch = 0
+        if self._pending_order is not None:
+            self._launch_order, self._pending_order = self._pending_order, None
         for fs in self.sets:
-            fs.next_reduce = 0
             for i in range(len(fs.tensors)):
                 fs.in_window[i] = fs.in_wire[i] = False
             for b in fs.buckets:
