@@ -78,6 +78,7 @@ SIGNATURES = {
     "dgs_step_sgd": [_vp, _vp, _i, _vp, _i, _i64, ctypes.POINTER(SgdRange), _i, _vp, _f, _vp],
     "dgs_metric_pack": [ctypes.POINTER(ScalarRef), _i, _vp, _vp, _vp],
     "dgs_metric_average": [_vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp],
+    "dgs_metric_average_packed": [_vp, _i64, _i, _i, _i, _vp, _vp, _vp, _vp, _vp],
     "dgs_metric_reduce": [_vp, _vp, _i, _i, _i, _vp, _vp],
     "dgs_comm_unique_id": [_vp],
     "dgs_comm_init": [_vp, _i, _i, _i, ctypes.POINTER(_vp)],

@@ -40,19 +40,20 @@ __global__ void metric_pack_kernel(const __grid_constant__ PackParams P, double*
   valid[j] = p != nullptr;
 }
 
-// one thread per (batch, metric): mean over contributing ranks, in rank order
-__global__ void metric_rank_mean_kernel(const double* __restrict__ gathered, const uint8_t* __restrict__ valid,
-                                        const long long* __restrict__ num_batches, int n_ranks, int b, int m,
+// one thread per (batch, metric): mean over contributing ranks, in rank order.  Rank r's values, validity
+// bytes and batch count start r * stride_* bytes after the base pointers (separate arrays or packed records).
+__global__ void metric_rank_mean_kernel(const char* __restrict__ gathered, const char* __restrict__ valid,
+                                        const char* __restrict__ num_batches, long long stride_vals,
+                                        long long stride_valid, long long stride_nb, int n_ranks, int b, int m,
                                         double* __restrict__ per_batch, uint8_t* __restrict__ per_batch_valid) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= b * m) return;
   double s = 0.0;
   long long c = 0;
   for (int r = 0; r < n_ranks; ++r) {
-    if (num_batches[r] == 0) continue;  // _process_combined_metrics_and_batches drops these ranks
-    const size_t k = (size_t)r * b * m + i;
-    if (valid[k]) {
-      s += gathered[k];
+    if (*reinterpret_cast<const long long*>(num_batches + r * stride_nb) == 0) continue;  // rank reported nothing
+    if (reinterpret_cast<const uint8_t*>(valid + r * stride_valid)[i]) {
+      s += reinterpret_cast<const double*>(gathered + r * stride_vals)[i];
       ++c;
     }
   }
@@ -150,11 +151,35 @@ extern "C" int dgs_metric_average(const double* gathered, const uint8_t* valid, 
   if (b > 0) {
     const int total = b * m;
     metric_rank_mean_kernel<<<(total + 255) / 256, 256, 0, st>>>(
-        gathered, valid, reinterpret_cast<const long long*>(num_batches), n_ranks, b, m, per_batch, per_batch_valid);
+        reinterpret_cast<const char*>(gathered), reinterpret_cast<const char*>(valid),
+        reinterpret_cast<const char*>(num_batches), 8LL * total, 1LL * total, 8LL, n_ranks, b, m, per_batch, per_batch_valid);
     DGS_LAUNCHED();
   }
   metric_batch_mean_kernel<<<m, 256, 0, st>>>(per_batch, per_batch_valid, b, m, avg,
                                               reinterpret_cast<long long*>(count));
+  DGS_LAUNCHED();
+  return DGS_OK;
+}
+
+extern "C" int dgs_metric_average_packed(const void* records, int64_t record_bytes, int n_ranks, int b, int m,
+                                         double* per_batch, uint8_t* per_batch_valid, double* avg, int64_t* count,
+                                         dgs_stream_t stream) {
+  using namespace dgs;
+  DGS_CHECK_ARG(n_ranks >= 1 && b >= 0 && m >= 0, "dgs_metric_average_packed: bad shape [%d, %d, %d]", n_ranks, b, m);
+  if (m == 0) return DGS_OK;
+  const long long total = (long long)b * m;
+  DGS_CHECK_ARG((record_bytes & 7) == 0 && record_bytes >= 9 * total + 8,
+                "dgs_metric_average_packed: record_bytes %lld too small or not a multiple of 8", (long long)record_bytes);
+  DGS_CHECK_ARG(records && per_batch && per_batch_valid && avg && count, "dgs_metric_average_packed: NULL argument");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const char* base = static_cast<const char*>(records);
+  if (b > 0) {
+    metric_rank_mean_kernel<<<(int)((total + 255) / 256), 256, 0, st>>>(
+        base, base + 8 * total + 8, base + 8 * total, record_bytes, record_bytes, record_bytes, n_ranks, b, m, per_batch,
+        per_batch_valid);
+    DGS_LAUNCHED();
+  }
+  metric_batch_mean_kernel<<<m, 256, 0, st>>>(per_batch, per_batch_valid, b, m, avg, reinterpret_cast<long long*>(count));
   DGS_LAUNCHED();
   return DGS_OK;
 }

@@ -221,30 +221,30 @@ class DeviceMetricBuffer:
             return [], {}, []
         assert self._ring is not None and self._valid is not None
         n = distributed.size
-        ring, valid = self._ring[:b].contiguous(), self._valid[:b].contiguous()
-        nb = torch.full((1,), b, dtype=torch.int64, device=self.device)
-        if n > 1:
-            comm = distributed.comm
-            if comm is None:
-                raise _lib.DgsError("DeviceMetricBuffer.reduce: no NCCL communicator attached to the DistributedContext")
-            all_ring = torch.empty(n, b, m, dtype=torch.float64, device=self.device)
-            all_valid = torch.empty(n, b, m, dtype=torch.uint8, device=self.device)
-            all_nb = torch.empty(n, dtype=torch.int64, device=self.device)
-            comm.allgather(ring, all_ring)
-            comm.allgather(valid, all_valid)
-            comm.allgather(nb, all_nb)
-            comm.wait()
-        else:
-            all_ring, all_valid, all_nb = ring, valid, nb
         # one result block -> one device->host copy: [per_batch b*m f64 | avg m f64 | count m i64 | valid b*m u8]
         n_f64 = b * m + m
         block = torch.empty(8 * n_f64 + 8 * m + b * m, dtype=torch.uint8, device=self.device)
         base = block.data_ptr()
-        _lib.calls.dgs_metric_average(
-            _p(all_ring), _p(all_valid), _p(all_nb), n, b, m,
-            ctypes.c_void_p(base), ctypes.c_void_p(base + 8 * n_f64 + 8 * m),
-            ctypes.c_void_p(base + 8 * b * m), ctypes.c_void_p(base + 8 * n_f64), _stream(),
-        )
+        outs = (ctypes.c_void_p(base), ctypes.c_void_p(base + 8 * n_f64 + 8 * m), ctypes.c_void_p(base + 8 * b * m),
+                ctypes.c_void_p(base + 8 * n_f64))
+        if n > 1:
+            comm = distributed.comm
+            if comm is None:
+                raise _lib.DgsError("DeviceMetricBuffer.reduce: no NCCL communicator attached to the DistributedContext")
+            # one packed record per rank -> ONE allgather: [b*m f64 values | int64 num_batches | b*m validity bytes]
+            rec = (8 * b * m + 8 + b * m + 7) // 8 * 8
+            send = torch.empty(rec, dtype=torch.uint8, device=self.device)
+            send[: 8 * b * m].view(torch.float64).copy_(self._ring[:b].reshape(-1))
+            send[8 * b * m: 8 * b * m + 8].view(torch.int64).fill_(b)
+            send[8 * b * m + 8: 9 * b * m + 8].copy_(self._valid[:b].reshape(-1))
+            recv = torch.empty(n * rec, dtype=torch.uint8, device=self.device)
+            comm.allgather(send, recv)
+            comm.wait()
+            _lib.calls.dgs_metric_average_packed(_p(recv), rec, n, b, m, *outs, _stream())
+        else:
+            ring, valid = self._ring[:b].contiguous(), self._valid[:b].contiguous()
+            nb = torch.full((1,), b, dtype=torch.int64, device=self.device)
+            _lib.calls.dgs_metric_average(_p(ring), _p(valid), _p(nb), 1, b, m, *outs, _stream())
         raw = block.cpu().numpy()
         host = raw[: 8 * n_f64].view(np.float64)
         counts = raw[8 * n_f64: 8 * n_f64 + 8 * m].view(np.int64).tolist()

@@ -44,29 +44,36 @@ class PyTorchExperimentalContext:
 
 class _BufferSync:
     """DDP's broadcast_buffers=True: before every training forward, rank 0's module buffers (batch-norm
-    running statistics, ...) overwrite every other rank's.  Buffers of one dtype live in one flat
-    tensor so that this is one NCCL broadcast per dtype."""
+    running statistics, ...) overwrite every other rank's.  All buffers live in one flat byte tensor so
+    that this is one NCCL broadcast."""
 
     def __init__(self, model: nn.Module, comm: Comm) -> None:
         self.comm = comm
         self.flats: List[torch.Tensor] = []
-        by_dtype: Dict[torch.dtype, List[Any]] = {}
+        items: List[Any] = []
         seen: Set[int] = set()
         for mod in model.modules():
             for name, buf in list(mod._buffers.items()):
                 if buf is None or id(buf) in seen or not buf.is_cuda:
                     continue
                 seen.add(id(buf))
-                by_dtype.setdefault(buf.dtype, []).append((mod, name, buf))
-        for dtype, items in by_dtype.items():
-            total = sum(b.numel() for _, _, b in items)
-            flat = torch.empty(total, dtype=dtype, device=items[0][2].device)
-            off = 0
-            for mod, name, buf in items:
-                view = flat[off:off + buf.numel()].view(buf.shape)
-                view.copy_(buf)
-                mod._buffers[name] = view
-                off += buf.numel()
+                items.append((mod, name, buf))
+        if items:
+            # one byte buffer for buffers of every dtype (16-byte aligned each): ONE broadcast per forward
+            offs, total = [], 0
+            for _, _, buf in items:
+                offs.append(total)
+                total += (buf.numel() * buf.element_size() + 15) // 16 * 16
+            flat = torch.zeros(total, dtype=torch.uint8, device=items[0][2].device)
+            for (mod, name, buf), off in zip(items, offs):
+                # alias the storage instead of taking a view: views of one tensor share ONE autograd version
+                # counter, and `num_batches_tracked.add_(1)` would then invalidate every running_mean that a
+                # batch-norm layer saved for backward
+                alias = torch.empty(0, dtype=buf.dtype, device=buf.device).set_(
+                    flat.untyped_storage(), off // buf.element_size(), buf.shape, buf.contiguous().stride()
+                )
+                alias.copy_(buf)
+                mod._buffers[name] = alias
             self.flats.append(flat)
         if self.flats:
             self.sync()

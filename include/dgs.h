@@ -206,6 +206,13 @@ int dgs_metric_average(const double* gathered, const uint8_t* valid, const int64
                        int n_ranks, int b, int m, double* per_batch, uint8_t* per_batch_valid,
                        double* avg, int64_t* count, dgs_stream_t stream);
 
+/* Same reduction over PACKED per-rank records, so that one allgather carries everything a rank reports:
+ * record r starts at records + r * record_bytes and holds [ b*m doubles | 1 int64 num_batches | b*m validity
+ * bytes ] (record_bytes a multiple of 8, >= 8*b*m + 8 + b*m). */
+int dgs_metric_average_packed(const void* records, int64_t record_bytes, int n_ranks, int b, int m,
+                              double* per_batch, uint8_t* per_batch_valid, double* avg, int64_t* count,
+                              dgs_stream_t stream);
+
 /* Reducer enum values of H/pytorch/_reducer.py:9-25 */
 #define DGS_REDUCE_AVG 1
 #define DGS_REDUCE_SUM 2

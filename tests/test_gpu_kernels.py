@@ -315,6 +315,39 @@ def host_f64(t):
     return t.detach().cpu().numpy()
 
 
+def test_metric_average_packed_records_equal_separate_arrays(lib):
+    """One allgather of packed per-rank records must reduce exactly like three separate arrays."""
+    rng = np.random.default_rng(9)
+    n_ranks, b, m = 5, 13, 3
+    vals = rng.standard_normal((n_ranks, b, m))
+    valid = (rng.random((n_ranks, b, m)) > 0.3).astype(np.uint8)
+    nb = np.array([b, 0, b, b, b], dtype=np.int64)
+    rec = (8 * b * m + 8 + b * m + 7) // 8 * 8
+    records = np.zeros((n_ranks, rec), dtype=np.uint8)
+    for r in range(n_ranks):
+        records[r, : 8 * b * m] = vals[r].reshape(-1).view(np.uint8)
+        records[r, 8 * b * m: 8 * b * m + 8] = nb[r: r + 1].view(np.uint8)
+        records[r, 8 * b * m + 8: 9 * b * m + 8] = valid[r].reshape(-1)
+    outs = []
+    for packed in (False, True):
+        per_batch = torch.zeros(b, m, dtype=torch.float64, device="cuda")
+        pb_valid = torch.zeros(b, m, dtype=torch.uint8, device="cuda")
+        avg = torch.zeros(m, dtype=torch.float64, device="cuda")
+        count = torch.zeros(m, dtype=torch.int64, device="cuda")
+        if packed:
+            recs = torch.from_numpy(records).cuda()
+            L.calls.dgs_metric_average_packed(ptr(recs), rec, n_ranks, b, m, ptr(per_batch), ptr(pb_valid), ptr(avg), ptr(count), stream())
+        else:
+            g, v, n = torch.from_numpy(vals).cuda(), torch.from_numpy(valid).cuda(), torch.from_numpy(nb).cuda()
+            L.calls.dgs_metric_average(ptr(g), ptr(v), ptr(n), n_ranks, b, m, ptr(per_batch), ptr(pb_valid), ptr(avg), ptr(count), stream())
+        torch.cuda.synchronize()
+        outs.append([t.cpu().numpy() for t in (per_batch, pb_valid, avg, count)])
+    for a, c in zip(*outs):
+        np.testing.assert_array_equal(a, c)
+    with pytest.raises(L.DgsError, match="record_bytes"):
+        L.calls.dgs_metric_average_packed(ptr(recs), 16, n_ranks, b, m, ptr(per_batch), ptr(pb_valid), ptr(avg), ptr(count), stream())
+
+
 def test_metric_reduce_and_pack(lib):
     metrics = np.array([0.25, 0.5, 0.75, 1, 25.5, 1.9])  # reference test_reducer.py:18-29
     weights = np.array([1, 2, 5, 4, 5, 6], dtype=np.int64)

@@ -138,3 +138,72 @@ def test_two_slot_trial_matches_reference(lib, name):
 
     ports = (_free_port(), _free_port())
     mp.spawn(_rank_main, args=(2, name, ports), nprocs=2, join=True)
+
+
+# ---- module buffers (batch norm) under 2 slots: ours vs torch DDP on the same GPUs -------------------------
+class _BnNet(torch.nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.conv = torch.nn.Conv2d(3, 8, 3, padding=1)
+        self.bn = torch.nn.BatchNorm2d(8)
+        self.fc = torch.nn.Linear(8, 4)
+
+    def forward(self, x):
+        return self.fc(torch.relu(self.bn(self.conv(x))).mean(dim=(2, 3)))
+
+
+def _bn_rank_main(rank: int, size: int, ports, init_port: int) -> None:
+    import copy
+
+    import torch.distributed as dist
+
+    from oracle import torch_port
+
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{init_port}", rank=rank, world_size=size,
+                            device_id=torch.device("cuda", rank))
+    dctx = core.DistributedContext(rank=rank, size=size, local_rank=rank, local_size=size, cross_rank=0, cross_size=1,
+                                   pub_port=ports[0], pull_port=ports[1])
+    try:
+        torch.manual_seed(100 + rank)  # DIFFERENT initial weights and buffers per rank: rank 0's must win
+        base = _BnNet()
+        with torch.no_grad():
+            base.bn.running_mean.add_(rank + 1.0)
+        g = torch.Generator().manual_seed(7 + rank)
+        data = [(torch.randn(4, 3, 8, 8, generator=g).cuda(), torch.randn(4, 4, generator=g).cuda()) for _ in range(5)]
+
+        ref = torch_port.RefContext(device=f"cuda:{rank}")
+        ref_model = torch.nn.parallel.DistributedDataParallel(copy.deepcopy(base).cuda())  # reference: _pytorch_context.py:295-296
+        ref.models.append(ref_model)
+        ref_opt = ref.wrap_optimizer(torch.optim.SGD(ref_model.parameters(), lr=0.1, momentum=0.9))
+        ours = pytorch.PyTorchTrialContext(distributed=dctx, hparams={"global_batch_size": 8}, slots_per_trial=size)
+        model = ours.wrap_model(copy.deepcopy(base))
+        opt = ours.wrap_optimizer(torch.optim.SGD(model.parameters(), lr=0.1, momentum=0.9))
+        for i, (x, y) in enumerate(data):
+            for ctx, mdl, o in ((ref, ref_model, ref_opt), (ours, model, opt)):
+                ctx._current_batch_idx = i
+                ctx.backward(torch.nn.functional.mse_loss(mdl(x), y))
+                ctx.step_optimizer(o)
+        torch.cuda.synchronize()
+        for (name, a), b in zip(model.state_dict().items(), ref_model.module.state_dict().values()):
+            if a.dtype.is_floating_point:
+                np.testing.assert_allclose(a.cpu().numpy(), b.cpu().numpy(), rtol=1e-5, atol=1e-6, err_msg=name)
+            else:
+                assert torch.equal(a.cpu(), b.cpu()), name  # num_batches_tracked: integer, exact
+        # every rank ends with identical parameters (rank 0's initial weights were broadcast)
+        flat = torch.cat([p.detach().reshape(-1) for p in model.parameters()])
+        gathered = [torch.empty_like(flat) for _ in range(size)]
+        dist.all_gather(gathered, flat)
+        assert all(torch.equal(gathered[0], t) for t in gathered)
+        ours.close()
+    finally:
+        dctx.close()
+        dist.destroy_process_group()
+
+
+def test_two_slot_buffers_and_initial_broadcast_match_torch_ddp(lib):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run with gpurun --gpus 2)")
+    import torch.multiprocessing as mp
+
+    mp.spawn(_bn_rank_main, args=(2, (_free_port(), _free_port()), _free_port()), nprocs=2, join=True)
