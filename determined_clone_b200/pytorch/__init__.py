@@ -22,3 +22,4 @@ from determined_clone_b200.pytorch._comm import Comm
 from determined_clone_b200.pytorch._gradsync import GradSyncEngine
 from determined_clone_b200.pytorch._pytorch_context import PyTorchExperimentalContext, PyTorchTrialContext
 from determined_clone_b200.pytorch._pytorch_trial import PyTorchTrial, TorchData, _PyTorchTrialController
+from determined_clone_b200.pytorch._trainer import Batch, Epoch, Record, Trainer, TrainUnit, init

@@ -1,0 +1,87 @@
+"""Single-box launch layer and Trainer API: argv construction, experiment-config plumbing, and
+the reference's end-to-end closed-form check run through the same YAML + entrypoint a cluster would use."""
+import json
+import os
+import pathlib
+import shlex
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import yaml
+
+from determined_clone_b200 import _info, pytorch
+from determined_clone_b200.launch import torch_distributed as launch
+from oracle import gradsync_oracle as O
+
+ROOT = pathlib.Path(__file__).resolve().parent.parent
+FIX = ROOT / "tests" / "fixtures" / "pytorch_identity"
+
+
+def test_launch_command_line():
+    # reference harness/tests/launch/test_torch_distributed.py asserts the same torchrun shape
+    cmd = launch.create_launch_cmd(1, 8, 0, "127.0.0.1", ["--rdzv_conf", "x=1"])
+    assert cmd[1:4] == ["-m", "torch.distributed.run", "--nnodes"]
+    assert cmd[cmd.index("--nproc_per_node") + 1] == "8" and cmd[cmd.index("--max_restarts") + 1] == "0"
+    assert cmd[cmd.index("--master_addr") + 1] == "127.0.0.1" and cmd[-2:] == ["--rdzv_conf", "x=1"]
+    assert launch.parse_args(["--a", "1", "--", "python3", "train.py"]) == (["--a", "1"], ["python3", "train.py"])
+    assert launch.parse_args(["python3", "train.py"]) == ([], ["python3", "train.py"])
+
+
+def test_cluster_info_from_experiment_yaml(monkeypatch):
+    monkeypatch.delenv("DET_EXPERIMENT_CONFIG", raising=False)
+    assert _info.get_cluster_info() is None
+    monkeypatch.setenv("DET_EXPERIMENT_CONFIG", str(FIX / "distributed.yaml"))
+    info = _info.get_cluster_info()
+    assert info.trial.hparams == {"global_batch_size": 4, "learning_rate": 0.001}
+    assert len(info.slot_ids) == 2 and info.task_type == "TRIAL"
+    assert info.trial._config["optimizations"]["aggregation_frequency"] == 2
+
+
+def test_train_units():
+    assert pytorch.TrainUnit._from_values(batches=3).value == 3
+    assert isinstance(pytorch.TrainUnit._from_searcher_unit(5, "epochs"), pytorch.Epoch)
+    r = pytorch.TrainUnit._from_searcher_unit(64, "records", 4)
+    assert isinstance(r, pytorch.Record) and r.global_batch_size == 4
+    with pytest.raises(ValueError):
+        pytorch.TrainUnit._from_values(batches=1, epochs=1)
+    ctx = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 4})
+    t = pytorch.Trainer(None, ctx)  # type: ignore
+    assert t._to_batches(pytorch.Batch(7), None) == 7 and t._to_batches(pytorch.Record(64), None) == 16
+    assert t._to_batches(pytorch.Epoch(2), 16) == 32
+    with pytest.raises(ValueError):
+        t._to_batches(pytorch.Epoch(1), None)
+
+
+def _run_experiment(config: str, tmp_path: pathlib.Path) -> list:
+    """Run the experiment's own `entrypoint:` the way a container would, on this box."""
+    conf = yaml.safe_load((FIX / config).read_text())
+    entry = conf["entrypoint"]
+    argv = shlex.split(entry) if " " in entry else ["python3", "-m", "determined.exec.harness", entry]
+    argv = [sys.executable if a == "python3" else a for a in argv]
+    report = tmp_path / "reports.json"
+    env = dict(os.environ, DET_EXPERIMENT_CONFIG=str(FIX / config), DET_REPORT_FILE=str(report),
+               PYTHONPATH=os.pathsep.join([str(ROOT / "determined_clone_b200" / "compat"), str(ROOT), os.environ.get("PYTHONPATH", "")]),
+               C10D_PORT="29433")
+    subprocess.run(argv, cwd=FIX, env=env, check=True, timeout=600)
+    return json.loads(report.read_text())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("config", ["const.yaml", "distributed.yaml"])
+def test_identity_experiment_matches_closed_form(lib, config, tmp_path):
+    """16 batches of y = w*x with aggregation_frequency 2 on 1 slot (global batch 4) and on 2 slots through
+    `determined.launch.torch_distributed`: the weight after every batch equals the reference's closed form
+    (test_pytorch_trial.py:1604-1642), and the chief reports after every batch (scheduling_unit 1)."""
+    import torch
+
+    slots = yaml.safe_load((FIX / config).read_text())["resources"]["slots_per_trial"]
+    if torch.cuda.device_count() < slots:
+        pytest.skip(f"needs {slots} GPUs")
+    reports = _run_experiment(config, tmp_path)
+    assert [r["steps_completed"] for r in reports] == list(range(1, 17))  # integer counters: exact
+    got = [r["batch_metrics"][0]["weight"] for r in reports]
+    want = O.identity_expected_weights()[:16]
+    np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-9)
+    assert got[0] == 0.0 and got[1] == got[2] != 0.0  # no update on non-boundary batches
