@@ -216,9 +216,14 @@ class DeviceMetricBuffer:
     def reduce(self, distributed: core.DistributedContext) -> Tuple[List[Dict[str, Any]], Dict[str, Any], List[int]]:
         """Average over ranks per batch, then over batches.  Returns (per-batch dicts, avg dict,
         per-metric batch counts); identical on every rank.  One device->host copy."""
+        return self.reduce_async(distributed).result()
+
+    def reduce_async(self, distributed: core.DistributedContext) -> "PendingMetrics":
+        """Enqueue the cross-rank reduction and the copy of its result into pinned host memory, and return
+        without waiting: the caller keeps launching the next batches and calls .result() later."""
         b, m = self._rows, len(self.names)
         if b == 0:
-            return [], {}, []
+            return PendingMetrics(None, None, 0, 0, [])
         assert self._ring is not None and self._valid is not None
         n = distributed.size
         # one result block -> one device->host copy: [per_batch b*m f64 | avg m f64 | count m i64 | valid b*m u8]
@@ -245,7 +250,26 @@ class DeviceMetricBuffer:
             ring, valid = self._ring[:b].contiguous(), self._valid[:b].contiguous()
             nb = torch.full((1,), b, dtype=torch.int64, device=self.device)
             _lib.calls.dgs_metric_average(_p(ring), _p(valid), _p(nb), 1, b, m, *outs, _stream())
-        raw = block.cpu().numpy()
+        host = torch.empty(block.numel(), dtype=torch.uint8, pin_memory=True)
+        host.copy_(block, non_blocking=True)
+        done = torch.cuda.Event()
+        done.record(torch.cuda.current_stream())
+        return PendingMetrics(host, done, b, m, list(self.names))
+
+
+class PendingMetrics:
+    """A metric reduction whose result is on its way to pinned host memory."""
+
+    def __init__(self, host: Optional[torch.Tensor], done: Any, b: int, m: int, names: List[str]) -> None:
+        self._host, self._done, self._b, self._m, self._names = host, done, b, m, names
+
+    def result(self) -> Tuple[List[Dict[str, Any]], Dict[str, Any], List[int]]:
+        if self._host is None:
+            return [], {}, []
+        self._done.synchronize()
+        b, m = self._b, self._m
+        n_f64 = b * m + m
+        raw = self._host.numpy()
         host = raw[: 8 * n_f64].view(np.float64)
         counts = raw[8 * n_f64: 8 * n_f64 + 8 * m].view(np.int64).tolist()
         host_valid = raw[8 * n_f64 + 8 * m:].reshape(b, m).astype(bool)
@@ -253,8 +277,8 @@ class DeviceMetricBuffer:
         per_batch: List[Dict[str, Any]] = []
         for i in range(b):
             row: Dict[str, Any] = {}
-            for j, name in enumerate(self.names):
+            for j, name in enumerate(self._names):
                 row[name] = np.array(per_batch_vals[i, j]) if host_valid[i, j] else None
             per_batch.append(row)
-        avg = {name: (float(host[b * m + j]) if counts[j] else None) for j, name in enumerate(self.names)}
+        avg = {name: (float(host[b * m + j]) if counts[j] else None) for j, name in enumerate(self._names)}
         return per_batch, avg, counts

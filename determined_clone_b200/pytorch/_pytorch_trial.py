@@ -124,6 +124,7 @@ class _PyTorchTrialController:
         it = iter(self.training_loader)
         self.context.reset_reducers()
         pending: List[Dict[str, Any]] = []
+        previous: Any = None
         samples = 0
         t0 = time.time()
         while self.batches_trained < self.max_length:
@@ -141,16 +142,40 @@ class _PyTorchTrialController:
                 pending.append(metrics)
             self.batches_trained += 1
             if self.batches_trained % self.reporting_period == 0 or self.batches_trained == self.max_length:
-                report = self._aggregate_training_metrics(pending)
-                dur = time.time() - t0
-                if self.is_chief:
-                    report["samples_per_second"] = samples / dur * self.context.distributed.size if dur > 0 else 0.0
-                    report["steps_completed"] = self.batches_trained
-                    self.reports.append(report)
-                    if self.on_report:
-                        self.on_report(self.batches_trained, report)
+                # the reduction of this period is enqueued now and read one period later (or at the end), so
+                # the host keeps launching batches instead of waiting for the GPU to drain
+                finish = self._begin_report(pending)
+                self._deliver(previous)
+                previous = (finish, self.batches_trained, samples, time.time() - t0)
                 pending, samples, t0 = [], 0, time.time()
                 self.context.reset_reducers()
+        self._deliver(previous)
+
+    def _begin_report(self, training_metrics: List[Dict]) -> Callable[[], Dict]:
+        """Start aggregating the period's metrics; returns the function that completes it."""
+        if len(self._metric_buffer) and not self.context._wrapped_reducers:
+            handle = self._metric_buffer.reduce_async(self.context.distributed)
+            self._metric_buffer.reset()
+
+            def finish() -> Dict:
+                batch_metrics, avg, _ = handle.result()
+                return {"batch_metrics": batch_metrics, "avg_metrics": avg} if self.is_chief else {}
+
+            return finish
+        report = self._aggregate_training_metrics(training_metrics)  # custom reducers / host values: synchronous
+        return lambda: report
+
+    def _deliver(self, previous: Any) -> None:
+        if previous is None:
+            return
+        finish, steps, samples, dur = previous
+        report = finish()
+        if self.is_chief:
+            report["samples_per_second"] = samples / dur * self.context.distributed.size if dur > 0 else 0.0
+            report["steps_completed"] = steps
+            self.reports.append(report)
+            if self.on_report:
+                self.on_report(steps, report)
 
     def _auto_step_lr_scheduler_per_batch(self, batch_idx: int, lr_scheduler: LRScheduler) -> None:
         """Never step the LR when the optimizer did not step; STEP_EVERY_BATCH catches up A steps at the
