@@ -52,7 +52,7 @@ def parse() -> argparse.Namespace:
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-microbench", action="store_true")
     ap.add_argument("--micro-mb", type=int, default=256)
-    ap.add_argument("--workload", default="cifar_resnet18", choices=["cifar_resnet18", "resnet50", "gpt2_medium"],
+    ap.add_argument("--workload", default="cifar_resnet18", choices=["mnist", "cifar_resnet18", "resnet50", "gpt2_medium"],
                     help="cifar_resnet18 = BASELINE.json configs[1] (the default the driver runs); the others are configs[2]/[3]")
     return ap.parse_args()
 

@@ -257,6 +257,41 @@ class DeviceMetricBuffer:
         return PendingMetrics(host, done, b, m, list(self.names))
 
 
+def reduce_validation_on_device(buffer: "DeviceMetricBuffer", distributed: core.DistributedContext,
+                                reducers: Dict[str, Reducer]) -> Dict[str, Any]:
+    """Validation metrics kept on the device: reduce every metric over this rank's batches with its Reducer
+    (dgs_metric_reduce), allgather the per-rank results and batch counts, reduce again over ranks -- AVG weighted
+    by batches per rank, as _reduce_metrics above does on the chief (reference _metric_utils.py:137-176) -- and
+    read the answer back once.  Every rank gets the same dict; non-chief callers drop it."""
+    b, m = len(buffer), len(buffer.names)
+    if b == 0 or m == 0:
+        return {}
+    assert buffer._ring is not None
+    dev, n = buffer.device, distributed.size
+    ring = buffer._ring[:b].contiguous()
+    ops = sorted({reducers[name].value for name in buffer.names})
+    local = torch.empty(len(ops), m, dtype=torch.float64, device=dev)  # one row per reducer kind in use
+    for k, op in enumerate(ops):
+        _lib.calls.dgs_metric_reduce(_p(ring), None, b, m, op, _p(local[k]), _stream())
+    if n > 1:
+        comm = distributed.comm
+        if comm is None:
+            raise _lib.DgsError("reduce_validation_on_device: no NCCL communicator attached to the DistributedContext")
+        send = torch.cat([local.reshape(-1), torch.full((1,), float(b), dtype=torch.float64, device=dev)])
+        recv = torch.empty(n, send.numel(), dtype=torch.float64, device=dev)
+        comm.allgather(send, recv)
+        comm.wait()
+        weights = recv[:, -1].to(torch.int64).contiguous()
+        out = torch.empty(len(ops), m, dtype=torch.float64, device=dev)
+        for k, op in enumerate(ops):
+            vals = recv[:, k * m:(k + 1) * m].contiguous()
+            _lib.calls.dgs_metric_reduce(_p(vals), _p(weights) if op == Reducer.AVG.value else None, n, m, op, _p(out[k]), _stream())
+    else:
+        out = local
+    host = out.cpu().numpy()
+    return {name: np.float64(host[ops.index(reducers[name].value), j]) for j, name in enumerate(buffer.names)}
+
+
 class PendingMetrics:
     """A metric reduction whose result is on its way to pinned host memory."""
 

@@ -256,20 +256,28 @@ class _PyTorchTrialController:
         for model in self.context.models:
             model.eval()
         self.context.reset_reducers()
-        batch_metrics = []
+        batch_metrics: List[Dict[str, Any]] = []
         keys = None
+        device_buf = _metric_utils.DeviceMetricBuffer(self.context.device) if self._device_metrics else None
         for idx, batch in enumerate(self.validation_loader):
             if self.context.experimental._auto_to_device:
                 batch = self.context.to_device(batch)
             vld = self.trial.evaluate_batch(batch=batch, batch_idx=idx)
-            vld = _metric_utils._convert_metrics_to_numpy(vld)
             if keys is None:
                 keys = vld.keys()
-            batch_metrics.append(vld)
+            if device_buf is not None and not batch_metrics and device_buf.accepts(vld) and all(v is not None for v in vld.values()):
+                device_buf.append(vld)  # stays on the GPU (the reference converts every batch: :999)
+                continue
+            if device_buf is not None and len(device_buf):
+                raise RuntimeError("evaluate_batch() must return the same kind of metrics for every batch")
+            batch_metrics.append(_metric_utils._convert_metrics_to_numpy(vld))
         d = self.context.distributed
         keys = d.broadcast(list(keys) if keys is not None else None) if d.size > 1 else keys
         reducers = _metric_utils._prepare_metrics_reducers(self.trial.evaluation_reducer(), keys=keys or [])
-        metrics = _metric_utils._reduce_metrics(d, batch_metrics=batch_metrics, keys=keys, metrics_reducers=reducers)
+        if device_buf is not None and len(device_buf):
+            metrics = _metric_utils.reduce_validation_on_device(device_buf, d, reducers)
+        else:
+            metrics = _metric_utils._reduce_metrics(d, batch_metrics=batch_metrics, keys=keys, metrics_reducers=reducers)
         metrics.update(_metric_utils._convert_metrics_to_numpy(self.context.reduce_metrics(for_training=False)))
         for model in self.context.models:
             model.train()

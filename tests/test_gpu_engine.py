@@ -217,6 +217,33 @@ def test_unmanaged_context_steps_every_batch(lib):
     ours.close()
 
 
+def test_mnist_tutorial_trial_ten_steps_match_reference_path(lib):
+    """BASELINE.json configs[0]: the MNIST tutorial trial, single slot, fixed seed, 10 steps -- here under this
+    repo's context vs the reference's step logic (torch_port.RefContext) on the same GPU, same weights, same
+    batches.  Adadelta is not fused, so this is the flatten -> gradient views -> torch step() route."""
+    from workloads.trials import MnistTrial
+
+    torch.backends.cudnn.deterministic = True
+    gen = torch.Generator().manual_seed(1234)
+    batches = [tuple(t.cuda() for t in MnistTrial.synthetic_batch(64, gen)) for _ in range(10)]
+    results = []
+    for make in (lambda: pytorch.PyTorchTrialContext(hparams={"global_batch_size": 64}, device=torch.device("cuda", 0)),
+                 lambda: torch_port.RefContext(device="cuda:0")):
+        torch.manual_seed(17)
+        ctx = make()
+        trial = MnistTrial(ctx)
+        losses = []
+        for i, b in enumerate(batches):
+            ctx._current_batch_idx = i
+            losses.append(float(trial.train_batch(b, 0, i)["loss"]))
+        results.append((losses, [p.detach().cpu().numpy().copy() for p in trial.model.parameters()]))
+    (l1, p1), (l2, p2) = results
+    np.testing.assert_allclose(l1, l2, rtol=1e-5)
+    for a, b in zip(p1, p2):
+        np.testing.assert_allclose(a, b, rtol=1e-5, atol=1e-5 * float(np.abs(b).max()))
+    torch.backends.cudnn.deterministic = False
+
+
 # ---- size-independent properties at full bucket sizes ---------------------------------------------------
 def _engine(n, dtype, agg, opt_fn):
     p = torch.nn.Parameter(torch.full((n,), 0.5, device="cuda", dtype=dtype))
@@ -269,3 +296,76 @@ def test_full_size_bucket_properties(lib, mb, dtype):
     eng.close()
     del p, opt, eng, g, wire, before
     torch.cuda.empty_cache()
+
+
+class _ValTrial(pytorch.PyTorchTrial):
+    """evaluate_batch returns device scalars; three reducer kinds at once."""
+
+    def __init__(self, context):
+        self.context = context
+        self.model = context.wrap_model(torch.nn.Linear(4, 1))
+        self.opt = context.wrap_optimizer(torch.optim.SGD(self.model.parameters(), lr=0.1))
+        g = torch.Generator().manual_seed(3)
+        self.data = torch.utils.data.TensorDataset(torch.randn(22, 4, generator=g), torch.randn(22, 1, generator=g))
+
+    def build_training_data_loader(self):
+        return pytorch.DataLoader(self.data, batch_size=4)
+
+    def build_validation_data_loader(self):
+        return pytorch.DataLoader(self.data, batch_size=4)  # 6 batches, the last one short
+
+    def train_batch(self, batch, epoch_idx, batch_idx):
+        return {"loss": self.model(batch[0]).mean()}
+
+    def evaluate_batch(self, batch, batch_idx=0):
+        err = (self.model(batch[0]) - batch[1]).abs()
+        return {"mean_err": err.mean(), "max_err": err.max(), "n": torch.tensor(float(len(err)), device=err.device)}
+
+    def evaluation_reducer(self):
+        return {"mean_err": pytorch.Reducer.AVG, "max_err": pytorch.Reducer.MAX, "n": pytorch.Reducer.SUM}
+
+
+def test_validation_metrics_reduced_on_device_match_host_route(lib):
+    outs = []
+    for device_metrics in (True, False):
+        torch.manual_seed(1)
+        ctx = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 4}, device=torch.device("cuda", 0))
+        trial = _ValTrial(ctx)
+        ctl = pytorch._PyTorchTrialController(trial, ctx, max_length=1, device_metrics=device_metrics)
+        ctl._set_data_loaders()
+        outs.append(ctl._validate())
+        ctx.close()
+    dev, host = outs
+    assert set(dev) == set(host) == {"mean_err", "max_err", "n"}
+    assert float(dev["n"]) == float(host["n"]) == 22.0  # a count: exact
+    for k in dev:
+        np.testing.assert_allclose(float(dev[k]), float(host[k]), rtol=1e-6)
+
+
+def test_grad_scaler_route_matches_reference(lib):
+    """AMP with a GradScaler passed to step_optimizer (reference _pytorch_context.py:899-921): the scaler works on
+    the engine's gradient views; the step stays in torch so that inf/nan skipping keeps its semantics."""
+    torch.manual_seed(9)
+    base = Net()
+    data = [(torch.randn(8, 12, device="cuda"), torch.randn(8, 5, device="cuda")) for _ in range(5)]
+    results = []
+    for which in ("ours", "ref"):
+        ours, ref = make_contexts()
+        ctx = ours if which == "ours" else ref
+        model = ctx.wrap_model(copy.deepcopy(base))
+        opt = ctx.wrap_optimizer(torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.9))
+        scaler = torch.amp.GradScaler("cuda", init_scale=1024.0)
+        for i, (x, y) in enumerate(data):
+            ctx._current_batch_idx = i
+            loss = torch.nn.functional.mse_loss(model(x), y)
+            ctx.backward(scaler.scale(loss))
+            if which == "ours":
+                ctx.step_optimizer(opt, scaler=scaler)
+            else:
+                scaler.step(opt)
+                opt.zero_grad()
+            scaler.update()
+        results.append([p.detach().cpu().numpy().copy() for p in model.parameters()])
+        ours.close()
+    for a, b in zip(*results):
+        np.testing.assert_allclose(a, b, rtol=1e-5, atol=1e-7)

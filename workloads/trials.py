@@ -50,6 +50,31 @@ class _VisionTrial:
         return x, y
 
 
+class MnistTrial(_VisionTrial):
+    """configs[0]: the MNIST tutorial trial (reference examples/tutorials/mnist_pytorch/model.py:17-35 and
+    train.py:28-72, hyper-parameters of const.yaml): two 3x3 convolutions, max-pool, two linear layers,
+    NLL loss, Adadelta lr 1.0, batch 64.  Dropout is set to 0 so that runs are comparable across back ends.
+    Adadelta is not one of the fused optimizers: its step() stays in torch on the engine's gradient views."""
+
+    NAME = "mnist_pytorch_tutorial_trial"
+    INPUT_SHAPE = (1, 28, 28)
+    NUM_CLASSES = 10
+    PER_SLOT_BATCH = 64
+    STEP_KERNEL = "torch Adadelta (not fused)"
+    OPTIMIZER = "adadelta lr 1.0"
+
+    def __init__(self, context: Any) -> None:
+        self.context = context
+        n1, n2 = 32, 64
+        net = nn.Sequential(
+            nn.Conv2d(1, n1, 3, 1), nn.ReLU(), nn.Conv2d(n1, n2, 3), nn.ReLU(), nn.MaxPool2d(2), nn.Dropout2d(0.0),
+            nn.Flatten(), nn.Linear(144 * n2, 128), nn.ReLU(), nn.Dropout(0.0), nn.Linear(128, 10), nn.LogSoftmax(dim=1),
+        )
+        self.model = context.wrap_model(net)
+        self.optimizer = context.wrap_optimizer(torch.optim.Adadelta(self.model.parameters(), lr=1.0))
+        self.loss_fn = nn.NLLLoss()
+
+
 class CifarResNetTrial(_VisionTrial):
     """configs[1]: CIFAR-10 ResNet (torchvision resnet18, 10 classes; the reference's
     examples/computer_vision/cifar10_pytorch directory is absent from the snapshot),
@@ -133,4 +158,4 @@ class GPT2MediumTrial:
         return (torch.randint(0, cls.VOCAB, (batch_size, cls.SEQ_LEN), generator=generator),)
 
 
-WORKLOADS = {"cifar_resnet18": CifarResNetTrial, "resnet50": ResNet50Trial, "gpt2_medium": GPT2MediumTrial}
+WORKLOADS = {"mnist": MnistTrial, "cifar_resnet18": CifarResNetTrial, "resnet50": ResNet50Trial, "gpt2_medium": GPT2MediumTrial}
