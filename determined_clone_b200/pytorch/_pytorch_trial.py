@@ -247,6 +247,69 @@ class _PyTorchTrialController:
             return {}
         return metrics
 
+    # ---- checkpoints ----------------------------------------------------------------------------------
+    def _save(self, path: Any) -> None:
+        """Write state_dict.pth + trial_state.pkl with the reference's keys (_pytorch_trial.py:1312-1385), so
+        that checkpoints move between the two harnesses.  Parameters and optimizer state are views of the
+        engine's flat buffers; torch.save stores them as ordinary per-tensor entries."""
+        import pathlib
+        import pickle
+
+        path = pathlib.Path(path)
+        path.mkdir(parents=True, exist_ok=True)
+        rng_state = {
+            "cpu_rng_state": torch.random.get_rng_state(),
+            "np_rng_state": np.random.get_state(),
+            "random_rng_state": random.getstate(),
+        }
+        if torch.cuda.is_available():
+            rng_state["gpu_rng_state"] = torch.cuda.get_rng_state(self.context.device)
+        checkpoint = {
+            "models_state_dict": [{k: v.detach().clone() for k, v in m.state_dict().items()} for m in self.context.models],
+            "optimizers_state_dict": [o.state_dict() for o in self.context.optimizers],
+            "lr_schedulers_state_dict": [s.state_dict() for s in self.context.lr_schedulers],
+            "callbacks": {},
+            "rng_state": rng_state,
+        }
+        if self.context._scaler:
+            checkpoint["scaler_state_dict"] = self.context._scaler.state_dict()
+        torch.save(checkpoint, str(path / "state_dict.pth"))
+        with (path / "trial_state.pkl").open("wb") as f:
+            pickle.dump({"batches_trained": self.batches_trained, "trial_id": 1, "last_ckpt": self.batches_trained}, f)
+
+    def _load(self, path: Any) -> None:
+        """Restore from a checkpoint directory written by _save() or by the reference's _save (incl. DDP-wrapped
+        models whose keys carry a "module." prefix, :1151-1168).  Loaded optimizer state is copied back into the
+        engine's flat buffers on the next step (GradSyncEngine._adopt_state)."""
+        import pathlib
+        import pickle
+
+        path = pathlib.Path(path)
+        checkpoint = torch.load(str(path / "state_dict.pth"), map_location="cpu", weights_only=False)
+        models = checkpoint.get("models_state_dict") or [checkpoint["model_state_dict"]]
+        for model, sd in zip(self.context.models, models):
+            sd = dict(sd)
+            torch.nn.modules.utils.consume_prefix_in_state_dict_if_present(sd, "module.")
+            model.load_state_dict(sd)
+        optimizers = checkpoint.get("optimizers_state_dict") or [checkpoint["optimizer_state_dict"]]
+        for optimizer, sd in zip(self.context.optimizers, optimizers):
+            optimizer.load_state_dict(sd)
+        for sched, sd in zip(self.context.lr_schedulers, checkpoint.get("lr_schedulers_state_dict", [])):
+            sched.load_state_dict(sd)
+        if "scaler_state_dict" in checkpoint and self.context._scaler:
+            self.context._scaler.load_state_dict(checkpoint["scaler_state_dict"])
+        rng = checkpoint.get("rng_state")
+        if rng:
+            torch.random.set_rng_state(rng["cpu_rng_state"])
+            np.random.set_state(rng["np_rng_state"])
+            random.setstate(rng["random_rng_state"])
+            if "gpu_rng_state" in rng and torch.cuda.is_available():
+                torch.cuda.set_rng_state(rng["gpu_rng_state"], self.context.device)
+        state_file = path / "trial_state.pkl"
+        if state_file.exists():
+            with state_file.open("rb") as f:
+                self.batches_trained = int(pickle.load(f).get("batches_trained", self.batches_trained))
+
     # ---- validation ---------------------------------------------------------------------------------
     @torch.no_grad()
     def _validate(self) -> Dict[str, Any]:

@@ -369,3 +369,59 @@ def test_grad_scaler_route_matches_reference(lib):
         ours.close()
     for a, b in zip(*results):
         np.testing.assert_allclose(a, b, rtol=1e-5, atol=1e-7)
+
+
+def test_checkpoint_files_interoperate_with_the_reference_layout(lib, tmp_path):
+    """state_dict.pth written here loads into plain torch objects (what the reference's _load does), and a
+    checkpoint in the reference's layout -- DDP-prefixed model keys, torch.optim state -- loads here and training
+    continues exactly as plain torch continues from it."""
+    torch.manual_seed(4)
+    base = Net()
+    data = [(torch.randn(8, 12, device="cuda"), torch.randn(8, 5, device="cuda")) for _ in range(8)]
+
+    def train(ctx, model, opt, rng):
+        for i in rng:
+            ctx._current_batch_idx = i
+            ctx.backward(torch.nn.functional.mse_loss(model(data[i][0]), data[i][1]))
+            ctx.step_optimizer(opt)
+
+    # (1) reference-side: plain torch trains 4 batches and saves with the reference's keys, DDP-style names
+    ref = torch_port.RefContext(device="cuda:0")
+    rmodel = ref.wrap_model(copy.deepcopy(base))
+    ropt = ref.wrap_optimizer(torch.optim.AdamW(rmodel.parameters(), lr=1e-2, weight_decay=0.1))
+    train(ref, rmodel, ropt, range(4))
+    ckpt = tmp_path / "from_reference"
+    ckpt.mkdir()
+    torch.save({"models_state_dict": [{"module." + k: v for k, v in rmodel.state_dict().items()}],
+                "optimizers_state_dict": [ropt.state_dict()], "lr_schedulers_state_dict": [], "callbacks": {},
+                "rng_state": {"cpu_rng_state": torch.random.get_rng_state(), "np_rng_state": np.random.get_state(),
+                              "random_rng_state": __import__("random").getstate()}}, ckpt / "state_dict.pth")
+    train(ref, rmodel, ropt, range(4, 8))  # the reference continues
+
+    # (2) ours: load that checkpoint into a fresh trial and continue
+    ours = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 8}, device=torch.device("cuda", 0))
+    model = ours.wrap_model(Net())
+    opt = ours.wrap_optimizer(torch.optim.AdamW(model.parameters(), lr=1e-2, weight_decay=0.1))
+    ctl = pytorch._PyTorchTrialController(None, ours, max_length=0)  # type: ignore
+    ctl._load(ckpt)
+    train(ours, model, opt, range(4, 8))
+    for a, b in zip(model.parameters(), rmodel.parameters()):
+        np.testing.assert_allclose(a.detach().cpu().numpy(), b.detach().cpu().numpy(), rtol=1e-5, atol=1e-7)
+    assert float(opt.state[model.a.weight]["step"]) == 8.0
+
+    # (3) ours saves; plain torch loads and agrees
+    ctl.batches_trained = 8
+    ctl._save(tmp_path / "from_ours")
+    saved = torch.load(tmp_path / "from_ours" / "state_dict.pth", weights_only=False)
+    assert set(saved) >= {"models_state_dict", "optimizers_state_dict", "lr_schedulers_state_dict", "rng_state"}
+    fresh = Net().cuda()
+    fresh.load_state_dict(saved["models_state_dict"][0])
+    fopt = torch.optim.AdamW(fresh.parameters(), lr=1e-2, weight_decay=0.1)
+    fopt.load_state_dict(saved["optimizers_state_dict"][0])
+    for a, b in zip(fresh.parameters(), rmodel.parameters()):
+        np.testing.assert_allclose(a.detach().cpu().numpy(), b.detach().cpu().numpy(), rtol=1e-5, atol=1e-7)
+    np.testing.assert_allclose(fopt.state[fresh.a.weight]["exp_avg"].cpu().numpy(), ropt.state[rmodel.a.weight]["exp_avg"].cpu().numpy(), rtol=1e-5, atol=1e-9)
+    ctl2 = pytorch._PyTorchTrialController(None, ours, max_length=0)  # type: ignore
+    ctl2._load(tmp_path / "from_ours")
+    assert ctl2.batches_trained == 8  # integer: exact
+    ours.close()
