@@ -66,7 +66,7 @@ def measured_peaks() -> Tuple[float, str]:
 
 # ---- clocks ---------------------------------------------------------------------------------------
 class ClockSampler:
-    """Samples SM clock and throttle reasons of one GPU every 100 ms while the timed region runs."""
+    """Samples SM clock and throttle reasons of one GPU every 20 ms while the timed region runs."""
 
     def __init__(self, index: int) -> None:
         self.index, self.samples, self.reasons = index, [], set()
@@ -104,7 +104,7 @@ class ClockSampler:
                         self.reasons.add(k)
             except Exception:
                 pass
-            self._stop.wait(0.1)
+            self._stop.wait(0.02)
 
     def __enter__(self) -> "ClockSampler":
         if self._nv is not None:

@@ -103,3 +103,59 @@ def test_bf16_round_matches_torch():
     x[:4] = [0.0, -0.0, 1.00390625, 3.3895314e38]
     want = torch.from_numpy(x).to(torch.bfloat16).float().numpy()
     np.testing.assert_array_equal(O.bf16_round(x), want)
+
+
+@pytest.mark.parametrize("name", [n for n, sc in SCENARIOS.items() if sc["slots"] == 1])
+def test_torch_port_reproduces_reference_run(name):
+    """oracle/torch_port.py (the timed CPU baseline: the reference's step_optimizer lines over torch) is pinned
+    too: driven with the fixtures' initial weights and data it must retrace the real reference harness's
+    single-slot runs -- losses, synchronized gradients, total norms and parameters after every optimizer step."""
+    import torch
+
+    from golden_model import GoldenNet, make_data, make_optimizer
+    from oracle import torch_port
+
+    g = Golden(name)
+    torch.set_num_threads(1)
+    dtype = getattr(torch, g.dtype)
+    model = GoldenNet().to(dtype)
+    with torch.no_grad():
+        for p, init in zip(model.parameters(), g.init_params()):
+            p.copy_(torch.from_numpy(init).to(dtype))
+    ctx = torch_port.RefContext(aggregation_frequency=g.agg, hparams=g.hp)
+    model = ctx.wrap_model(model)
+    opt = ctx.wrap_optimizer(make_optimizer(model, g.hp))
+    x, y = make_data(g.steps * g.agg, g.hp["global_batch_size"])
+    x, y = x.to(dtype), y.to(dtype)
+    bs = ctx.get_per_slot_batch_size()
+    seen = {"avg": [], "norm": []}
+
+    def clip(params):
+        params = list(params)
+        seen["avg"].append([p.grad.detach().float().numpy().copy() for p in params])
+        if g.clip is not None:
+            kind, val = g.clip
+            if kind == "norm":
+                seen["norm"].append(float(torch.nn.utils.clip_grad_norm_(params, val)))
+            else:
+                torch.nn.utils.clip_grad_value_(params, val)
+
+    tight = dict(rtol=1e-6, atol=1e-8) if g.dtype == "float32" else dict(rtol=1e-2, atol=1e-3)
+    for i in range(g.steps * g.agg):
+        ctx._current_batch_idx = i
+        xb, yb = x[i * bs:(i + 1) * bs], y[i * bs:(i + 1) * bs]
+        loss = torch.nn.functional.mse_loss(model(xb).float(), yb.float())
+        np.testing.assert_allclose(float(loss), g.loss(0)[i], **tight)
+        ctx.backward(loss)
+        ctx.step_optimizer(opt, clip_grads=clip)
+        if (i + 1) % g.agg == 0:
+            s = (i + 1) // g.agg - 1
+            for p, want in zip(model.parameters(), g.per_step("params", s)):
+                np.testing.assert_allclose(p.detach().float().numpy(), want, **tight)
+    opt_order = [0, 4, 1, 2, 3, 5]
+    for s in range(g.steps):
+        want = g.per_step("avg_grads", s)
+        for j, i in enumerate(opt_order):
+            np.testing.assert_allclose(seen["avg"][s][j], want[i], **tight)
+    if g.clip is not None and g.clip[0] == "norm":
+        np.testing.assert_allclose(seen["norm"], g.z["total_norm"], **tight)
