@@ -115,6 +115,7 @@ class _FlatSet:
         self.dtype_code = self.wire_code = 0
         self.acc_ptr: Any = None
         self.wire_ptr: Any = None
+        self.segs_all: Any = None  # prebuilt dgs_seg[len(tensors)] for whole-set launches (single GPU)
         self.group_runs: Optional[List[Tuple[int, int, int, List[_Tensor]]]] = None
         self.steady = False  # last step covered every parameter and left every state tensor as our view
         self.uniform_step: Optional[int] = None  # Adam: the common step count while all parameters move together
@@ -169,6 +170,7 @@ class GradSyncEngine:
         self._eager_unused = 0
         self._norm_slots_valid = True
         self._norm_requested = False
+        self._wire_versions: List[int] = []
         self._launch_order: List[Tuple[int, int]] = []
         self._pending_order: Optional[List[Tuple[int, int]]] = None
         self._next_launch = 0
@@ -230,6 +232,9 @@ class GradSyncEngine:
             self._cut_buckets(fs)
             fs.dtype_code, fs.wire_code = _lib.dtype_code(fs.dtype), _lib.dtype_code(fs.wire_dtype)
             fs.acc_ptr, fs.wire_ptr = _ptr(fs.acc), _ptr(fs.wire)
+            fs.segs_all = (_lib.Seg * len(fs.tensors))()
+            for k, t in enumerate(fs.tensors):
+                fs.segs_all[k].dst_off, fs.segs_all[k].numel = t.off, t.numel
         # norm scratch: [whole-buffer partials of every set | per-bucket partials of every set]
         n_partials = sum(_lib.calls.dgs_l2norm_grid(fs.total) for fs in self.sets)
         self._bucket_partials_base = n_partials
@@ -304,6 +309,8 @@ class GradSyncEngine:
     def end_pass(self) -> None:
         """Called right after loss.backward(): flatten whatever the hooks have not taken yet."""
         for si, fs in enumerate(self.sets):
+            if self.comm is None and self._flush_whole_set(fs):
+                continue
             for bi, b in enumerate(fs.buckets):
                 grads = self._collect(fs, b)
                 if grads:
@@ -311,6 +318,41 @@ class GradSyncEngine:
         if self._sentinels is None and self._hooks:
             self._finish_learning()
         self._in_pass = self._final_pass = False
+
+    def _flush_whole_set(self, fs: _FlatSet) -> bool:
+        """Single GPU, the usual case (every parameter has a gradient, all in the same accumulation state):
+        one call for the whole flat set instead of one per bucket -- buckets only exist to pipeline
+        communication.  Returns False, having touched nothing, when the case does not apply."""
+        tensors, in_window = fs.tensors, fs.in_window
+        state = in_window[0]
+        for t in tensors:
+            g = t.param.grad
+            if g is None or g.dtype != fs.dtype or g.is_sparse or not g.is_contiguous() or in_window[t.index] != state:
+                return False
+        if any(b.flushed for b in fs.buckets):
+            return False
+        to_wire = self._final_pass
+        if not to_wire and fs.acc is None:
+            fs.acc = torch.zeros(fs.total, dtype=torch.float32, device=self.device)
+            fs.acc_ptr = _ptr(fs.acc)
+        segs = fs.segs_all
+        keep = []
+        for k, t in enumerate(tensors):
+            g = t.param.grad
+            t.param.grad = None
+            keep.append(g)
+            segs[k].src = g.data_ptr()
+        mode = (_lib.READ_ACC if state else 0) | (_lib.WRITE_WIRE if to_wire else 0)
+        _lib.calls.dgs_flatten_accumulate(segs, len(tensors), fs.dtype_code, fs.acc_ptr, fs.wire_ptr, fs.wire_code, mode,
+                                          self.scale, _stream())
+        flags = fs.in_wire if to_wire else fs.in_window
+        for i in range(len(tensors)):
+            flags[i] = True
+        if to_wire:
+            for b in fs.buckets:
+                b.flushed = True
+            self._reduce_ready()
+        return True
 
     def _learn_order(self, p: torch.nn.Parameter) -> None:
         self._order.append(self._where[id(p)])
@@ -492,13 +534,18 @@ class GradSyncEngine:
             present.append(have)
         if self.comm is not None:
             self.comm.wait()
+        # in-place edits of the gradient views by user code (clip_grad_value_, manual scaling, ...) bump the
+        # wire tensors' autograd version; the kernels never do.  total_norm() uses it to notice stale partials.
+        self._wire_versions = [fs.wire._version for fs in self.sets]
         return present
 
     def total_norm(self) -> torch.Tensor:
         """Global L2 norm of the synchronized gradients, left on the device (fp32 scalar).  Call after
         finish_window()."""
         stream = _stream()
-        if self.comm is not None and self._eager_norm and self._norm_slots_valid and all(b.norm_done for fs in self.sets for b in fs.buckets):
+        untouched = self._wire_versions == [fs.wire._version for fs in self.sets]
+        if (self.comm is not None and self._eager_norm and self._norm_slots_valid and untouched
+                and all(b.norm_done for fs in self.sets for b in fs.buckets)):
             # pass 1 already ran bucket by bucket behind the allreduces: only the final reduction is left
             n = self._partials.numel() - self._bucket_partials_base
             _lib.calls.dgs_l2norm_final(_ptr(self._partials, 4 * self._bucket_partials_base), n, _ptr(self._norm), stream)

@@ -156,6 +156,7 @@ class PyTorchTrialContext(_PyTorchReducerContext):
 
         # grad-sync state
         self._engines: Dict[torch.optim.Optimizer, _gradsync.GradSyncEngine] = {}
+        self._owned_params: Set[int] = set()
         self._buffer_syncs: List[_BufferSync] = []
         self._backward_calls = 0
         self._backward_calls_batch: Optional[int] = None
@@ -266,6 +267,13 @@ class PyTorchTrialContext(_PyTorchReducerContext):
         self._optimizer_configs[optimizer] = {"average_aggregated_gradients": average_aggregated_gradients}
         if optimizer in self._engines:
             raise errors.InvalidExperimentException("wrap_optimizer() was called twice on the same optimizer")
+        mine = {id(p) for g in optimizer.param_groups for p in g["params"]}
+        if mine & self._owned_params:
+            raise errors.InvalidExperimentException(
+                "a parameter belongs to two wrapped optimizers; each parameter's gradient and state can live in "
+                "only one optimizer's flat buffers"
+            )
+        self._owned_params |= mine
         if True:  # managed or not (Trainer / Core API use): the same engine carries the step
             self._engines[optimizer] = _gradsync.GradSyncEngine(
                 optimizer,

@@ -425,3 +425,26 @@ def test_checkpoint_files_interoperate_with_the_reference_layout(lib, tmp_path):
     ctl2._load(tmp_path / "from_ours")
     assert ctl2.batches_trained == 8  # integer: exact
     ours.close()
+
+
+def test_fp16_wire_compression(lib):
+    """optimizations.gradient_compression (Horovod's Compression.fp16, reference _pytorch_context.py:357-366):
+    fp32 gradients travel as fp16; the fused step reads the fp16 wire directly.  Checked against torch stepping
+    on the same fp16-rounded averaged gradients."""
+    torch.manual_seed(2)
+    n = 10000
+    p = torch.nn.Parameter(torch.randn(n, device="cuda"))
+    q = torch.nn.Parameter(p.detach().clone())
+    opt = torch.optim.SGD([p], lr=0.1, momentum=0.9, weight_decay=1e-3)
+    ref = torch.optim.SGD([q], lr=0.1, momentum=0.9, weight_decay=1e-3)
+    eng = pytorch.GradSyncEngine(opt, torch.device("cuda", 0), None, aggregation_frequency=2, average_aggregated_gradients=True,
+                                 fp16_compression=True)
+    assert eng.sets[0].wire.dtype == torch.float16
+    for step in range(4):
+        g1, g2 = torch.randn(n, device="cuda") * 0.1, torch.randn(n, device="cuda") * 0.1
+        _window(eng, p, [g1.clone(), g2.clone()])
+        q.grad = ((g1 + g2) * 0.5).half().float()
+        ref.step()
+        torch.cuda.synchronize()
+        np.testing.assert_allclose(p.detach().cpu().numpy(), q.detach().cpu().numpy(), rtol=2e-6, atol=1e-7)
+    eng.close()
