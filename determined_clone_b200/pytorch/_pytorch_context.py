@@ -197,6 +197,31 @@ class PyTorchTrialContext(_PyTorchReducerContext):
             )
         return self.get_hparams()[name]
 
+    def get_experiment_config(self) -> Dict[str, Any]:
+        if self._exp_conf is None:
+            raise ValueError("exp_conf must be passed to the context (or pytorch.init()) to use get_experiment_config()")
+        return self._exp_conf
+
+    def get_data_config(self) -> Dict[str, Any]:
+        return (self._exp_conf or {}).get("data", {})
+
+    def get_trial_seed(self) -> int:
+        if self._trial_seed is None:
+            raise ValueError("trial_seed was not set for this context")
+        return self._trial_seed
+
+    def get_initial_batch(self) -> int:
+        return self._steps_completed
+
+    def get_enable_tensorboard_logging(self) -> bool:
+        return False  # TensorBoard upload belongs to the control plane; metrics go to on_report
+
+    def configure_apex_amp(self, *args: Any, **kwargs: Any) -> Any:
+        # deprecated in the reference (_pytorch_context.py:635-640) and apex is not installed here
+        raise errors.InvalidExperimentException(
+            "apex.amp is not supported on this path; use torch.amp (autocast + GradScaler via wrap_scaler())"
+        )
+
     def get_per_slot_batch_size(self) -> int:
         if self._per_slot_batch_size is None:
             raise ValueError("global_batch_size not specified in the hyperparameters")

@@ -74,10 +74,12 @@ class _PyTorchTrialController:
         on_report: Optional[Callable[[int, Dict[str, Any]], None]] = None,
         steps_completed: int = 0,
         device_metrics: bool = True,
+        test_mode: bool = False,
     ) -> None:
         self.trial = trial_inst
         self.context = context
-        self.max_length = max_length
+        # test_mode trains exactly one batch (reference _pytorch_trial.py:742-743,755-756)
+        self.max_length = steps_completed + 1 if test_mode else max_length
         self.reporting_period = reporting_period
         self.on_report = on_report
         self.batches_trained = steps_completed
