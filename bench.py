@@ -13,8 +13,9 @@ context.step_optimizer (fused step kernel).
   value  device-timed: inputs already resident in HBM, CUDA events around exactly K steps, max over ranks
   e2e    the same trial driven through the public API (_PyTorchTrialController.run): every step copies
          its batch from pinned host memory and reads the step's metrics back to the host
-  roofline  the fused optimizer kernel (largest HBM mover of the path), CUDA events around each launch
-            inside the timed region; algorithmic bytes per element as stated in DESIGN.md
+  roofline  the fused optimizer kernel (largest HBM mover of the path), CUDA events recorded inside libdgs
+            immediately around each launch (dgs_timer_*) during the timed region, on the launching stream;
+            algorithmic bytes per element as stated in DESIGN.md
   gradsync_microbench  BASELINE.json configs[4]: one flat 256 MiB fp32 bucket, accumulate + allreduce +
             clip + AdamW, time per step against max(HBM, NVLink) roofline
   cpu_baseline  (N=1, rank 0) the torch port of the reference's path on the host cores, bounded sample
@@ -399,8 +400,8 @@ def run_ours(args: argparse.Namespace) -> None:
         roofline = {"bound": "hbm", "kernel": CifarResNetTrial.STEP_KERNEL, "achieved": achieved, "peak": peak, "unit": "GB/s",
                     "frac": achieved / peak, "traffic": NCU_TRAFFIC_BYTES if args.workload == "cifar_resnet18" else None, "peak_source": peak_src, "elements": p_total,
                     "algorithmic_bytes_per_element": bytes_per_elem, "us_per_launch": k_ms * 1e3,
-                    "note": "events recorded immediately around the launch; for models smaller than L2 the wire bucket just written by "
-                            "the flatten kernels is partly still cached"}
+                    "note": "median over the timed region of CUDA events recorded inside libdgs around each launch (dgs_timer_read); for "
+                            "models smaller than L2 the wire bucket just written by the flatten kernel is partly still cached"}
 
     micro = None
     if not args.no_microbench:

@@ -18,6 +18,9 @@ extern std::atomic<int64_t> g_launches;
 int sm_count();  // SMs of the current device (148 on B200), cached per device
 // Upper bound on the grid of a streaming kernel, in CTAs per SM (env DGS_GRID_MULT overrides, for tuning).
 int grid_mult();
+// Optional CUDA-event bracket around a kernel launch (dgs_timer_enable); no-ops when timing is off.
+void timer_begin(cudaStream_t st);
+void timer_end(cudaStream_t st);
 
 #define DGS_CHECK_ARG(cond, ...)                     \
   do {                                               \

@@ -230,7 +230,9 @@ int launch_adam_u(void* param, void* ea, void* eas, const void* grad, int64_t n,
                   const float* tn, float max_norm, cudaStream_t st) {
   const long long tiles = (n + StepCfg<P, G, U>::TILE - 1) / StepCfg<P, G, U>::TILE;
   const int grid = tile_grid(tiles);
+  timer_begin(st);
   adam_kernel<P, G, U><<<grid, kThreads, 0, st>>>((P*)param, (P*)ea, (P*)eas, (const G*)grad, n, T, tn, max_norm);
+  timer_end(st);
   DGS_LAUNCHED();
   return DGS_OK;
 }
@@ -249,11 +251,13 @@ int launch_sgd_u(void* param, void* buf, const void* grad, int64_t n, const Tabl
                  const float* tn, float max_norm, cudaStream_t st) {
   const long long tiles = (n + StepCfg<P, G, U>::TILE - 1) / StepCfg<P, G, U>::TILE;
   const int grid = tile_grid(tiles);
+  timer_begin(st);
   if (buf != nullptr) {
     sgd_kernel<P, G, true, U><<<grid, kThreads, 0, st>>>((P*)param, (P*)buf, (const G*)grad, n, T, tn, max_norm);
   } else {
     sgd_kernel<P, G, false, U><<<grid, kThreads, 0, st>>>((P*)param, nullptr, (const G*)grad, n, T, tn, max_norm);
   }
+  timer_end(st);
   DGS_LAUNCHED();
   return DGS_OK;
 }

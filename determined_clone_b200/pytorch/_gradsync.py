@@ -162,7 +162,6 @@ class GradSyncEngine:
         self._step_views: List[torch.Tensor] = []
         self._fused_kind = self._classify(optimizer)
         self.last_total_norm: Optional[torch.Tensor] = None
-        self._timing: Optional[List[Tuple[torch.cuda.Event, torch.cuda.Event]]] = None
         # Several GPUs: norm pass 1 is run per bucket right behind the bucket's allreduce (aux stream, bucket still
         # in L2) once a clip_grad_norm_ request has been seen; switched off again if nobody asks for the norm.
         # One GPU: a single pass over the whole buffer at step time (fewer launches, nothing to hide behind).
@@ -641,14 +640,17 @@ class GradSyncEngine:
 
     # -- measurement: CUDA events around the optimizer kernel, on the stream it is launched on ----------
     def enable_step_timing(self, on: bool = True) -> None:
-        self._timing = [] if on else None
+        """CUDA events recorded inside libdgs immediately around every optimizer-kernel launch."""
+        _lib.calls.dgs_timer_enable(1 if on else 0)
+        if on:
+            self.step_timings_ms()  # drop anything logged earlier
 
     def step_timings_ms(self) -> List[float]:
-        """Durations of the fused step launches since enable_step_timing(); synchronizes."""
-        if not self._timing:
-            return []
-        self._timing[-1][1].synchronize()
-        return [a.elapsed_time(b) for a, b in self._timing]
+        """Durations (ms) of the optimizer-kernel launches since the last call; synchronizes with the last one."""
+        buf = (ctypes.c_float * 1024)()
+        n = ctypes.c_int(0)
+        _lib.calls.dgs_timer_read(buf, 1024, ctypes.byref(n))
+        return [buf[i] / 1000.0 for i in range(n.value)]
 
     def fused_step(self, present: List[List[bool]], clip: Optional[ClipRequest]) -> None:
         """clip + optimizer.step() in one kernel per flat set (several if there are > 24 ranges)."""
@@ -656,17 +658,7 @@ class GradSyncEngine:
         self._fused_step(present, clip)
 
     def _launch_step(self, fn: Any, *args: Any) -> None:
-        """Launch one optimizer kernel; with timing on, CUDA events are recorded immediately around the
-        launch call on the launching stream."""
-        if self._timing is None:
-            fn(*args)
-            return
-        st = torch.cuda.current_stream()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record(st)
         fn(*args)
-        b.record(st)
-        self._timing.append((a, b))
 
     def _fused_step(self, present: List[List[bool]], clip: Optional[ClipRequest]) -> None:
         norm_ptr, max_norm = None, 0.0

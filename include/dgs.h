@@ -179,6 +179,15 @@ int dgs_step_sgd(void* param, void* momentum_buf, int state_dtype, const void* g
                  int64_t n, const dgs_sgd_range* ranges, int n_ranges, const float* total_norm,
                  float max_norm, dgs_stream_t stream);
 
+/* Device-side timing of the optimizer kernels (grad-sync us/step without host noise): while enabled, every
+ * dgs_step_adam / dgs_step_sgd launch is bracketed by CUDA events recorded inside the call, on the stream it
+ * is launched on.  dgs_timer_read synchronises with the last recorded launch, writes the elapsed microseconds
+ * of up to `capacity` launches since the previous read (oldest first) and clears the log (at most 1024 are kept).
+ * No reference counterpart: the reference times regions with host clocks
+ * (H/profiler.py:487-506 record_timing, optionally after torch.cuda.synchronize). */
+int dgs_timer_enable(int enabled);
+int dgs_timer_read(float* us_out, int capacity, int* n_out);
+
 /* ------------------------------------------------------------------------------------------------
  * 4. metric reducer
  *

@@ -377,3 +377,26 @@ def test_metric_reduce_and_pack(lib):
     torch.cuda.synchronize()
     assert row.tolist() == [1.5, 2.25, 7.0, 0.0, -3.0]
     assert vrow.tolist() == [1, 1, 1, 0, 1]
+
+
+def test_step_kernel_timer(lib):
+    n = 1 << 20
+    p, b, g = (torch.zeros(n, device="cuda") for _ in range(3))
+    specs = [dict(begin=0, end=n, lr=0.1, momentum=0.9, weight_decay=0.0)]
+    out = (ctypes.c_float * 16)()
+    cnt = ctypes.c_int(-1)
+    L.calls.dgs_timer_enable(0)
+    L.calls.dgs_timer_read(out, 16, ctypes.byref(cnt))  # clear
+    L.calls.dgs_step_sgd(ptr(p), ptr(b), L.F32, ptr(g), L.F32, n, sgd_ranges(specs), 1, None, 0.0, stream())
+    L.calls.dgs_timer_read(out, 16, ctypes.byref(cnt))
+    assert cnt.value == 0  # nothing is recorded while timing is off
+    L.calls.dgs_timer_enable(1)
+    for _ in range(3):
+        L.calls.dgs_step_sgd(ptr(p), ptr(b), L.F32, ptr(g), L.F32, n, sgd_ranges(specs), 1, None, 0.0, stream())
+    L.calls.dgs_timer_read(out, 16, ctypes.byref(cnt))
+    L.calls.dgs_timer_enable(0)
+    assert cnt.value == 3
+    # 20 MB of traffic: a few microseconds, certainly under a millisecond
+    assert all(1.0 < out[i] < 1000.0 for i in range(3)), list(out)[:3]
+    L.calls.dgs_timer_read(out, 16, ctypes.byref(cnt))
+    assert cnt.value == 0  # reading clears the log
