@@ -188,7 +188,7 @@ def _free_port() -> int:
         return s.getsockname()[1]
 
 
-def gradsync_microbench(ctx: Any, mb: int, steps: int, peak_gbs: float) -> Dict[str, Any]:
+def gradsync_microbench(ctx: Any, mb: int, steps: int, peak_gbs: float, sharded: bool = False) -> Dict[str, Any]:
     """configs[4]: one flat fp32 bucket through the path: flatten*scale -> allreduce -> L2 norm -> clip+AdamW."""
     import torch
 
@@ -200,7 +200,8 @@ def gradsync_microbench(ctx: Any, mb: int, steps: int, peak_gbs: float) -> Dict[
     world = ctx.distributed.size
     params = [torch.nn.Parameter(torch.randn(n_piece, device=ctx.device) * 0.02) for _ in range(pieces)]
     opt = torch.optim.AdamW(params, lr=3e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
-    eng = pytorch.GradSyncEngine(opt, ctx.device, ctx._get_comm(), aggregation_frequency=1, average_aggregated_gradients=True)
+    eng = pytorch.GradSyncEngine(opt, ctx.device, ctx._get_comm(), aggregation_frequency=1, average_aggregated_gradients=True,
+                                 sharded_step=sharded)
     grads = [[torch.randn(n_piece, device=ctx.device) * 1e-2 for _ in range(pieces)] for _ in range(2)]
     clip = pytorch._gradsync.ClipRequest()
     clip.max_norm = 1.0
@@ -236,7 +237,7 @@ def gradsync_microbench(ctx: Any, mb: int, steps: int, peak_gbs: float) -> Dict[
     t_hbm = hbm_bytes / (peak_gbs * 1e9)
     t_nvl = (2 * (world - 1) / world * 4 * n) / 770e9 if world > 1 else 0.0  # measured peer bandwidth per direction
     eng.close()
-    return {"bucket_mib": mb, "dtype": "f32", "optimizer": "adamw", "aggregation_frequency": 1, "clip": 1.0,
+    return {"bucket_mib": mb, "dtype": "f32", "optimizer": "adamw", "aggregation_frequency": 1, "clip": 1.0, "sharded_step": eng.sharded,
             "us_per_step": ms * 1e3, "hbm_bytes_per_step": hbm_bytes, "roofline_us": max(t_hbm, t_nvl) * 1e6,
             "frac_of_roofline": max(t_hbm, t_nvl) / (ms * 1e-3), "bound": "nvlink" if t_nvl > t_hbm else "hbm"}
 
@@ -406,6 +407,8 @@ def run_ours(args: argparse.Namespace) -> None:
     micro = None
     if not args.no_microbench:
         micro = gradsync_microbench(ctx, args.micro_mb, 20, peak)
+        if world > 1:  # the opt-in reduce-scatter / sharded-step / all-gather variant of the same step
+            micro["sharded_variant"] = gradsync_microbench(ctx, args.micro_mb, 20, peak, sharded=True)
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:

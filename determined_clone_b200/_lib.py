@@ -71,6 +71,8 @@ SIGNATURES = {
     "dgs_l2norm_grid": [_i64],
     "dgs_l2norm_partial": [_vp, _i, _i64, _vp, _vp],
     "dgs_l2norm_final": [_vp, _i, _vp, _vp],
+    "dgs_l2norm_final_sumsq": [_vp, _i, _vp, _vp],
+    "dgs_sqrt_inplace": [_vp, _vp],
     "dgs_l2norm": [_vp, _i, _i64, _vp, _vp, _vp],
     "dgs_l2norm_noalloc": [_vp, _i, _i64, _vp, _vp],
     "dgs_clip_scale": [_vp, _i, _i64, _vp, _f, _vp],
@@ -87,6 +89,7 @@ SIGNATURES = {
     "dgs_comm_destroy": [_vp],
     "dgs_comm_rank": [_vp, ctypes.POINTER(_i), ctypes.POINTER(_i)],
     "dgs_comm_allreduce_async": [_vp, _vp, _i64, _i, _vp],
+    "dgs_comm_reduce_scatter_async": [_vp, _vp, _i64, _i, _vp],
     "dgs_comm_broadcast_async": [_vp, _vp, _i64, _i, _vp],
     "dgs_comm_allgather_async": [_vp, _vp, _vp, _i64, _vp],
     "dgs_comm_l2norm_partial_async": [_vp, _vp, _i, _i64, _vp],

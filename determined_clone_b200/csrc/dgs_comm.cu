@@ -42,6 +42,7 @@ struct NcclApi {
   ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*ReduceScatter)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
   const char* (*GetErrorString)(ncclResult_t) = nullptr;
   const char* (*GetLastError)(ncclComm_t) = nullptr;
   char why[256] = {0};
@@ -75,6 +76,7 @@ NcclApi* nccl() {
     DGS_SYM(AllReduce, "ncclAllReduce")
     DGS_SYM(Broadcast, "ncclBroadcast")
     DGS_SYM(AllGather, "ncclAllGather")
+    DGS_SYM(ReduceScatter, "ncclReduceScatter")
     DGS_SYM(GetErrorString, "ncclGetErrorString")
     DGS_SYM(GetLastError, "ncclGetLastError")
 #undef DGS_SYM
@@ -199,6 +201,22 @@ extern "C" int dgs_comm_allreduce_async(dgs_comm* c, void* buf, int64_t count, i
   NcclApi* api = nccl();
   if (int rc = fence_in(c, static_cast<cudaStream_t>(compute))) return rc;
   DGS_NCCL(api, c->comm, api->AllReduce(buf, buf, (size_t)count, dt, ncclSum, c->comm, c->side));
+  return mark_out(c);
+}
+
+extern "C" int dgs_comm_reduce_scatter_async(dgs_comm* c, void* buf, int64_t count_per_rank, int dtype,
+                                             dgs_stream_t compute) {
+  using namespace dgs;
+  DGS_CHECK_ARG(c && c->comm, "dgs_comm_reduce_scatter_async: NULL communicator");
+  DGS_CHECK_ARG(count_per_rank >= 0, "dgs_comm_reduce_scatter_async: count_per_rank < 0");
+  if (count_per_rank == 0) return DGS_OK;
+  DGS_CHECK_ARG(buf != nullptr, "dgs_comm_reduce_scatter_async: NULL buffer");
+  ncclDataType_t dt;
+  DGS_CHECK_ARG(nccl_dtype(dtype, &dt), "dgs_comm_reduce_scatter_async: bad dtype %d", dtype);
+  NcclApi* api = nccl();
+  if (int rc = fence_in(c, static_cast<cudaStream_t>(compute))) return rc;
+  char* mine = static_cast<char*>(buf) + (size_t)c->rank * (size_t)count_per_rank * (size_t)dtype_size(dtype);
+  DGS_NCCL(api, c->comm, api->ReduceScatter(buf, mine, (size_t)count_per_rank, dt, ncclSum, c->comm, c->side));
   return mark_out(c);
 }
 

@@ -59,6 +59,17 @@ norm_final_kernel(const float* __restrict__ partials, int n, float* __restrict__
   if (threadIdx.x == 0) out[0] = (float)sqrt(s);
 }
 
+__global__ void __launch_bounds__(kThreads)
+norm_final_sumsq_kernel(const float* __restrict__ partials, int n, float* __restrict__ out) {
+  __shared__ double red[32];
+  double s = 0.0;
+  for (int i = threadIdx.x; i < n; i += kThreads) s += (double)partials[i];
+  s = block_sum(s, red);
+  if (threadIdx.x == 0) out[0] = (float)s;
+}
+
+__global__ void sqrt_kernel(float* x) { x[0] = sqrtf(x[0]); }
+
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
 clip_scale_kernel(T* __restrict__ g, long long n, const float* __restrict__ total_norm, float max_norm) {
@@ -132,6 +143,23 @@ extern "C" int dgs_l2norm_final(const float* partials, int n_partials, float* ou
   DGS_CHECK_ARG(partials != nullptr && out_norm != nullptr, "dgs_l2norm_final: NULL buffer");
   DGS_CHECK_ARG(n_partials >= 0, "dgs_l2norm_final: n_partials < 0");
   norm_final_kernel<<<1, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(partials, n_partials, out_norm);
+  DGS_LAUNCHED();
+  return DGS_OK;
+}
+
+extern "C" int dgs_l2norm_final_sumsq(const float* partials, int n_partials, float* out_sumsq, dgs_stream_t stream) {
+  using namespace dgs;
+  DGS_CHECK_ARG(partials != nullptr && out_sumsq != nullptr, "dgs_l2norm_final_sumsq: NULL buffer");
+  DGS_CHECK_ARG(n_partials >= 0, "dgs_l2norm_final_sumsq: n_partials < 0");
+  norm_final_sumsq_kernel<<<1, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(partials, n_partials, out_sumsq);
+  DGS_LAUNCHED();
+  return DGS_OK;
+}
+
+extern "C" int dgs_sqrt_inplace(float* x, dgs_stream_t stream) {
+  using namespace dgs;
+  DGS_CHECK_ARG(x != nullptr, "dgs_sqrt_inplace: NULL buffer");
+  sqrt_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(x);
   DGS_LAUNCHED();
   return DGS_OK;
 }

@@ -49,6 +49,16 @@ class Comm:
     def allreduce_raw(self, ptr: int, count: int, dtype_code: int) -> None:
         _lib.calls.dgs_comm_allreduce_async(self._handle(), ctypes.c_void_p(ptr), count, dtype_code, _stream())
 
+    def reduce_scatter_raw(self, ptr: int, count_per_rank: int, dtype_code: int) -> None:
+        """In place: this rank's slice of [ptr, ptr + size*count_per_rank) ends up holding the sum over ranks."""
+        _lib.calls.dgs_comm_reduce_scatter_async(self._handle(), ctypes.c_void_p(ptr), count_per_rank, dtype_code, _stream())
+
+    def allgather_inplace_raw(self, ptr: int, bytes_per_rank: int) -> None:
+        """In place: every rank's slice of [ptr, ptr + size*bytes_per_rank) is filled with its owner's data."""
+        _lib.calls.dgs_comm_allgather_async(
+            self._handle(), ctypes.c_void_p(ptr + self.rank * bytes_per_rank), ctypes.c_void_p(ptr), bytes_per_rank, _stream()
+        )
+
     def broadcast(self, t: torch.Tensor, root: int = 0) -> None:
         _lib.calls.dgs_comm_broadcast_async(
             self._handle(), ctypes.c_void_p(t.data_ptr()), t.numel() * t.element_size(), root, _stream()

@@ -308,6 +308,7 @@ class PyTorchTrialContext(_PyTorchReducerContext):
                 average_aggregated_gradients=bool(average_aggregated_gradients),
                 backward_passes_per_step=backward_passes_per_step,
                 fp16_compression=bool(fp16_compression) and self.distributed.size > 1,
+                sharded_step=((self._exp_conf or {}).get("optimizations", {}) or {}).get("sharded_step"),
             )
         self.optimizers.append(optimizer)
         return optimizer
@@ -409,6 +410,8 @@ class PyTorchTrialContext(_PyTorchReducerContext):
         parameters = [p for group in optimizer.param_groups for p in group.get("params", [])]
         if scaler is None and self.experimental._auto_amp:
             scaler = self._scaler
+        if eng.sharded:
+            return self._sharded_step(eng, optimizer, parameters, present, clip_grads, scaler)
         aliased = all(fs.wire_dtype == fs.dtype for fs in eng.sets)
         fused = eng.can_fuse() and scaler is None and (aliased or clip_grads is None)
 
@@ -434,6 +437,27 @@ class PyTorchTrialContext(_PyTorchReducerContext):
         if auto_zero_grads:
             if materialized:
                 eng.clear_grads()
+        eng.reset_window()
+
+    def _sharded_step(self, eng: Any, optimizer: Any, parameters: List[Any], present: Any, clip_grads: Any, scaler: Any) -> None:
+        """step_optimizer when the engine reduce-scatters (opt-in sharded step): each rank holds only its slice
+        of the averaged gradients, so the only clip function that can be honoured is the one the kernels
+        implement -- torch.nn.utils.clip_grad_norm_ over all of the optimizer's parameters."""
+        if scaler:
+            raise errors.InvalidExperimentException("sharded_step cannot be combined with a GradScaler")
+        clip_req = None
+        if clip_grads is not None:
+            eng.materialize_grads(present)
+            versions = [fs.wire._version for fs in eng.sets]
+            clip_req = _run_clip(eng, clip_grads, parameters, defer=True)
+            eng.clear_grads()
+            if versions != [fs.wire._version for fs in eng.sets]:  # the function edited gradients in place
+                raise errors.InvalidExperimentException(
+                    "with optimizations.sharded_step the clip_grads function may only call "
+                    "torch.nn.utils.clip_grad_norm_(params, max_norm) on the parameters it is given: every rank "
+                    "holds just its own slice of the averaged gradients"
+                )
+        eng.fused_step(present, clip_req)
         eng.reset_window()
 
     # ---- epoch helpers the controller maintains ---------------------------------------------------

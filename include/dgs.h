@@ -105,6 +105,10 @@ int dgs_scale_cast(const float* acc, void* wire, int wire_dtype, int64_t n, floa
 int dgs_l2norm_grid(int64_t n);
 int dgs_l2norm_partial(const void* x, int dtype, int64_t n, float* partials, dgs_stream_t stream);
 int dgs_l2norm_final(const float* partials, int n_partials, float* out_norm, dgs_stream_t stream);
+/* Pass 2 variants for a norm whose elements are spread over ranks (sharded step): write the SUM of squares
+ * instead of its root, all-reduce that one float, then take the root in place. */
+int dgs_l2norm_final_sumsq(const float* partials, int n_partials, float* out_sumsq, dgs_stream_t stream);
+int dgs_sqrt_inplace(float* x, dgs_stream_t stream);
 /* both passes; `partials` must hold dgs_l2norm_grid(n) floats */
 int dgs_l2norm(const void* x, int dtype, int64_t n, float* partials, float* out_norm,
                dgs_stream_t stream);
@@ -259,6 +263,12 @@ int dgs_comm_allreduce_async(dgs_comm* comm, void* buf, int64_t count, int dtype
                              dgs_stream_t compute);
 int dgs_comm_broadcast_async(dgs_comm* comm, void* buf, int64_t bytes, int root,
                              dgs_stream_t compute);
+/* In-place reduce-scatter (sum): buf holds nranks * count_per_rank elements; afterwards this rank's slice
+ * buf[rank * count_per_rank ...] holds the sum over ranks of that slice (the other slices are undefined).
+ * First half of an allreduce: with dgs_comm_allgather_async (send = recv + rank * bytes_per_rank, in place) on the
+ * updated PARAMETERS it lets every rank run the optimizer step on 1/nranks of the elements only. */
+int dgs_comm_reduce_scatter_async(dgs_comm* comm, void* buf, int64_t count_per_rank, int dtype,
+                                  dgs_stream_t compute);
 /* recv holds nranks * bytes_per_rank bytes, ordered by rank */
 int dgs_comm_allgather_async(dgs_comm* comm, const void* send, void* recv, int64_t bytes_per_rank,
                              dgs_stream_t compute);

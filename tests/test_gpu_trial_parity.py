@@ -207,3 +207,64 @@ def test_two_slot_buffers_and_initial_broadcast_match_torch_ddp(lib):
     import torch.multiprocessing as mp
 
     mp.spawn(_bn_rank_main, args=(2, (_free_port(), _free_port()), _free_port()), nprocs=2, join=True)
+
+
+# ---- opt-in sharded step (reduce-scatter, step on 1/N of each bucket, all-gather parameters) ----------------
+class ShardedGoldenTrial(GoldenTrial):
+    """Same trial, but the clip function only does what sharded mode allows: clip_grad_norm_ on its argument."""
+
+    def _clip(self, params):
+        self.rec["norm"].append(torch.nn.utils.clip_grad_norm_(list(params), self.g.clip[1]))
+
+    def train_batch(self, batch, epoch_idx, batch_idx):
+        x, y = batch
+        loss = torch.nn.functional.mse_loss(self.model(x).float(), y.float())
+        self.context.backward(loss)
+        self.context.step_optimizer(self.opt, clip_grads=self._clip if self.g.clip is not None else None)
+        if (batch_idx + 1) % self.g.agg == 0:
+            self.rec["params"].append([_np(p) for p in self.plist])
+        return {"loss": loss}
+
+
+def _sharded_rank_main(rank: int, size: int, name: str, ports) -> None:
+    torch.cuda.set_device(rank)
+    dctx = core.DistributedContext(rank=rank, size=size, local_rank=rank, local_size=size, cross_rank=0, cross_size=1,
+                                   pub_port=ports[0], pull_port=ports[1])
+    try:
+        g = Golden(name)
+        rec = {"avg": [], "norm": [], "params": [], "state": []}
+        pytorch._PyTorchTrialController.pre_execute_hook(17)
+        ctx = pytorch.PyTorchTrialContext(distributed=dctx, hparams=g.hp, slots_per_trial=g.slots, aggregation_frequency=g.agg,
+                                          exp_conf={"optimizations": {"sharded_step": True}})
+        trial = ShardedGoldenTrial(ctx, g, rec)
+        assert ctx._engines[trial.opt].sharded
+        pytorch._PyTorchTrialController(trial, ctx, max_length=g.steps * g.agg, reporting_period=g.agg).run()
+        torch.cuda.synchronize()
+        dt = g.dtype
+        wide = 1.0 if dt == "float32" else 5.0
+        for s in range(g.steps):
+            for i in range(N_PARAMS):  # every rank ends every step with the full, identical parameters
+                assert_close(rec["params"][s][i], g.per_step("params", s)[i], dt, f"{name}: parameter {i} after step {s}", factor=wide)
+            if g.clip is not None:
+                assert_close(float(rec["norm"][s]), g.z["total_norm"][s], dt, f"{name}: total norm step {s}")
+        # optimizer.state_dict() gathers the other ranks' slices: complete and in the reference layout
+        sd = trial.opt.state_dict()["state"]
+        key = "momentum_buffer" if g.hp["optimizer"] == "sgd" else "exp_avg"
+        for j, i in enumerate([0, 4, 1, 2, 3, 5]):  # optimizer order -> model order
+            assert_close(_np(sd[j][key]), g.state(g.steps - 1, i, key), dt, f"{name}: gathered {key} of param {i}", factor=wide)
+        with pytest.raises(det.errors.InvalidExperimentException, match="sharded_step"):
+            ctx._current_batch_idx = g.agg - 1  # a boundary batch
+            ctx.backward(trial.model(torch.randn(4, 24, device="cuda").to(trial.plist[0].dtype)).float().sum())
+            ctx.step_optimizer(trial.opt, clip_grads=lambda ps: torch.nn.utils.clip_grad_value_(ps, 0.1))
+        ctx.close()
+    finally:
+        dctx.close()
+
+
+@pytest.mark.parametrize("name", [n for n, sc in SCENARIOS.items() if sc["slots"] == 2])
+def test_two_slot_sharded_step_matches_reference(lib, name):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run with gpurun --gpus 2)")
+    import torch.multiprocessing as mp
+
+    mp.spawn(_sharded_rank_main, args=(2, name, (_free_port(), _free_port())), nprocs=2, join=True)
