@@ -16,8 +16,8 @@ context.step_optimizer (fused step kernel).
   roofline  the fused optimizer kernel (largest HBM mover of the path), CUDA events recorded inside libdgs
             immediately around each launch (dgs_timer_*) during the timed region, on the launching stream;
             algorithmic bytes per element as stated in DESIGN.md
-  gradsync_microbench  BASELINE.json configs[4]: one flat 256 MiB fp32 bucket, accumulate + allreduce +
-            clip + AdamW, time per step against max(HBM, NVLink) roofline
+  gradsync_microbench  BASELINE.json configs[4]: one flat 1 GiB fp32 bucket, accumulate + allreduce +
+            clip + AdamW, time per step against max(HBM, NVLink) roofline (N > 1: also the opt-in sharded step)
   cpu_baseline  (N=1, rank 0) the torch port of the reference's path on the host cores, bounded sample
 """
 import argparse
@@ -52,7 +52,9 @@ def parse() -> argparse.Namespace:
                          "(torch DDP on NCCL + torch.optim), the number to beat, for comparison only")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-microbench", action="store_true")
-    ap.add_argument("--micro-mb", type=int, default=256)
+    ap.add_argument("--micro-mb", type=int, default=1024)
+    ap.add_argument("--micro-only", action="store_true", help="run only the grad-sync microbench (both step variants) and print it")
+    ap.add_argument("--micro-bucket-mb", type=int, nargs="*", default=[0], help="bucket caps to try with --micro-only (0 = adaptive)")
     ap.add_argument("--workload", default="cifar_resnet18", choices=["mnist", "cifar_resnet18", "resnet50", "gpt2_medium"],
                     help="cifar_resnet18 = BASELINE.json configs[1] (the default the driver runs); the others are configs[2]/[3]")
     return ap.parse_args()
@@ -188,7 +190,7 @@ def _free_port() -> int:
         return s.getsockname()[1]
 
 
-def gradsync_microbench(ctx: Any, mb: int, steps: int, peak_gbs: float, sharded: bool = False) -> Dict[str, Any]:
+def gradsync_microbench(ctx: Any, mb: int, steps: int, peak_gbs: float, sharded: bool = False, bucket_mb: int = 0) -> Dict[str, Any]:
     """configs[4]: one flat fp32 bucket through the path: flatten*scale -> allreduce -> L2 norm -> clip+AdamW."""
     import torch
 
@@ -201,7 +203,7 @@ def gradsync_microbench(ctx: Any, mb: int, steps: int, peak_gbs: float, sharded:
     params = [torch.nn.Parameter(torch.randn(n_piece, device=ctx.device) * 0.02) for _ in range(pieces)]
     opt = torch.optim.AdamW(params, lr=3e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
     eng = pytorch.GradSyncEngine(opt, ctx.device, ctx._get_comm(), aggregation_frequency=1, average_aggregated_gradients=True,
-                                 sharded_step=sharded)
+                                 sharded_step=sharded, bucket_bytes=bucket_mb << 20)
     grads = [[torch.randn(n_piece, device=ctx.device) * 1e-2 for _ in range(pieces)] for _ in range(2)]
     clip = pytorch._gradsync.ClipRequest()
     clip.max_norm = 1.0
@@ -290,6 +292,24 @@ def run_ours(args: argparse.Namespace) -> None:
 
         def build_validation_data_loader(self) -> Any:
             return None
+
+    if args.micro_only:
+        peak, _ = measured_peaks()
+        out = []
+        for cap in args.micro_bucket_mb:
+            for sharded in ((False, True) if world > 1 else (False,)):
+                m = gradsync_microbench(ctx, args.micro_mb, 12, peak, sharded=sharded, bucket_mb=cap)
+                m["bucket_cap_mib"] = cap or "adaptive"
+                out.append(m)
+                torch.cuda.empty_cache()
+        if rank == 0:
+            print(json.dumps({"n_gpus": world, "gradsync_microbench": out}), flush=True)
+        ctx.close()
+        dctx.close()
+        if dist is not None:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
 
     trial = BenchTrial(ctx)
     eng = ctx._engines[trial.optimizer]
@@ -406,9 +426,11 @@ def run_ours(args: argparse.Namespace) -> None:
 
     micro = None
     if not args.no_microbench:
-        micro = gradsync_microbench(ctx, args.micro_mb, 20, peak)
+        # one bucket = the whole buffer: the microbench has no backward pass for smaller buckets to overlap with
+        micro = gradsync_microbench(ctx, args.micro_mb, 12, peak, bucket_mb=args.micro_mb)
         if world > 1:  # the opt-in reduce-scatter / sharded-step / all-gather variant of the same step
-            micro["sharded_variant"] = gradsync_microbench(ctx, args.micro_mb, 20, peak, sharded=True)
+            torch.cuda.empty_cache()
+            micro["sharded_variant"] = gradsync_microbench(ctx, args.micro_mb, 12, peak, sharded=True, bucket_mb=args.micro_mb)
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
