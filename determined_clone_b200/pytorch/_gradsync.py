@@ -294,10 +294,6 @@ class GradSyncEngine:
             self._state_hook.remove()
             self._state_hook = None
 
-    @property
-    def parameters(self) -> List[torch.nn.Parameter]:
-        return [t.param for fs in self.sets for t in fs.tensors]
-
     # ---- backward ---------------------------------------------------------------------------------
     # Gradients are left where autograd puts them (p.grad) and picked up per bucket:
     #   * single GPU: after loss.backward() returns (end_pass) -- there is nothing to overlap with, and
