@@ -58,6 +58,37 @@ except AttributeError:  # pragma: no cover
     _raw_stream = None
 
 
+def plan_layout(numels: Sequence[int]) -> Tuple[List[int], int]:
+    """Element offset of every tensor in a flat buffer (each on an ALIGN_ELEMS boundary) and the buffer length."""
+    offs, total = [], 0
+    for n in numels:
+        offs.append(total)
+        total = _align(total + n)
+    return offs, total
+
+
+def plan_buckets(offs: Sequence[int], numels: Sequence[int], total: int, itemsize: int, first_bytes: int,
+                 cap_bytes: int) -> List[Tuple[int, int, List[int]]]:
+    """Cut the flat buffer into communication buckets (begin, end, tensor indices), from the END: the first
+    bucket closes once it holds first_bytes, the following ones at cap_bytes; a bucket is a contiguous element
+    range made of whole tensors, and together the buckets tile [0, total)."""
+    buckets: List[Tuple[int, int, List[int]]] = []
+    limit, cur, cur_bytes, end = first_bytes, [], 0, total
+    for i in range(len(offs) - 1, -1, -1):
+        cur.append(i)
+        cur_bytes += numels[i] * itemsize
+        if cur_bytes >= limit:
+            buckets.append((offs[i], end, cur))
+            end, cur, cur_bytes, limit = offs[i], [], 0, cap_bytes
+    if cur:
+        buckets.append((0, end, cur))
+    return buckets
+
+
+def adaptive_bucket_cap(total_bytes: int) -> int:
+    return min(max(total_bytes // 8, MIN_BUCKET_BYTES), MAX_BUCKET_BYTES)
+
+
 def _stream() -> ctypes.c_void_p:
     """cudaStream_t of torch's current stream on the current device."""
     if _raw_stream is not None:
@@ -266,19 +297,10 @@ class GradSyncEngine:
 
     def _cut_buckets(self, fs: _FlatSet) -> None:
         itemsize = torch.empty(0, dtype=fs.wire_dtype).element_size()
-        cap = self.bucket_bytes or min(max(fs.total * itemsize // 8, MIN_BUCKET_BYTES), MAX_BUCKET_BYTES)
-        limit = self.first_bucket_bytes
-        cur: List[int] = []
-        cur_bytes = 0
-        end = fs.total
-        for t in reversed(fs.tensors):
-            cur.append(t.index)
-            cur_bytes += t.numel * itemsize
-            if cur_bytes >= limit:
-                fs.buckets.append(_Bucket(t.off, end, cur))
-                end, cur, cur_bytes, limit = t.off, [], 0, cap
-        if cur:
-            fs.buckets.append(_Bucket(0, end, cur))
+        cap = self.bucket_bytes or adaptive_bucket_cap(fs.total * itemsize)
+        for begin, end, idxs in plan_buckets([t.off for t in fs.tensors], [t.numel for t in fs.tensors], fs.total, itemsize,
+                                             self.first_bucket_bytes, cap):
+            fs.buckets.append(_Bucket(begin, end, idxs))
         for bi, b in enumerate(fs.buckets):
             b.segs = (_lib.Seg * len(b.tensors))()
             for k, ti in enumerate(b.tensors):

@@ -362,3 +362,34 @@ def test_lr_scheduler_step_modes():
     assert counts == {SM.STEP_EVERY_BATCH: 24, SM.STEP_EVERY_OPTIMIZER_STEP: 6, SM.STEP_EVERY_EPOCH: 4, SM.MANUAL_STEP: 0}
     with pytest.raises(TypeError):
         pytorch.LRScheduler(Count(), "every batch")  # type: ignore
+
+
+# ---- flat layout and bucket planning (pure host logic of the engine) --------------------------------------------
+def test_layout_and_bucket_planning():
+    from determined_clone_b200.pytorch import _gradsync as G
+
+    rng = np.random.default_rng(0)
+    for trial in range(20):
+        numels = [int(x) for x in rng.integers(1, 3_000_000, size=int(rng.integers(1, 60)))]
+        offs, total = G.plan_layout(numels)
+        assert offs[0] == 0 and total % G.ALIGN_ELEMS == 0
+        for o, n, nxt in zip(offs, numels, offs[1:] + [total]):
+            assert o % G.ALIGN_ELEMS == 0 and o + n <= nxt < o + n + G.ALIGN_ELEMS  # aligned, no overlap, minimal padding
+        for itemsize, first, cap in ((4, 1 << 20, 25 << 20), (2, 1 << 20, 128 << 20), (4, 1, 1)):
+            buckets = G.plan_buckets(offs, numels, total, itemsize, first, cap)
+            # the buckets tile [0, total) from the end, each a contiguous run of whole tensors
+            assert buckets[0][1] == total and buckets[-1][0] == 0
+            for (b0, e0, _), (b1, e1, _) in zip(buckets, buckets[1:]):
+                assert e1 == b0 and b1 < e1
+            seen = [i for _, _, idxs in buckets for i in idxs]
+            assert sorted(seen) == list(range(len(numels))) and seen == sorted(seen, reverse=True)
+            for k, (b, e, idxs) in enumerate(buckets):
+                assert b == offs[min(idxs)] and (e - b) % G.ALIGN_ELEMS == 0  # divisible by 8 * world for world in {2,4,8}
+                nbytes = sum(numels[i] for i in idxs) * itemsize
+                limit = first if k == 0 else cap
+                if k < len(buckets) - 1:
+                    assert nbytes >= limit  # closed because it reached its limit ...
+                    assert nbytes - numels[min(idxs)] * itemsize < limit  # ... with the tensor that crossed it
+    assert G.adaptive_bucket_cap(44 << 20) == 25 << 20       # small model: torch DDP's size
+    assert G.adaptive_bucket_cap(710 << 20) == (710 << 20) // 8
+    assert G.adaptive_bucket_cap(14 << 30) == 128 << 20      # capped where NCCL's bandwidth has levelled off
