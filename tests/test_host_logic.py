@@ -393,3 +393,38 @@ def test_layout_and_bucket_planning():
     assert G.adaptive_bucket_cap(44 << 20) == 25 << 20       # small model: torch DDP's size
     assert G.adaptive_bucket_cap(710 << 20) == (710 << 20) // 8
     assert G.adaptive_bucket_cap(14 << 30) == 128 << 20      # capped where NCCL's bandwidth has levelled off
+
+
+def test_step_plan_cuts_ranges_to_this_ranks_slices():
+    """Sharded step: the per-group element ranges of one optimizer step are intersected with this rank's 1/N
+    slice of every bucket; together the ranks cover every range exactly once, each launch holds at most
+    DGS_MAX_RANGES ranges and its window [lo, hi) encloses them."""
+    from determined_clone_b200.pytorch import _gradsync as G
+
+    class FakeComm:
+        def __init__(self, rank):
+            self.rank = rank
+
+    numels = [640 * 64, 64, 128, 1000 * 64, 192, 64, 300 * 64]
+    offs, total = G.plan_layout(numels)
+    buckets = [G._Bucket(b, e, idxs) for b, e, idxs in G.plan_buckets(offs, numels, total, 4, 4096, 64 * 400 * 4)]
+    fs = G._FlatSet(torch.float32, torch.device("cpu"))
+    fs.total, fs.buckets = total, buckets
+    # ranges: one per "param group run" -- here simply one per tensor, with a key
+    items = [(o, G._align(o + n), ("g", i)) for i, (o, n) in enumerate(zip(offs, numels))]
+    eng = G.GradSyncEngine.__new__(G.GradSyncEngine)
+    eng.sharded, eng.world, eng.comm = False, 1, None
+    plan = eng._step_plan(fs, items)
+    assert plan == [(0, total, items)]
+    for world in (2, 4, 8):
+        covered = np.zeros(total, dtype=np.int32)
+        for rank in range(world):
+            eng.sharded, eng.world, eng.comm = True, world, FakeComm(rank)
+            for lo, hi, chunk in eng._step_plan(fs, items):
+                assert 0 < len(chunk) <= _lib.MAX_RANGES and lo == chunk[0][0] and hi == chunk[-1][1]
+                for b, e, key in chunk:
+                    assert lo <= b < e <= hi and b % 8 == 0 and e % 8 == 0
+                    src = [it for it in items if it[2] == key][0]
+                    assert src[0] <= b and e <= src[1]
+                    covered[b:e] += 1
+        assert (covered == 1).all()  # every element of every range is stepped by exactly one rank
