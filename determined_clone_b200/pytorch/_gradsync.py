@@ -360,22 +360,20 @@ class GradSyncEngine:
         communication.  Returns False, having touched nothing, when the case does not apply."""
         tensors, in_window = fs.tensors, fs.in_window
         state = in_window[0]
-        for t in tensors:
-            g = t.param.grad
-            if g is None or g.dtype != fs.dtype or g.is_sparse or not g.is_contiguous() or in_window[t.index] != state:
+        grads = [t.param.grad for t in tensors]
+        dtype = fs.dtype
+        for g in grads:
+            if g is None or g.dtype != dtype or g.is_sparse or not g.is_contiguous():
                 return False
-        if any(b.flushed for b in fs.buckets):
+        if any(s != state for s in in_window) or any(b.flushed for b in fs.buckets):
             return False
         to_wire = self._final_pass
         if not to_wire and fs.acc is None:
             fs.acc = torch.zeros(fs.total, dtype=torch.float32, device=self.device)
             fs.acc_ptr = _ptr(fs.acc)
         segs = fs.segs_all
-        keep = []
-        for k, t in enumerate(tensors):
-            g = t.param.grad
-            t.param.grad = None
-            keep.append(g)
+        for k, g in enumerate(grads):  # `grads` keeps the tensors alive until the launch below
+            tensors[k].param.grad = None
             segs[k].src = g.data_ptr()
         mode = (_lib.READ_ACC if state else 0) | (_lib.WRITE_WIRE if to_wire else 0)
         _lib.calls.dgs_flatten_accumulate(segs, len(tensors), fs.dtype_code, fs.acc_ptr, fs.wire_ptr, fs.wire_code, mode,
