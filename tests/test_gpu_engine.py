@@ -445,3 +445,48 @@ def test_fp16_wire_compression(lib):
         torch.cuda.synchronize()
         np.testing.assert_allclose(p.detach().cpu().numpy(), q.detach().cpu().numpy(), rtol=2e-6, atol=1e-7)
     eng.close()
+
+
+def test_tiny_gpt2_with_tied_embeddings_matches_reference_path(lib):
+    """BASELINE.json configs[3] in miniature: a GPT-2 causal LM (tied input/output embedding: one parameter used
+    twice in the graph), AdamW with a decay and a no-decay group, aggregation_frequency 2, clip_grad_norm_ 1.0 --
+    ours vs the reference's step logic on the same GPU, fp32, 6 optimizer steps."""
+    transformers = pytest.importorskip("transformers")
+
+    def build():
+        torch.manual_seed(21)
+        cfg = transformers.GPT2Config(vocab_size=211, n_positions=32, n_embd=64, n_layer=2, n_head=4,
+                                      resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0, use_cache=False)
+        return transformers.GPT2LMHeadModel(cfg)
+
+    g = torch.Generator().manual_seed(5)
+    batches = [torch.randint(0, 211, (4, 32), generator=g).cuda() for _ in range(12)]
+    results = []
+    for which in ("ours", "ref"):
+        ours, ref = make_contexts(agg=2)
+        ctx = ours if which == "ours" else ref
+        model = ctx.wrap_model(build())
+        assert model.lm_head.weight is model.transformer.wte.weight  # tied
+        decay = [p for p in model.parameters() if p.ndim >= 2]
+        no_decay = [p for p in model.parameters() if p.ndim < 2]
+        opt = ctx.wrap_optimizer(torch.optim.AdamW([{"params": decay, "weight_decay": 0.1}, {"params": no_decay, "weight_decay": 0.0}],
+                                                   lr=1e-3, betas=(0.9, 0.95)))
+        norms, losses = [], []
+        for i, tok in enumerate(batches):
+            ctx._current_batch_idx = i
+            loss = model(input_ids=tok, labels=tok).loss
+            losses.append(float(loss.detach()))
+            ctx.backward(loss)
+            ctx.step_optimizer(opt, clip_grads=lambda ps: norms.append(float(torch.nn.utils.clip_grad_norm_(ps, 1.0))))
+        results.append((losses, norms, [p.detach().cpu().numpy().copy() for p in model.parameters()]))
+        ours.close()
+    (l1, n1, p1), (l2, n2, p2) = results
+    assert len(n1) == len(n2) == 6
+    np.testing.assert_allclose(l1, l2, rtol=2e-5)
+    np.testing.assert_allclose(n1, n2, rtol=2e-5)
+    # The key bias of attention has a mathematically zero gradient (softmax is invariant to it): what reaches
+    # the optimizer is run-to-run rounding noise of the model's own backward kernels, which Adam divides by
+    # sqrt(v) + eps and turns into moves of up to lr per step.  Those elements cannot agree to 1e-5 between any
+    # two runs; they are bounded by a small fraction of the distance Adam can move at all (lr * steps).
+    for a, b in zip(p1, p2):
+        np.testing.assert_allclose(a, b, rtol=2e-5, atol=max(2e-5 * float(np.abs(b).max()), 2e-3 * 1e-3 * 6))
