@@ -102,6 +102,11 @@ SCENARIOS: Dict[str, Dict[str, Any]] = {
                 global_batch_size=8),
         slots=1, agg=4, steps=10, clip=("norm", 1.0), dtype="bfloat16",
     ),
+    # optimizations.average_aggregated_gradients: false -> gradients of the 3 micro-batches are summed, not averaged
+    "sgd_n1_a3_noavg": dict(
+        hp=dict(optimizer="sgd", lr=0.02, momentum=0.9, weight_decay=1e-3, global_batch_size=8),
+        slots=1, agg=3, steps=10, clip=("norm", 2.0), dtype="float32", average=False,
+    ),
     "adamw_bf16_n2_a2_clip": dict(
         hp=dict(optimizer="adamw", lr=3e-4, betas=[0.9, 0.95], eps=1e-8, weight_decay=0.1,
                 global_batch_size=8),

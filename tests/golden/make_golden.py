@@ -155,7 +155,7 @@ def run_rank(name: str, rank: int, size: int, out_dir: str) -> None:
         "resources": {"native_parallel": False, "slots_per_trial": size},
         "hyperparameters": hp,
         "optimizations": {"aggregation_frequency": agg, "gradient_compression": False,
-                          "average_training_metrics": True, "average_aggregated_gradients": True},
+                          "average_training_metrics": True, "average_aggregated_gradients": bool(sc.get("average", True))},
         "checkpoint_policy": "none",
         "perform_initial_validation": False,
         "checkpoint_storage": {"type": "shared_fs", "host_path": out_dir},
@@ -171,7 +171,7 @@ def run_rank(name: str, rank: int, size: int, out_dir: str) -> None:
         debug_enabled=False, enable_tensorboard_logging=False,
     )
     context._set_default_gradient_compression(False)
-    context._set_default_average_aggregated_gradients(True)
+    context._set_default_average_aggregated_gradients(bool(sc.get("average", True)))
     trial = RefGoldenTrial(context)
     controller = pytorch._PyTorchTrialController(
         trial_inst=trial, context=context, max_length=pytorch.Batch(steps * agg),

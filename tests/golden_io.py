@@ -26,6 +26,7 @@ class Golden:
         self.slots, self.agg, self.steps = self.sc["slots"], self.sc["agg"], self.sc["steps"]
         self.dtype: str = self.sc["dtype"]
         self.clip = self.sc["clip"]
+        self.average: bool = bool(self.sc.get("average", True))
         with np.load(GOLDEN / f"{name}.npz") as z:
             self.z = {k: z[k] for k in z.files}
 

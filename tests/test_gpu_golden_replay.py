@@ -43,7 +43,7 @@ def test_replay(lib, name):
     acc = torch.zeros(total, device="cuda")
     norm = torch.zeros(1, device="cuda")
     partials = torch.zeros(L.calls.dgs_l2norm_grid(total), device="cuda")
-    scale = 1.0 / (g.slots * g.agg)
+    scale = 1.0 / (g.slots * (g.agg if g.average else 1))
     groups = g.groups()
     kind = g.hp["optimizer"]
 

@@ -35,7 +35,7 @@ class GoldenTrial(pytorch.PyTorchTrial):
                 p.copy_(torch.from_numpy(init).to(dtype))
         self.model = context.wrap_model(model)
         self.plist = list(self.model.parameters())
-        self.opt = context.wrap_optimizer(make_optimizer(self.model, g.hp))
+        self.opt = context.wrap_optimizer(make_optimizer(self.model, g.hp), average_aggregated_gradients=g.average)
         x, y = make_data(g.steps * g.agg, g.hp["global_batch_size"])
         self.ds = torch.utils.data.TensorDataset(x.to(dtype), y.to(dtype))
 

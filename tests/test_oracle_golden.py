@@ -22,7 +22,7 @@ def test_oracle_reproduces_reference_run(name):
             assert_close(a, d, g.dtype, what)
     opt = O.OptimizerOracle(g.hp["optimizer"], g.init_params(), GROUP_OF, g.groups(), g.dtype)
     for s in range(g.steps):
-        out = O.train_window(opt, g.raw(s), g.agg, g.clip)
+        out = O.train_window(opt, g.raw(s), g.agg, g.clip, average=g.average)
         for i in range(N_PARAMS):
             close(out["avg_grads"][i], g.per_step("avg_grads", s)[i], f"avg grad step {s} param {i}")
             close(out["clipped_grads"][i], g.per_step("clipped_grads", s)[i], f"clipped step {s} param {i}")
@@ -124,7 +124,7 @@ def test_torch_port_reproduces_reference_run(name):
             p.copy_(torch.from_numpy(init).to(dtype))
     ctx = torch_port.RefContext(aggregation_frequency=g.agg, hparams=g.hp)
     model = ctx.wrap_model(model)
-    opt = ctx.wrap_optimizer(make_optimizer(model, g.hp))
+    opt = ctx.wrap_optimizer(make_optimizer(model, g.hp), average_aggregated_gradients=g.average)
     x, y = make_data(g.steps * g.agg, g.hp["global_batch_size"])
     x, y = x.to(dtype), y.to(dtype)
     bs = ctx.get_per_slot_batch_size()
