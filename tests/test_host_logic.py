@@ -428,3 +428,58 @@ def test_step_plan_cuts_ranges_to_this_ranks_slices():
                     assert src[0] <= b and e <= src[1]
                     covered[b:e] += 1
         assert (covered == 1).all()  # every element of every range is stepped by exactly one rank
+
+
+def test_clip_interception_routes_only_the_exact_pattern():
+    """_run_clip: torch's clip_grad_norm_ over exactly this optimizer's gradient views is answered by the engine
+    (norm kernels, clip deferred into the step); anything else falls through to torch untouched.  Exercised on
+    CPU with a stand-in engine that computes its norm with torch."""
+    from torch.nn.utils import clip_grad_norm_ as imported_at_module_level
+
+    from determined_clone_b200.pytorch import _gradsync as G
+    from determined_clone_b200.pytorch import _pytorch_context as C
+
+    params = [torch.nn.Parameter(torch.zeros(5)), torch.nn.Parameter(torch.zeros(3, 2))]
+    wire = torch.arange(11, dtype=torch.float32) * 0.5
+
+    class FakeSet:
+        tensors = [G._Tensor(params[0], 0, 0, 0), G._Tensor(params[1], 0, 5, 1)]
+        grad_views = [wire[0:5], wire[5:11].view(3, 2)]
+        wire_dtype = dtype = torch.float32
+
+    class FakeEngine:
+        sets = [FakeSet()]
+        calls = 0
+
+        def total_norm(self):
+            self.calls += 1
+            return torch.linalg.vector_norm(wire)
+
+    eng = FakeEngine()
+    for p, v in zip(params, FakeSet.grad_views):
+        p.grad = v
+    want = float(torch.linalg.vector_norm(wire))
+    seen = {}
+
+    # (1) the exact pattern, through a name bound at import time: intercepted, clip deferred, gradients untouched
+    req = C._run_clip(eng, lambda ps: seen.__setitem__("n", imported_at_module_level(ps, 0.25)), params, defer=True)
+    assert req.max_norm == 0.25 and eng.calls == 1 and float(seen["n"]) == pytest.approx(want)
+    assert torch.equal(wire, torch.arange(11, dtype=torch.float32) * 0.5)
+
+    # (2) a subset of the parameters, another norm type, or error_if_nonfinite: torch's own code runs
+    before = wire.clone()
+    req = C._run_clip(eng, lambda ps: torch.nn.utils.clip_grad_norm_(ps[:1], 0.1), params, defer=True)
+    assert req.max_norm is None and eng.calls == 1
+    assert float(torch.linalg.vector_norm(wire[:5])) == pytest.approx(0.1, rel=1e-4) and torch.equal(wire[5:], before[5:])
+    req = C._run_clip(eng, lambda ps: torch.nn.utils.clip_grad_norm_(ps, 1.0, norm_type=float("inf")), params, defer=True)
+    assert req.max_norm is None and eng.calls == 1 and float(wire.abs().max()) == pytest.approx(1.0, rel=1e-4)
+
+    # (3) a function that never asks for a norm: nothing requested, the patch is removed afterwards
+    from torch.nn.utils import clip_grad as tcg
+
+    real = tcg._get_total_norm
+    req = C._run_clip(eng, lambda ps: None, params, defer=True)
+    assert req.max_norm is None and tcg._get_total_norm is real
+    with pytest.raises(ZeroDivisionError):  # ... also when the user's function raises
+        C._run_clip(eng, lambda ps: 1 / 0, params, defer=True)
+    assert tcg._get_total_norm is real
