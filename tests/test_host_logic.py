@@ -483,3 +483,39 @@ def test_clip_interception_routes_only_the_exact_pattern():
     with pytest.raises(ZeroDivisionError):  # ... also when the user's function raises
         C._run_clip(eng, lambda ps: 1 / 0, params, defer=True)
     assert tcg._get_total_norm is real
+
+
+def test_controller_reporting_cadence_and_reducers_on_host_values():
+    """The train/report loop with host-valued metrics (the object route): a report every reporting_period batches
+    and at the end, per-batch metrics preserved, averages per period, custom reducers reset per period, one batch
+    in test_mode; delivered one period late but complete and in order."""
+
+    class Trial(pytorch.PyTorchTrial):
+        def __init__(self, context):
+            self.context = context
+            self.total = context.wrap_reducer(lambda vals: sum(vals), name="seen_sum", for_validation=False)
+
+        def build_training_data_loader(self):
+            ds = torch.utils.data.TensorDataset(torch.arange(40).float())
+            return pytorch.DataLoader(ds, batch_size=5)
+
+        def train_batch(self, batch, epoch_idx, batch_idx):
+            self.total.update(batch_idx)
+            return {"loss": float(batch_idx), "first": float(batch[0][0]), "maybe": None if batch_idx % 2 else 1.0}
+
+    ctx = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 5})
+    got = []
+    ctl = pytorch._PyTorchTrialController(Trial(ctx), ctx, max_length=8, reporting_period=3, on_report=lambda n, r: got.append((n, r)))
+    ctl.run()
+    assert [n for n, _ in got] == [3, 6, 8] and ctl.batches_trained == 8
+    assert [r["avg_metrics"]["loss"] for _, r in got] == [1.0, 4.0, 6.5]
+    assert [r["avg_metrics"]["seen_sum"] for _, r in got] == [3, 12, 13]          # reducers are reset every period
+    assert [b["first"] for b in got[0][1]["batch_metrics"]] == [0.0, 5.0, 10.0]    # batches arrive in order
+    assert [r["avg_metrics"]["maybe"] for _, r in got] == [1.0, 1.0, 1.0]          # None values are ignored
+    assert all(r["steps_completed"] == n and r["samples_per_second"] > 0 for n, r in got)
+    assert ctx.is_epoch_start() is False and ctx.current_train_epoch() == 0 and ctx._epoch_len == 8
+
+    once = pytorch._PyTorchTrialController(Trial(pytorch.PyTorchTrialContext(hparams={"global_batch_size": 5})),
+                                           ctx, max_length=100, test_mode=True)
+    once.run()
+    assert once.batches_trained == 1 and len(once.reports) == 1
