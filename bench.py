@@ -521,6 +521,10 @@ def run_torch_gpu(args: argparse.Namespace) -> None:
 
 
 def main() -> None:
+    # stdout carries exactly one JSON line: keep NCCL's "NCCL version ..." banner (printed to stdout when the image
+    # sets NCCL_DEBUG=VERSION) out of it; an explicit NCCL_DEBUG=INFO from the caller is respected
+    if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"
     args = parse()
     if args.impl == "reference":
         run_reference(args)
