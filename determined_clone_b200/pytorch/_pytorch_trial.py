@@ -13,7 +13,10 @@ What changes on the hot path: scalar device metrics are not pulled to the host e
 ranks by kernels once per reporting period (_metric_utils.DeviceMetricBuffer).
 """
 import abc
+import json
 import logging
+import pathlib
+import pickle
 import random
 import time
 from typing import Any, Callable, Dict, List, Optional, Union
@@ -64,6 +67,30 @@ class PyTorchTrial(abc.ABC):
         return {}
 
 
+class _TrialState:
+    """What trial_state.pkl holds (reference _pytorch_trial.py:164-186).  trial_id tells a pause/restart (same
+    trial: counters continue) from a warm start off another trial's checkpoint (counters restart)."""
+
+    def __init__(self, trial_id: int = 0, last_ckpt: int = 0, step_id: int = 0, last_val: int = 0,
+                 batches_trained: int = 0, epochs_trained: int = 0) -> None:
+        self.trial_id = trial_id
+        self.last_ckpt = last_ckpt
+        self.step_id = step_id
+        self.last_val = last_val
+        self.batches_trained = batches_trained
+        self.epochs_trained = epochs_trained
+
+
+def _clone_tensors(obj: Any) -> Any:
+    if isinstance(obj, torch.Tensor):
+        return obj.detach().clone()
+    if isinstance(obj, dict):
+        return {k: _clone_tensors(v) for k, v in obj.items()}
+    if isinstance(obj, (list, tuple)):
+        return type(obj)(_clone_tensors(v) for v in obj)
+    return obj
+
+
 class _PyTorchTrialController:
     def __init__(
         self,
@@ -75,6 +102,8 @@ class _PyTorchTrialController:
         steps_completed: int = 0,
         device_metrics: bool = True,
         test_mode: bool = False,
+        trial_id: int = 1,
+        val_from_previous_run: int = 0,
     ) -> None:
         self.trial = trial_inst
         self.context = context
@@ -89,6 +118,9 @@ class _PyTorchTrialController:
         self._metric_buffer = _metric_utils.DeviceMetricBuffer(context.device, capacity=max(reporting_period, 1))
         self.training_loader: Any = None
         self.validation_loader: Any = None
+        self.trial_id = trial_id
+        self.state = _TrialState(trial_id=trial_id, batches_trained=steps_completed)
+        self.val_from_previous_run = val_from_previous_run
 
     # ---- set-up -------------------------------------------------------------------------------------
     @classmethod
@@ -251,12 +283,10 @@ class _PyTorchTrialController:
 
     # ---- checkpoints ----------------------------------------------------------------------------------
     def _save(self, path: Any) -> None:
-        """Write state_dict.pth + trial_state.pkl with the reference's keys (_pytorch_trial.py:1312-1385), so
-        that checkpoints move between the two harnesses.  Parameters and optimizer state are views of the
-        engine's flat buffers; torch.save stores them as ordinary per-tensor entries."""
-        import pathlib
-        import pickle
-
+        """Write state_dict.pth + trial_state.pkl + load_data.json with the reference's keys
+        (_pytorch_trial.py:1312-1385), so that checkpoints move between the two harnesses.  Parameters and
+        optimizer state are views of the engine's flat buffers; they are cloned so that torch.save stores
+        ordinary per-tensor entries instead of one copy of the whole flat storage per view."""
         path = pathlib.Path(path)
         path.mkdir(parents=True, exist_ok=True)
         rng_state = {
@@ -268,7 +298,7 @@ class _PyTorchTrialController:
             rng_state["gpu_rng_state"] = torch.cuda.get_rng_state(self.context.device)
         checkpoint = {
             "models_state_dict": [{k: v.detach().clone() for k, v in m.state_dict().items()} for m in self.context.models],
-            "optimizers_state_dict": [o.state_dict() for o in self.context.optimizers],
+            "optimizers_state_dict": [_clone_tensors(o.state_dict()) for o in self.context.optimizers],
             "lr_schedulers_state_dict": [s.state_dict() for s in self.context.lr_schedulers],
             "callbacks": {},
             "rng_state": rng_state,
@@ -276,41 +306,123 @@ class _PyTorchTrialController:
         if self.context._scaler:
             checkpoint["scaler_state_dict"] = self.context._scaler.state_dict()
         torch.save(checkpoint, str(path / "state_dict.pth"))
+        self.state.batches_trained = self.batches_trained
+        self.state.epochs_trained = self._get_epoch_idx(self.batches_trained)
+        self.state.last_ckpt = self.batches_trained
         with (path / "trial_state.pkl").open("wb") as f:
-            pickle.dump({"batches_trained": self.batches_trained, "trial_id": 1, "last_ckpt": self.batches_trained}, f)
+            pickle.dump(vars(self.state), f)
+        cls = type(self.trial)
+        with (path / "load_data.json").open("w") as f:
+            json.dump({
+                "trial_type": "PyTorchTrial",
+                "experiment_config": self.context._exp_conf,
+                "hparams": self.context._hparams,
+                "trial_cls_spec": f"{cls.__module__}:{cls.__qualname__}",
+                "is_trainer": True,
+            }, f)
+
+    # where state_dict.pth has lived over the reference's releases, newest first (:1118-1125)
+    _CHECKPOINT_FILES = (("state_dict.pth",), ("determined", "state_dict.pth"), ("pedl", "state_dict.pth"), ("checkpoint.pt",))
+    # (current list-valued key, pre-multi-model singular key, what it restores)
+    _CHECKPOINT_PARTS = (
+        ("models_state_dict", "model_state_dict", "model"),
+        ("optimizers_state_dict", "optimizer_state_dict", "optimizer"),
+        ("lr_schedulers_state_dict", "lr_scheduler", "LR scheduler"),
+    )
 
     def _load(self, path: Any) -> None:
-        """Restore from a checkpoint directory written by _save() or by the reference's _save (incl. DDP-wrapped
-        models whose keys carry a "module." prefix, :1151-1168).  Loaded optimizer state is copied back into the
-        engine's flat buffers on the next step (GradSyncEngine._adopt_state)."""
-        import pathlib
-        import pickle
-
+        """Restore from a checkpoint directory written by _save() or by any reference release the reference's
+        own _load accepts (:1117-1271): the older file locations, the singular pre-multi-model keys, model keys
+        with or without DDP's "module." prefix, and workload_sequencer.pkl from before trial_state.pkl.  Loaded
+        optimizer state is copied back into the engine's flat buffers on the next step
+        (GradSyncEngine._adopt_state)."""
         path = pathlib.Path(path)
-        checkpoint = torch.load(str(path / "state_dict.pth"), map_location="cpu", weights_only=False)
-        models = checkpoint.get("models_state_dict") or [checkpoint["model_state_dict"]]
-        for model, sd in zip(self.context.models, models):
-            sd = dict(sd)
-            torch.nn.modules.utils.consume_prefix_in_state_dict_if_present(sd, "module.")
-            model.load_state_dict(sd)
-        optimizers = checkpoint.get("optimizers_state_dict") or [checkpoint["optimizer_state_dict"]]
-        for optimizer, sd in zip(self.context.optimizers, optimizers):
-            optimizer.load_state_dict(sd)
-        for sched, sd in zip(self.context.lr_schedulers, checkpoint.get("lr_schedulers_state_dict", [])):
-            sched.load_state_dict(sd)
-        if "scaler_state_dict" in checkpoint and self.context._scaler:
-            self.context._scaler.load_state_dict(checkpoint["scaler_state_dict"])
+        checkpoint = None
+        for parts in self._CHECKPOINT_FILES:
+            if path.joinpath(*parts).exists():
+                checkpoint = torch.load(str(path.joinpath(*parts)), map_location="cpu", weights_only=False)
+                break
+        if not isinstance(checkpoint, dict):
+            return  # same as the reference: nothing to restore, not an error
+
+        targets = {"model": self.context.models, "optimizer": self.context.optimizers, "LR scheduler": self.context.lr_schedulers}
+        for plural, singular, what in self._CHECKPOINT_PARTS:
+            if singular in checkpoint:
+                if plural in checkpoint:
+                    raise RuntimeError(f"Both {singular} and {plural} in checkpoint.")
+                if len(targets[what]) > 1:
+                    raise RuntimeError(f"Old-format checkpoint cannot be loaded into a context with more than one {what}.")
+                saved = [checkpoint[singular]]
+            else:
+                saved = checkpoint[plural] if targets[what] else []  # a missing key only matters if something needs it
+            for obj, sd in zip(targets[what], saved):
+                if what == "model":
+                    # this harness never wraps the model, so its keys are the bare ones: a checkpoint taken from a
+                    # DDP-wrapped model (reference, slots > 1) loses the prefix, everything else loads unchanged
+                    sd = dict(sd)
+                    torch.nn.modules.utils.consume_prefix_in_state_dict_if_present(sd, "module.")
+                obj.load_state_dict(sd)
+
+        scaler = self.context._scaler
+        if "scaler_state_dict" in checkpoint:
+            if scaler:
+                scaler.load_state_dict(checkpoint["scaler_state_dict"])
+            else:
+                logger.warning("There exists scaler_state_dict in checkpoint but the experiment is not using AMP.")
+        elif scaler:
+            logger.warning("The experiment is using AMP but scaler_state_dict does not exist in the checkpoint.")
+
         rng = checkpoint.get("rng_state")
         if rng:
-            torch.random.set_rng_state(rng["cpu_rng_state"])
             np.random.set_state(rng["np_rng_state"])
             random.setstate(rng["random_rng_state"])
-            if "gpu_rng_state" in rng and torch.cuda.is_available():
-                torch.cuda.set_rng_state(rng["gpu_rng_state"], self.context.device)
-        state_file = path / "trial_state.pkl"
-        if state_file.exists():
-            with state_file.open("rb") as f:
-                self.batches_trained = int(pickle.load(f).get("batches_trained", self.batches_trained))
+            torch.random.set_rng_state(rng["cpu_rng_state"])
+            if torch.cuda.is_available() and self.context.device.type == "cuda":
+                if "gpu_rng_state" in rng:
+                    torch.cuda.set_rng_state(rng["gpu_rng_state"], self.context.device)
+                else:
+                    logger.warning("The system has a gpu but no gpu_rng_state exists in the checkpoint.")
+            elif "gpu_rng_state" in rng:
+                logger.warning("There exists gpu_rng_state in checkpoint but the system has no gpu.")
+        else:
+            logger.warning("The checkpoint has no random state to restore.")
+
+        if (path / "trial_state.pkl").exists():
+            with (path / "trial_state.pkl").open("rb") as f:
+                self._load_state(pickle.load(f))
+        elif (path / "workload_sequencer.pkl").exists():
+            with (path / "workload_sequencer.pkl").open("rb") as f:
+                self._load_wlsq_state(pickle.load(f))
+
+    def _get_epoch_idx(self, batch_id: int) -> int:
+        return batch_id // self.context._epoch_len if self.context._epoch_len else 0
+
+    def _adopt_trial_state(self, state: "_TrialState") -> None:
+        self.state = state
+        # a validation made against exactly this checkpoint is known to the master but not to the file (:1287-1293)
+        if state.batches_trained == self.val_from_previous_run:
+            state.last_val = state.batches_trained
+        self.batches_trained = state.batches_trained
+
+    def _load_state(self, state: Dict[str, Any]) -> None:
+        """trial_state.pkl (:1273-1293).  A checkpoint of ANOTHER trial only warm-starts the weights: the counters
+        start from zero."""
+        if state.get("trial_id") != self.trial_id:
+            self.state = _TrialState(trial_id=self.trial_id)
+            return
+        self._adopt_trial_state(_TrialState(**state))
+
+    def _load_wlsq_state(self, state: Dict[str, Any]) -> None:
+        """workload_sequencer.pkl, the pre-Trainer file (:1295-1313): `steps_completed` there is what
+        trial_state.pkl calls batches_trained; epochs are recomputed from it."""
+        if state.get("trial_id") != self.trial_id:
+            self.state = _TrialState(trial_id=self.trial_id)
+            return
+        done = state.get("steps_completed")
+        self._adopt_trial_state(_TrialState(
+            trial_id=state.get("trial_id"), last_ckpt=state.get("last_ckpt"), last_val=state.get("last_val"),
+            step_id=state.get("step_id"), batches_trained=done, epochs_trained=self._get_epoch_idx(done),
+        ))
 
     # ---- validation ---------------------------------------------------------------------------------
     @torch.no_grad()

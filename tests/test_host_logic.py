@@ -519,3 +519,107 @@ def test_controller_reporting_cadence_and_reducers_on_host_values():
                                            ctx, max_length=100, test_mode=True)
     once.run()
     assert once.batches_trained == 1 and len(once.reports) == 1
+
+
+def _model_only_controller(model, trial_id=1, epoch_len=None, val_from_previous_run=0):
+    class Trial(pytorch.PyTorchTrial):
+        def __init__(self, context):
+            self.context = context
+            self.model = context.wrap_model(model)
+
+        def build_training_data_loader(self):
+            raise AssertionError("not used")
+
+        def train_batch(self, batch, epoch_idx, batch_idx):
+            raise AssertionError("not used")
+
+    ctx = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 16})
+    ctx._epoch_len = epoch_len
+    return pytorch._PyTorchTrialController(Trial(ctx), ctx, max_length=1, trial_id=trial_id, val_from_previous_run=val_from_previous_run)
+
+
+def test_checkpoint_load_accepts_every_layout_the_reference_accepts(tmp_path):
+    """_load (reference _pytorch_trial.py:1117-1313) on host objects only: older file locations, the singular
+    pre-multi-model keys and their error texts, DDP's "module." prefix, trial_state.pkl vs the older
+    workload_sequencer.pkl, and the trial_id rule."""
+    import pickle
+
+    src = torch.nn.Linear(3, 2)
+    rng = {"cpu_rng_state": torch.random.get_rng_state(), "np_rng_state": np.random.get_state(), "random_rng_state": __import__("random").getstate()}
+
+    def write(d, payload, where=("state_dict.pth",), **state_files):
+        d.joinpath(*where).parent.mkdir(parents=True, exist_ok=True)
+        torch.save(payload, d.joinpath(*where))
+        for name, state in state_files.items():
+            with (d / f"{name}.pkl").open("wb") as f:
+                pickle.dump(state, f)
+        return d
+
+    def loaded(ctl):
+        return {k: v.clone() for k, v in ctl.context.models[0].state_dict().items()}
+
+    def same(ctl):
+        return all(torch.equal(v, src.state_dict()[k]) for k, v in loaded(ctl).items())
+
+    # current layout, keys as a DDP-wrapped model writes them, state of the same trial
+    ddp_keys = {"module." + k: v for k, v in src.state_dict().items()}
+    d = write(tmp_path / "a", {"models_state_dict": [ddp_keys], "optimizers_state_dict": [], "lr_schedulers_state_dict": [], "rng_state": rng},
+              trial_state=dict(trial_id=1, last_ckpt=40, step_id=4, last_val=30, batches_trained=40, epochs_trained=2))
+    ctl = _model_only_controller(torch.nn.Linear(3, 2), val_from_previous_run=40)
+    ctl._load(d)
+    assert same(ctl) and ctl.batches_trained == 40
+    # the validation made against exactly this checkpoint is known to the master only (:1287-1293)
+    assert vars(ctl.state) == dict(trial_id=1, last_ckpt=40, step_id=4, last_val=40, batches_trained=40, epochs_trained=2)
+
+    # oldest layout: pedl/state_dict.pth with singular keys, and the pre-Trainer workload_sequencer.pkl
+    d = write(tmp_path / "b", {"model_state_dict": src.state_dict(), "optimizer_state_dict": {}, "rng_state": rng}, where=("pedl", "state_dict.pth"),
+              workload_sequencer=dict(trial_id=1, last_ckpt=1, steps_completed=25, step_id=1, last_val=0))
+    ctl = _model_only_controller(torch.nn.Linear(3, 2), epoch_len=10)
+    ctl._load(d)
+    assert same(ctl)
+    assert vars(ctl.state) == dict(trial_id=1, last_ckpt=1, step_id=1, last_val=0, batches_trained=25, epochs_trained=2)
+
+    # another trial's checkpoint warm-starts the weights, the counters start over
+    for files in (dict(trial_state=dict(trial_id=9, batches_trained=40)), dict(workload_sequencer=dict(trial_id=9, steps_completed=40))):
+        d = write(tmp_path / ("c" + next(iter(files))), {"models_state_dict": [src.state_dict()], "optimizers_state_dict": [], "lr_schedulers_state_dict": []}, **files)
+        ctl = _model_only_controller(torch.nn.Linear(3, 2), trial_id=3)
+        ctl._load(d)
+        assert same(ctl) and ctl.batches_trained == 0
+        assert vars(ctl.state) == dict(trial_id=3, last_ckpt=0, step_id=0, last_val=0, batches_trained=0, epochs_trained=0)
+
+    # both spellings at once is an error, with the reference's message
+    d = write(tmp_path / "d", {"model_state_dict": src.state_dict(), "models_state_dict": [src.state_dict()]})
+    with pytest.raises(RuntimeError, match="Both model_state_dict and models_state_dict in checkpoint."):
+        _model_only_controller(torch.nn.Linear(3, 2))._load(d)
+    # a singular-key checkpoint cannot feed two models
+    d = write(tmp_path / "e", {"model_state_dict": src.state_dict(), "optimizer_state_dict": {}})
+    ctl = _model_only_controller(torch.nn.Linear(3, 2))
+    ctl.context.wrap_model(torch.nn.Linear(3, 2))
+    with pytest.raises(RuntimeError, match="Old-format checkpoint cannot be loaded into a context with more than one model."):
+        ctl._load(d)
+    # no checkpoint file at all, or a file that is not a dict: nothing happens
+    ctl = _model_only_controller(torch.nn.Linear(3, 2))
+    before = loaded(ctl)
+    ctl._load(tmp_path / "nothing-here")
+    ctl._load(write(tmp_path / "f", [1, 2, 3], where=("checkpoint.pt",)))
+    assert all(torch.equal(v, before[k]) for k, v in loaded(ctl).items()) and ctl.batches_trained == 0
+
+
+ANCIENT = pathlib.Path("/root/reference/harness/tests/experiment/fixtures/ancient-checkpoints")
+
+
+@pytest.mark.skipif(not ANCIENT.exists(), reason="the reference tree is only present in the build container")
+@pytest.mark.parametrize("ckpt,trial_id,want", [
+    # reference test_legacy_checkpoint_loading (test_pytorch_trial.py:1262-1303) asserts exactly these six values
+    ("0.20.0-pytorch", 1, dict(trial_id=1, last_ckpt=1, step_id=1, last_val=0, batches_trained=1, epochs_trained=0)),
+    ("0.21.0-pytorch-main", 60, dict(trial_id=60, last_ckpt=1, step_id=0, last_val=1, batches_trained=1, epochs_trained=0)),
+    ("0.21.0-pytorch", 62, dict(trial_id=62, last_ckpt=1, step_id=0, last_val=1, batches_trained=1, epochs_trained=0)),
+])
+def test_checkpoints_from_old_reference_releases_load(ckpt, trial_id, want):
+    """The reference keeps checkpoints written by its old releases to pin this path; they are read in place (data
+    files only: state_dict.pth and the .pkl beside it), the one-weight model they hold is rebuilt here."""
+    saved = torch.load(ANCIENT / ckpt / "state_dict.pth", map_location="cpu", weights_only=False)["models_state_dict"][0]
+    ctl = _model_only_controller(torch.nn.Linear(1, 1, False), trial_id=trial_id)
+    ctl._load(ANCIENT / ckpt)
+    assert vars(ctl.state) == want and ctl.batches_trained == 1
+    assert torch.equal(ctl.context.models[0].weight, saved["weight"])
