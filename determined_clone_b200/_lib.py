@@ -78,6 +78,8 @@ SIGNATURES = {
     "dgs_clip_scale": [_vp, _i, _i64, _vp, _f, _vp],
     "dgs_step_adam": [_vp, _vp, _vp, _i, _vp, _i, _i64, ctypes.POINTER(AdamRange), _i, _vp, _f, _vp],
     "dgs_step_sgd": [_vp, _vp, _i, _vp, _i, _i64, ctypes.POINTER(SgdRange), _i, _vp, _f, _vp],
+    "dgs_step_adam_scaled": [_vp, _vp, _vp, _i, _vp, _i, _i64, ctypes.POINTER(AdamRange), _i, _vp, _f, _vp, _vp],
+    "dgs_step_sgd_scaled": [_vp, _vp, _i, _vp, _i, _i64, ctypes.POINTER(SgdRange), _i, _vp, _f, _vp, _vp],
     "dgs_timer_enable": [_i],
     "dgs_timer_read": [_vp, _i, ctypes.POINTER(_i)],
     "dgs_metric_pack": [ctypes.POINTER(ScalarRef), _i, _vp, _vp, _vp],

@@ -181,4 +181,16 @@ __device__ __forceinline__ float clip_coef(const float* __restrict__ total_norm,
   return (c > 1.0f) ? 1.0f : c;  // NaN stays NaN, as torch.clamp(max=1.0) does
 }
 
+// Gradients that still carry a GradScaler's loss scale S: inv_scale[0] = 1/S.  The factor every gradient element
+// is multiplied by is (1/S) * clip_coef(norm of the UNSCALED gradients), where total_norm[0] was measured on the
+// scaled buffer.  inv_scale == nullptr multiplies by exactly 1.0f everywhere, i.e. gives clip_coef() bit for bit.
+__device__ __forceinline__ float grad_coef(const float* __restrict__ total_norm, float max_norm,
+                                           const float* __restrict__ inv_scale) {
+  const float inv = (inv_scale != nullptr) ? *inv_scale : 1.0f;
+  if (total_norm == nullptr) return inv;
+  float c = max_norm / (*total_norm * inv + 1e-6f);
+  c = (c > 1.0f) ? 1.0f : c;
+  return c * inv;
+}
+
 }  // namespace dgs

@@ -101,10 +101,10 @@ template <typename P, typename G, int kUnroll>
 __global__ void __launch_bounds__(kThreads)
 adam_kernel(P* __restrict__ param, P* __restrict__ ea, P* __restrict__ eas, const G* __restrict__ grad,
             long long n, const __grid_constant__ Table<AdamHp> T,
-            const float* __restrict__ total_norm, float max_norm) {
+            const float* __restrict__ total_norm, float max_norm, const float* __restrict__ inv_scale) {
   constexpr int VEC = StepCfg<P, G, kUnroll>::VEC;
   constexpr int TILE = StepCfg<P, G, kUnroll>::TILE;
-  const float clip = clip_coef(total_norm, max_norm);
+  const float clip = grad_coef(total_norm, max_norm, inv_scale);
   const long long tiles = (n + TILE - 1) / TILE;
   for (long long t = blockIdx.x; t < tiles; t += gridDim.x) {
     const long long e0 = t * TILE;
@@ -152,10 +152,10 @@ template <typename P, typename G, bool HAS_BUF, int kUnroll>
 __global__ void __launch_bounds__(kThreads)
 sgd_kernel(P* __restrict__ param, P* __restrict__ buf, const G* __restrict__ grad, long long n,
            const __grid_constant__ Table<SgdHp> T, const float* __restrict__ total_norm,
-           float max_norm) {
+           float max_norm, const float* __restrict__ inv_scale) {
   constexpr int VEC = StepCfg<P, G, kUnroll>::VEC;
   constexpr int TILE = StepCfg<P, G, kUnroll>::TILE;
-  const float clip = clip_coef(total_norm, max_norm);
+  const float clip = grad_coef(total_norm, max_norm, inv_scale);
   const long long tiles = (n + TILE - 1) / TILE;
   for (long long t = blockIdx.x; t < tiles; t += gridDim.x) {
     const long long e0 = t * TILE;
@@ -227,11 +227,11 @@ int check_ranges(const char* who, const Range* ranges, int n_ranges, int64_t n) 
 
 template <typename P, typename G, int U>
 int launch_adam_u(void* param, void* ea, void* eas, const void* grad, int64_t n, const Table<AdamHp>& T,
-                  const float* tn, float max_norm, cudaStream_t st) {
+                  const float* tn, float max_norm, const float* inv, cudaStream_t st) {
   const long long tiles = (n + StepCfg<P, G, U>::TILE - 1) / StepCfg<P, G, U>::TILE;
   const int grid = tile_grid(tiles);
   timer_begin(st);
-  adam_kernel<P, G, U><<<grid, kThreads, 0, st>>>((P*)param, (P*)ea, (P*)eas, (const G*)grad, n, T, tn, max_norm);
+  adam_kernel<P, G, U><<<grid, kThreads, 0, st>>>((P*)param, (P*)ea, (P*)eas, (const G*)grad, n, T, tn, max_norm, inv);
   timer_end(st);
   DGS_LAUNCHED();
   return DGS_OK;
@@ -239,23 +239,23 @@ int launch_adam_u(void* param, void* ea, void* eas, const void* grad, int64_t n,
 
 template <typename P, typename G>
 int launch_adam(void* param, void* ea, void* eas, const void* grad, int64_t n, const Table<AdamHp>& T,
-                const float* tn, float max_norm, cudaStream_t st) {
+                const float* tn, float max_norm, const float* inv, cudaStream_t st) {
   // one vector per array per thread (4 loads in flight) measured best; DGS_STEP_UNROLL=2|4 re-runs the sweep
-  if (step_unroll() == 2) return launch_adam_u<P, G, 2>(param, ea, eas, grad, n, T, tn, max_norm, st);
-  if (step_unroll() == 4) return launch_adam_u<P, G, 4>(param, ea, eas, grad, n, T, tn, max_norm, st);
-  return launch_adam_u<P, G, 1>(param, ea, eas, grad, n, T, tn, max_norm, st);
+  if (step_unroll() == 2) return launch_adam_u<P, G, 2>(param, ea, eas, grad, n, T, tn, max_norm, inv, st);
+  if (step_unroll() == 4) return launch_adam_u<P, G, 4>(param, ea, eas, grad, n, T, tn, max_norm, inv, st);
+  return launch_adam_u<P, G, 1>(param, ea, eas, grad, n, T, tn, max_norm, inv, st);
 }
 
 template <typename P, typename G, int U>
 int launch_sgd_u(void* param, void* buf, const void* grad, int64_t n, const Table<SgdHp>& T,
-                 const float* tn, float max_norm, cudaStream_t st) {
+                 const float* tn, float max_norm, const float* inv, cudaStream_t st) {
   const long long tiles = (n + StepCfg<P, G, U>::TILE - 1) / StepCfg<P, G, U>::TILE;
   const int grid = tile_grid(tiles);
   timer_begin(st);
   if (buf != nullptr) {
-    sgd_kernel<P, G, true, U><<<grid, kThreads, 0, st>>>((P*)param, (P*)buf, (const G*)grad, n, T, tn, max_norm);
+    sgd_kernel<P, G, true, U><<<grid, kThreads, 0, st>>>((P*)param, (P*)buf, (const G*)grad, n, T, tn, max_norm, inv);
   } else {
-    sgd_kernel<P, G, false, U><<<grid, kThreads, 0, st>>>((P*)param, nullptr, (const G*)grad, n, T, tn, max_norm);
+    sgd_kernel<P, G, false, U><<<grid, kThreads, 0, st>>>((P*)param, nullptr, (const G*)grad, n, T, tn, max_norm, inv);
   }
   timer_end(st);
   DGS_LAUNCHED();
@@ -264,10 +264,10 @@ int launch_sgd_u(void* param, void* buf, const void* grad, int64_t n, const Tabl
 
 template <typename P, typename G>
 int launch_sgd(void* param, void* buf, const void* grad, int64_t n, const Table<SgdHp>& T,
-               const float* tn, float max_norm, cudaStream_t st) {
-  if (step_unroll() == 2) return launch_sgd_u<P, G, 2>(param, buf, grad, n, T, tn, max_norm, st);
-  if (step_unroll() == 4) return launch_sgd_u<P, G, 4>(param, buf, grad, n, T, tn, max_norm, st);
-  return launch_sgd_u<P, G, 1>(param, buf, grad, n, T, tn, max_norm, st);
+               const float* tn, float max_norm, const float* inv, cudaStream_t st) {
+  if (step_unroll() == 2) return launch_sgd_u<P, G, 2>(param, buf, grad, n, T, tn, max_norm, inv, st);
+  if (step_unroll() == 4) return launch_sgd_u<P, G, 4>(param, buf, grad, n, T, tn, max_norm, inv, st);
+  return launch_sgd_u<P, G, 1>(param, buf, grad, n, T, tn, max_norm, inv, st);
 }
 
 }  // namespace
@@ -277,6 +277,14 @@ extern "C" int dgs_step_adam(void* param, void* exp_avg, void* exp_avg_sq, int s
                              const void* grad, int grad_dtype, int64_t n,
                              const dgs_adam_range* ranges, int n_ranges, const float* total_norm,
                              float max_norm, dgs_stream_t stream) {
+  return dgs_step_adam_scaled(param, exp_avg, exp_avg_sq, state_dtype, grad, grad_dtype, n, ranges, n_ranges,
+                              total_norm, max_norm, nullptr, stream);
+}
+
+extern "C" int dgs_step_adam_scaled(void* param, void* exp_avg, void* exp_avg_sq, int state_dtype,
+                                    const void* grad, int grad_dtype, int64_t n,
+                                    const dgs_adam_range* ranges, int n_ranges, const float* total_norm,
+                                    float max_norm, const float* inv_scale, dgs_stream_t stream) {
   using namespace dgs;
   DGS_CHECK_ARG(n >= 0, "dgs_step_adam: n < 0");
   if (int rc = check_ranges("dgs_step_adam", ranges, n_ranges, n)) return rc;
@@ -304,7 +312,7 @@ extern "C" int dgs_step_adam(void* param, void* exp_avg, void* exp_avg_sq, int s
   cudaStream_t st = static_cast<cudaStream_t>(stream);
 #define DGS_ADAM_CASE(PD, PT, GD, GT) \
   if (state_dtype == PD && grad_dtype == GD) \
-    return launch_adam<PT, GT>(param, exp_avg, exp_avg_sq, grad, n, T, total_norm, max_norm, st);
+    return launch_adam<PT, GT>(param, exp_avg, exp_avg_sq, grad, n, T, total_norm, max_norm, inv_scale, st);
   DGS_ADAM_CASE(DGS_F32, float, DGS_F32, float)
   DGS_ADAM_CASE(DGS_F32, float, DGS_BF16, __nv_bfloat16)
   DGS_ADAM_CASE(DGS_F32, float, DGS_F16, __half)
@@ -319,6 +327,14 @@ extern "C" int dgs_step_adam(void* param, void* exp_avg, void* exp_avg_sq, int s
 extern "C" int dgs_step_sgd(void* param, void* momentum_buf, int state_dtype, const void* grad,
                             int grad_dtype, int64_t n, const dgs_sgd_range* ranges, int n_ranges,
                             const float* total_norm, float max_norm, dgs_stream_t stream) {
+  return dgs_step_sgd_scaled(param, momentum_buf, state_dtype, grad, grad_dtype, n, ranges, n_ranges, total_norm,
+                             max_norm, nullptr, stream);
+}
+
+extern "C" int dgs_step_sgd_scaled(void* param, void* momentum_buf, int state_dtype, const void* grad,
+                                   int grad_dtype, int64_t n, const dgs_sgd_range* ranges, int n_ranges,
+                                   const float* total_norm, float max_norm, const float* inv_scale,
+                                   dgs_stream_t stream) {
   using namespace dgs;
   DGS_CHECK_ARG(n >= 0, "dgs_step_sgd: n < 0");
   if (int rc = check_ranges("dgs_step_sgd", ranges, n_ranges, n)) return rc;
@@ -352,7 +368,7 @@ extern "C" int dgs_step_sgd(void* param, void* momentum_buf, int state_dtype, co
   cudaStream_t st = static_cast<cudaStream_t>(stream);
 #define DGS_SGD_CASE(PD, PT, GD, GT) \
   if (state_dtype == PD && grad_dtype == GD) \
-    return launch_sgd<PT, GT>(param, buf, grad, n, T, total_norm, max_norm, st);
+    return launch_sgd<PT, GT>(param, buf, grad, n, T, total_norm, max_norm, inv_scale, st);
   DGS_SGD_CASE(DGS_F32, float, DGS_F32, float)
   DGS_SGD_CASE(DGS_F32, float, DGS_BF16, __nv_bfloat16)
   DGS_SGD_CASE(DGS_F32, float, DGS_F16, __half)

@@ -180,6 +180,9 @@ class GradSyncEngine:
         self.fp16_compression = fp16_compression
         self.bucket_bytes, self.first_bucket_bytes = bucket_bytes, first_bucket_bytes
         self.scale = 1.0 / (self.world * (self.agg if self.average else 1))
+        # extra factor folded into the flatten kernel's scale: 1/S while an auto-AMP GradScaler's loss scale S is
+        # in the gradients (PyTorchTrialContext.backward sets it per window), else exactly 1.0
+        self.unscale = 1.0
         self.needs_acc = self.agg * self.bpps > 1
         self.sets: List[_FlatSet] = []
         self._where: Dict[int, Tuple[int, int]] = {}  # id(param) -> (set index, tensor index)
@@ -205,6 +208,7 @@ class GradSyncEngine:
         self.sharded = bool(sharded_step and comm is not None and self._fused_kind is not None and not fp16_compression
                             and ALIGN_ELEMS % (8 * self.world) == 0)
         self.last_total_norm: Optional[torch.Tensor] = None
+        self._inv_scale: Optional[torch.Tensor] = None
         # Several GPUs: norm pass 1 is run per bucket right behind the bucket's allreduce (aux stream, bucket still
         # in L2) once a clip_grad_norm_ request has been seen; switched off again if nobody asks for the norm.
         # One GPU: a single pass over the whole buffer at step time (fewer launches, nothing to hide behind).
@@ -377,7 +381,7 @@ class GradSyncEngine:
             segs[k].src = g.data_ptr()
         mode = (_lib.READ_ACC if state else 0) | (_lib.WRITE_WIRE if to_wire else 0)
         _lib.calls.dgs_flatten_accumulate(segs, len(tensors), fs.dtype_code, fs.acc_ptr, fs.wire_ptr, fs.wire_code, mode,
-                                          self.scale, _stream())
+                                          self.scale * self.unscale, _stream())
         flags = fs.in_wire if to_wire else fs.in_window
         for i in range(len(tensors)):
             flags[i] = True
@@ -475,7 +479,7 @@ class GradSyncEngine:
                 segs[k].src = grads[ti].data_ptr()
             mode = (_lib.READ_ACC if first_state else 0) | (_lib.WRITE_WIRE if to_wire else 0)
             _lib.calls.dgs_flatten_accumulate(
-                segs, len(b.tensors), fs.dtype_code, fs.acc_ptr, fs.wire_ptr, fs.wire_code, mode, self.scale, stream,
+                segs, len(b.tensors), fs.dtype_code, fs.acc_ptr, fs.wire_ptr, fs.wire_code, mode, self.scale * self.unscale, stream,
             )
         else:
             for read_acc in (False, True):
@@ -489,7 +493,7 @@ class GradSyncEngine:
                     seg.src, seg.dst_off, seg.numel = grads[ti].data_ptr(), t.off, t.numel
                 mode = (_lib.READ_ACC if read_acc else 0) | (_lib.WRITE_WIRE if to_wire else 0)
                 _lib.calls.dgs_flatten_accumulate(
-                    segs, len(idxs), fs.dtype_code, fs.acc_ptr, fs.wire_ptr, fs.wire_code, mode, self.scale, stream,
+                    segs, len(idxs), fs.dtype_code, fs.acc_ptr, fs.wire_ptr, fs.wire_code, mode, self.scale * self.unscale, stream,
                 )
         flags = fs.in_wire if to_wire else fs.in_window
         for ti in grads:
@@ -533,6 +537,7 @@ class GradSyncEngine:
         remaining allreduces and make the compute stream wait for them.  Returns, per set, which tensors
         received any gradient in this window."""
         present: List[List[bool]] = []
+        self.last_total_norm = None
         for si, fs in enumerate(self.sets):
             for bi, b in enumerate(fs.buckets):
                 grads = self._collect(fs, b)  # gradients produced outside context.backward()
@@ -551,7 +556,7 @@ class GradSyncEngine:
                         segs[k].src, segs[k].dst_off, segs[k].numel = fs.acc.data_ptr() + 4 * t.off, t.off, t.numel
                     _lib.calls.dgs_flatten_accumulate(
                         segs, len(late), _lib.F32, None, _ptr(fs.wire), _lib.dtype_code(fs.wire_dtype),
-                        _lib.WRITE_WIRE, self.scale, _stream(),
+                        _lib.WRITE_WIRE, self.scale * self.unscale, _stream(),
                     )
                     for ti in late:
                         fs.in_wire[ti] = True
@@ -583,6 +588,8 @@ class GradSyncEngine:
         finish_window()."""
         stream = _stream()
         untouched = self._wire_versions == [fs.wire._version for fs in self.sets]
+        if self.last_total_norm is not None and untouched:
+            return self.last_total_norm  # already measured in this window (AMP's inf check, then the clip function)
         eager_ok = (self.comm is not None and self._eager_norm and self._norm_slots_valid and untouched
                     and all(b.norm_done for fs in self.sets for b in fs.buckets))
         n_bucket_slots = self._partials.numel() - self._bucket_partials_base
@@ -707,10 +714,22 @@ class GradSyncEngine:
         _lib.calls.dgs_timer_read(buf, 1024, ctypes.byref(n))
         return [buf[i] / 1000.0 for i in range(n.value)]
 
-    def fused_step(self, present: List[List[bool]], clip: Optional[ClipRequest]) -> None:
-        """clip + optimizer.step() in one kernel per flat set (several if there are > 24 ranges)."""
+    def fused_step(self, present: List[List[bool]], clip: Optional[ClipRequest], inv_scale: Optional[torch.Tensor] = None) -> None:
+        """clip + optimizer.step() in one kernel per flat set (several if there are > 24 ranges).  `inv_scale`: fp32
+        device scalar 1/S when the wire still carries a GradScaler's loss scale; the kernel multiplies it in."""
         assert self._fused_kind is not None
-        self._fused_step(present, clip)
+        self._inv_scale = inv_scale
+        try:
+            self._fused_step(present, clip)
+        finally:
+            self._inv_scale = None
+
+    def _step_call(self, plain: Any, scaled: Any, *args: Any) -> None:
+        """args = everything up to and including max_norm; the stream goes last."""
+        if self._inv_scale is None:
+            self._launch_step(plain, *args, _stream())
+        else:
+            self._launch_step(scaled, *args, _ptr(self._inv_scale), _stream())
 
     def _launch_step(self, fn: Any, *args: Any) -> None:
         fn(*args)
@@ -782,7 +801,6 @@ class GradSyncEngine:
         return fs.group_runs
 
     def _fused_sgd(self, present: List[List[bool]], groups: List[Dict[str, Any]], norm_ptr: Any, max_norm: float) -> None:
-        stream = _stream()
         for fs, have in zip(self.sets, present):
             any_momentum = any(g["momentum"] != 0 for g in groups)
             buf, intact = self._adopt_state(fs, "momentum_buffer") if any_momentum else (None, True)
@@ -813,9 +831,10 @@ class GradSyncEngine:
                             | (_lib.SGD_FIRST_STEP if first else 0)
                             | (_lib.OPT_MAXIMIZE if g.get("maximize") else 0)
                         )
-                    self._launch_step(
-                        _lib.calls.dgs_step_sgd, _ptr(fs.param, lo * psz), _ptr(buf, lo * psz) if with_momentum else None,
-                        fs.dtype_code, _ptr(fs.wire, lo * wsz), fs.wire_code, hi - lo, arr, len(chunk), norm_ptr, max_norm, stream,
+                    self._step_call(
+                        _lib.calls.dgs_step_sgd, _lib.calls.dgs_step_sgd_scaled,
+                        _ptr(fs.param, lo * psz), _ptr(buf, lo * psz) if with_momentum else None,
+                        fs.dtype_code, _ptr(fs.wire, lo * wsz), fs.wire_code, hi - lo, arr, len(chunk), norm_ptr, max_norm,
                     )
             if buf is not None:
                 views = fs.state_views["momentum_buffer"]
@@ -834,7 +853,6 @@ class GradSyncEngine:
 
     def _fused_adam(self, present: List[List[bool]], groups: List[Dict[str, Any]], norm_ptr: Any, max_norm: float) -> None:
         steps = self._ensure_steps()
-        stream = _stream()
         base = 0
         decoupled = self._fused_kind == "adamw"
         for fs, have in zip(self.sets, present):
@@ -882,8 +900,9 @@ class GradSyncEngine:
                     r.flags = (_lib.ADAM_DECOUPLED_WD if use_decoupled else 0) | (_lib.OPT_MAXIMIZE if g.get("maximize") else 0)
                     if g["weight_decay"] == 0:
                         r.flags |= _lib.ADAM_DECOUPLED_WD  # p *= 1 exactly; skips the L2 add
-                self._launch_step(
-                    _lib.calls.dgs_step_adam, _ptr(fs.param, lo * psz), _ptr(m, lo * psz), _ptr(v, lo * psz), fs.dtype_code,
-                    _ptr(fs.wire, lo * wsz), fs.wire_code, hi - lo, arr, len(chunk), norm_ptr, max_norm, stream,
+                self._step_call(
+                    _lib.calls.dgs_step_adam, _lib.calls.dgs_step_adam_scaled,
+                    _ptr(fs.param, lo * psz), _ptr(m, lo * psz), _ptr(v, lo * psz), fs.dtype_code,
+                    _ptr(fs.wire, lo * wsz), fs.wire_code, hi - lo, arr, len(chunk), norm_ptr, max_norm,
                 )
             base += n_t

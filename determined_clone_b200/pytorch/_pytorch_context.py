@@ -41,6 +41,14 @@ class PyTorchExperimentalContext:
     def disable_auto_to_device(self) -> None:
         self._auto_to_device = False
 
+    def use_amp(self) -> None:
+        """Automatic mixed precision with a default GradScaler (reference _experimental.py:24-36): forward passes
+        of models wrapped AFTER this call run under autocast, backward() scales the loss, step_optimizer() unscales,
+        checks for inf/nan and steps through the scaler, and the controller updates the scaler at every
+        aggregation boundary.  Do not call wrap_scaler() yourself when using this."""
+        self._parent.wrap_scaler(torch.amp.GradScaler(self._parent.device.type))
+        self._auto_amp = True
+
 
 class _BufferSync:
     """DDP's broadcast_buffers=True: before every training forward, rank 0's module buffers (batch-norm
@@ -161,6 +169,12 @@ class PyTorchTrialContext(_PyTorchReducerContext):
         self._backward_calls = 0
         self._backward_calls_batch: Optional[int] = None
         self._comm: Optional[Comm] = None
+        # auto-AMP: host copy of the GradScaler's loss scale S, refreshed by an asynchronous read after every
+        # scaler.update() (see _loss_scale_on_host)
+        self._amp_scale_host: Optional[float] = None
+        self._amp_scale_pinned: Optional[torch.Tensor] = None
+        self._amp_scale_event: Optional[torch.cuda.Event] = None
+        self._amp_scale_used = 1.0
 
     # ---- device / communicator ----------------------------------------------------------------
     def _init_device(self) -> torch.device:
@@ -265,8 +279,47 @@ class PyTorchTrialContext(_PyTorchReducerContext):
             self._wrapped_models[model] = model
         model_id = len(self.models)
         self._main_model.__setattr__(f"model_{model_id}", model)
+        if self.experimental._auto_amp:
+            model = self.autocast_forward_pass(model)
         self.models.append(model)
         return model
+
+    def autocast_forward_pass(self, to_wrap: nn.Module) -> nn.Module:
+        """experimental.use_amp(): run the module's forward under autocast and hand fp16 outputs back as fp32, so
+        that loss code needs no autocast region of its own (reference _pytorch_context.py:235-282, which builds a
+        proxy subclass around the module).  Here the module object stays the one the user made -- attributes,
+        state_dict keys and parameter identity are untouched -- and only its bound `forward` is replaced."""
+        inner = to_wrap.forward
+        device_type = self.device.type
+        warned: Set[type] = set()
+
+        def widen(out: Any) -> Any:
+            if isinstance(out, torch.Tensor):
+                return out.float() if out.dtype == torch.float16 else out
+            if isinstance(out, dict):
+                plain = {k: widen(v) for k, v in out.items()}
+                if type(out) is dict:
+                    return plain
+                try:  # dict subclasses with keyword constructors (transformers' ModelOutput) keep their type
+                    return type(out)(**plain)
+                except Exception:
+                    return plain
+            if isinstance(out, tuple) and hasattr(out, "_fields"):
+                return type(out)(*(widen(v) for v in out))
+            if isinstance(out, (list, tuple)):
+                return type(out)(widen(v) for v in out)
+            if type(out) not in warned:
+                warned.add(type(out))
+                logger.warning(f"Unexpected type '{type(out).__name__}' outputted by model in experimental AMP mode.")
+            return out
+
+        def forward(*args: Any, **kwargs: Any) -> Any:
+            with torch.autocast(device_type=device_type):
+                out = inner(*args, **kwargs)
+            return widen(out)
+
+        to_wrap.forward = forward  # type: ignore
+        return to_wrap
 
     def wrap_optimizer(
         self,
@@ -361,7 +414,11 @@ class PyTorchTrialContext(_PyTorchReducerContext):
             self._backward_calls_batch, self._backward_calls = self._current_batch_idx, 0
         self._backward_calls += 1
         boundary = self._should_communicate_and_update() if self._engines else False
+        unscale = 1.0 / self._loss_scale_on_host() if self._auto_amp_active() else 1.0
         for eng in self._engines.values():
+            # auto-AMP: 1/S rides on the 1/(N*A) factor of the flatten kernel, so the wire holds true gradients
+            # and GradScaler.unscale_'s read+write pass over every gradient never runs
+            eng.unscale = unscale if self._prefolds(eng) else 1.0
             eng.begin_pass(final=boundary and self._backward_calls >= eng.bpps)
         try:
             loss.backward(gradient=gradient, retain_graph=retain_graph, create_graph=create_graph)  # type: ignore
@@ -379,6 +436,119 @@ class PyTorchTrialContext(_PyTorchReducerContext):
         for p in parameters:
             if p.grad is not None:
                 p.grad.data.div_(divisor_value)
+
+    # ---- AMP ------------------------------------------------------------------------------------------
+    def _auto_amp_active(self) -> bool:
+        return bool(self._scaler) and self.experimental._auto_amp and self._scaler.is_enabled()
+
+    def _prefolds(self, eng: Any) -> bool:
+        """Whether this engine's gradients are unscaled by the flatten kernel (auto-AMP + a step we fuse)."""
+        return (self._auto_amp_active() and eng.can_fuse() and not eng.sharded
+                and all(fs.wire_dtype == fs.dtype for fs in eng.sets))
+
+    def _loss_scale_on_host(self) -> float:
+        """S of the auto-AMP scaler, without a device round trip in steady state: S only changes in
+        scaler.update(), after which _scaler_updated() starts an asynchronous read into pinned memory; by the next
+        boundary backward pass (a whole forward/backward later) that read is long complete.  step_optimizer()
+        cross-checks the value against the device copy in the read-back it does anyway."""
+        if self._amp_scale_event is not None:
+            self._amp_scale_event.synchronize()
+            self._amp_scale_host = float(self._amp_scale_pinned[0])  # type: ignore
+            self._amp_scale_event = None
+        elif self._amp_scale_host is None:
+            self._amp_scale_host = float(self._scaler.get_scale())  # first window: one blocking read
+        self._amp_scale_used = self._amp_scale_host
+        return self._amp_scale_host
+
+    def _scaler_updated(self) -> None:
+        """The controller calls this right after scaler.update() (reference _pytorch_trial.py:903-910)."""
+        scale = getattr(self._scaler, "_scale", None)
+        if not self._auto_amp_active() or scale is None or not scale.is_cuda:
+            self._amp_scale_host = None
+            return
+        if self._amp_scale_pinned is None:
+            self._amp_scale_pinned = torch.zeros(1, dtype=torch.float32).pin_memory()
+        self._amp_scale_pinned.copy_(scale.reshape(1), non_blocking=True)
+        self._amp_scale_event = torch.cuda.Event()
+        self._amp_scale_event.record()
+
+    def _amp_fused_step(self, eng: Any, optimizer: Any, parameters: List[Any], present: Any, clip_grads: Any,
+                        scaler: Any, auto_zero_grads: bool) -> None:
+        """step_optimizer with a GradScaler when the optimizer step is ours (reference :899-921: unscale_, the
+        user's clip function, scaler.step -> optimizer.step unless an inf/nan was found).  Same observable
+        protocol as torch's -- per-optimizer stage, found_inf recorded for scaler.update(), ONE host read per
+        step to decide whether to step (torch: found_inf.item() in GradScaler._maybe_opt_step) -- but the
+        unscale never runs as a pass of its own and clip + step stay one kernel:
+
+        * auto-AMP (experimental.use_amp): the flatten kernel already divided by S; the inf/nan check is the
+          L2-norm pass (non-finite norm <=> some element is inf/nan), which is also the clip norm.
+        * a scaler passed to step_optimizer(): gradients are still scaled.  If the user's clip function called
+          scaler.unscale_() itself, torch has unscaled the views in place and recorded found_inf; otherwise the
+          norm pass is the check and the step kernel multiplies by 1/S (dgs_step_*_scaled)."""
+        import math
+
+        from torch.amp.grad_scaler import OptState
+
+        scaler._check_scale_growth_tracker("step")
+        st = scaler._per_optimizer_states[id(optimizer)]
+        if st["stage"] is OptState.STEPPED:
+            raise RuntimeError("step() has already been called since the last update().")
+        prefolded = scaler is self._scaler and self._prefolds(eng)
+        clip_req: Optional[_gradsync.ClipRequest] = None
+        inv_scale: Optional[torch.Tensor] = None
+        found: Optional[bool] = None
+        materialized = False
+
+        if prefolded:
+            norm_val, s_dev = torch.stack([eng.total_norm(), scaler._scale.reshape(())]).tolist()
+            if s_dev != self._amp_scale_used:
+                # S changed behind the controller's back (a manual update() or load_state_dict()): rescale once
+                fix = self._amp_scale_used / s_dev
+                for fs in eng.sets:
+                    fs.wire.mul_(fix)
+                eng._norm.mul_(fix)
+                eng._wire_versions = [fs.wire._version for fs in eng.sets]
+                norm_val *= fix
+                self._amp_scale_host = None
+            found = not math.isfinite(norm_val)
+            st["found_inf_per_device"] = {self.device: torch.full((), float(found), dtype=torch.float32, device=self.device)}
+            st["stage"] = OptState.UNSCALED  # what the user's function would see after the reference's unscale_
+
+        if clip_grads is not None or not auto_zero_grads:
+            eng.materialize_grads(present)
+            materialized = True
+        if clip_grads is not None:
+            if not prefolded and self._scaler and self.experimental._auto_amp:
+                self._scaler.unscale_(optimizer)
+            clip_req = _run_clip(eng, clip_grads, parameters, defer=True)
+            _fold_back_replaced_grads(eng, present)
+
+        if found is None and st["stage"] is OptState.UNSCALED:
+            # torch unscaled the gradient views in place and checked them
+            found = bool(sum(v.item() for v in st["found_inf_per_device"].values()))
+        elif found is None:
+            if clip_req is not None and clip_req.max_norm is not None:
+                # clip_grad_norm_ on still-scaled gradients: honoured literally (max_norm against the scaled norm)
+                _apply_clip_now(eng, clip_req.max_norm)
+                clip_req = None
+                norm = eng._norm[0]
+            else:
+                norm = eng.total_norm()
+            found = not math.isfinite(float(norm))
+            st["found_inf_per_device"] = {self.device: torch.full((), float(found), dtype=torch.float32, device=self.device)}
+            inv_scale = scaler._scale.double().reciprocal().float()
+
+        if not found:
+            eng.fused_step(present, clip_req, inv_scale=inv_scale)
+        else:
+            # skipped.  A whole-buffer clip with a non-finite coefficient has also turned the alignment gaps between
+            # tensors into NaN; the flatten kernel never rewrites those and the norm pass reads them
+            for fs in eng.sets:
+                fs.wire.zero_()
+        st["stage"] = OptState.STEPPED
+        if auto_zero_grads and materialized:
+            eng.clear_grads()
+        eng.reset_window()
 
     # ---- optimizer step -----------------------------------------------------------------------------
     def step_optimizer(
@@ -413,6 +583,10 @@ class PyTorchTrialContext(_PyTorchReducerContext):
         if eng.sharded:
             return self._sharded_step(eng, optimizer, parameters, present, clip_grads, scaler)
         aliased = all(fs.wire_dtype == fs.dtype for fs in eng.sets)
+        if scaler is not None and not scaler.is_enabled():
+            scaler = None  # a disabled GradScaler is a pass-through in torch too
+        if scaler is not None and eng.can_fuse() and (aliased or clip_grads is None):
+            return self._amp_fused_step(eng, optimizer, parameters, present, clip_grads, scaler, auto_zero_grads)
         fused = eng.can_fuse() and scaler is None and (aliased or clip_grads is None)
 
         clip_req: Optional[_gradsync.ClipRequest] = None
@@ -498,6 +672,16 @@ def _fold_back_replaced_grads(eng: _gradsync.GradSyncEngine, present: List[List[
                 t.param.grad = view
 
 
+def _apply_clip_now(eng: _gradsync.GradSyncEngine, max_norm: float) -> None:
+    """g *= min(max_norm / (norm + 1e-6), 1) over the wire, with the norm the engine measured last."""
+    for fs in eng.sets:
+        _lib.calls.dgs_clip_scale(
+            _gradsync._ptr(fs.wire), _lib.dtype_code(fs.wire_dtype), fs.total, _gradsync._ptr(eng._norm),
+            float(max_norm), _gradsync._stream(),
+        )
+    eng.last_total_norm = None  # the buffer changed under the cached value
+
+
 def _run_clip(eng: _gradsync.GradSyncEngine, clip_grads: Callable, parameters: List[Any], defer: bool) -> _gradsync.ClipRequest:
     """Run the user's clip function with torch's clip_grad_norm_ internals redirected to the kernels.
 
@@ -528,11 +712,7 @@ def _run_clip(eng: _gradsync.GradSyncEngine, clip_grads: Callable, parameters: L
             if defer:
                 req.max_norm = float(max_norm)  # fused into the optimizer kernel
             else:
-                for fs in eng.sets:
-                    _lib.calls.dgs_clip_scale(
-                        _gradsync._ptr(fs.wire), _lib.dtype_code(fs.wire_dtype), fs.total, _gradsync._ptr(eng._norm),
-                        float(max_norm), _gradsync._stream(),
-                    )
+                _apply_clip_now(eng, max_norm)
             return
         real_clip(params, max_norm, total, foreach)
 

@@ -243,6 +243,7 @@ class _PyTorchTrialController:
         training_metrics = self.trial.train_batch(batch=batch, epoch_idx=epoch_idx, batch_idx=batch_idx)
         if self._should_update_scaler():
             self.context._scaler.update()
+            self.context._scaler_updated()
         if isinstance(training_metrics, torch.Tensor):
             training_metrics = {"loss": training_metrics}
         for lr_scheduler in self.context.lr_schedulers:

@@ -183,6 +183,23 @@ int dgs_step_sgd(void* param, void* momentum_buf, int state_dtype, const void* g
                  int64_t n, const dgs_sgd_range* ranges, int n_ranges, const float* total_norm,
                  float max_norm, dgs_stream_t stream);
 
+/* The same two steps for gradients that still carry a torch.amp.GradScaler loss scale S (AMP, reference
+ * H/pytorch/_pytorch_context.py:798-799 scales the loss, :899-911 `scaler.unscale_` + `scaler.step`).  Replaces the
+ * separate unscale pass of GradScaler.unscale_ (torch/amp/grad_scaler.py: _amp_foreach_non_finite_check_and_unscale_,
+ * one read + one write of every gradient): inv_scale[0] = 1/S is a device scalar, every gradient element is
+ * multiplied by it on the fly, and total_norm[0] is expected to be the norm of the SCALED buffer (the clip
+ * coefficient is computed from total_norm[0] * inv_scale[0]).  The inf/nan check that decides whether the step
+ * runs at all is the caller's: a non-finite total_norm[0] of the scaled buffer means "skip", exactly when some
+ * element is inf/nan (or when the fp32 sum of squares overflowed, norm > 1.8e19).  inv_scale == NULL is
+ * dgs_step_adam / dgs_step_sgd bit for bit. */
+int dgs_step_adam_scaled(void* param, void* exp_avg, void* exp_avg_sq, int state_dtype, const void* grad,
+                         int grad_dtype, int64_t n, const dgs_adam_range* ranges, int n_ranges,
+                         const float* total_norm, float max_norm, const float* inv_scale,
+                         dgs_stream_t stream);
+int dgs_step_sgd_scaled(void* param, void* momentum_buf, int state_dtype, const void* grad, int grad_dtype,
+                        int64_t n, const dgs_sgd_range* ranges, int n_ranges, const float* total_norm,
+                        float max_norm, const float* inv_scale, dgs_stream_t stream);
+
 /* Device-side timing of the optimizer kernels (grad-sync us/step without host noise): while enabled, every
  * dgs_step_adam / dgs_step_sgd launch is bracketed by CUDA events recorded inside the call, on the stream it
  * is launched on.  dgs_timer_read synchronises with the last recorded launch, writes the elapsed microseconds

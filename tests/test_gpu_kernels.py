@@ -235,6 +235,56 @@ def test_step_sgd_ranges(lib, pdt, gdt, first, nesterov):
     np.testing.assert_array_equal(host(p)[10000:12288], ph[10000:12288])
 
 
+@pytest.mark.parametrize("gdt", ["float32", "float16"])
+@pytest.mark.parametrize("clip", [None, 0.3])
+def test_step_scaled_entries_equal_the_plain_step_on_unscaled_gradients(lib, gdt, clip):
+    """dgs_step_*_scaled on gradients that carry a loss scale S, with inv_scale = 1/S and the norm of the SCALED
+    buffer, against dgs_step_* on the same gradients without the scale.  S is a power of two (as a GradScaler's
+    always is), so scaling commutes with every rounding on the way and the results must be bit-identical."""
+    rng = np.random.default_rng(11)
+    n, S = 40000 + 3, 1024.0
+    g_true = dev(rng.standard_normal(n) * 0.01, gdt)
+    g_scaled = (g_true.float() * S).to(TD[gdt])
+    assert torch.equal(g_scaled.float() / S, g_true.float())  # nothing overflowed or went subnormal
+    inv = torch.tensor([1.0 / S], device="cuda")
+    partials = torch.zeros(L.calls.dgs_l2norm_grid(n), device="cuda")
+    norms = {}
+    for key, g in (("true", g_true), ("scaled", g_scaled)):
+        norms[key] = torch.zeros(1, device="cuda")
+        L.calls.dgs_l2norm(ptr(g), CODE[gdt], n, ptr(partials), ptr(norms[key]), stream())
+    torch.cuda.synchronize()
+    assert float(norms["scaled"]) == float(norms["true"]) * S
+    nptr = (lambda k: ptr(norms[k])) if clip is not None else (lambda k: None)
+
+    a_specs = [dict(begin=0, end=16384, lr=1e-3, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1, step=3),
+               dict(begin=16384, end=n, lr=2e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.01, step=5, decoupled=False)]
+    s_specs = [dict(begin=0, end=16384, lr=0.1, momentum=0.9, weight_decay=5e-4, nesterov=True),
+               dict(begin=16384, end=n, lr=0.05, momentum=0.8, dampening=0.1, weight_decay=0.0)]
+    p0, m0, v0 = dev(rng.standard_normal(n) * 0.5), dev(rng.standard_normal(n) * 0.01), dev(np.abs(rng.standard_normal(n)) * 1e-3)
+    out = {}
+    for key in ("plain", "scaled"):
+        p, m, v = p0.clone(), m0.clone(), v0.clone()
+        q, b = p0.clone(), m0.clone()
+        if key == "plain":
+            L.calls.dgs_step_adam(ptr(p), ptr(m), ptr(v), L.F32, ptr(g_true), CODE[gdt], n, adam_ranges(a_specs), 2, nptr("true"), clip or 0.0, stream())
+            L.calls.dgs_step_sgd(ptr(q), ptr(b), L.F32, ptr(g_true), CODE[gdt], n, sgd_ranges(s_specs), 2, nptr("true"), clip or 0.0, stream())
+        else:
+            L.calls.dgs_step_adam_scaled(ptr(p), ptr(m), ptr(v), L.F32, ptr(g_scaled), CODE[gdt], n, adam_ranges(a_specs), 2,
+                                         nptr("scaled"), clip or 0.0, ptr(inv), stream())
+            L.calls.dgs_step_sgd_scaled(ptr(q), ptr(b), L.F32, ptr(g_scaled), CODE[gdt], n, sgd_ranges(s_specs), 2,
+                                        nptr("scaled"), clip or 0.0, ptr(inv), stream())
+        torch.cuda.synchronize()
+        out[key] = [t.clone() for t in (p, m, v, q, b)]
+    for a, b in zip(out["plain"], out["scaled"]):
+        assert torch.equal(a, b)
+    assert not torch.equal(out["plain"][0], p0) and not torch.equal(out["plain"][3], p0)  # and something did happen
+    # inv_scale == NULL is the plain entry
+    p, m, v = p0.clone(), m0.clone(), v0.clone()
+    L.calls.dgs_step_adam_scaled(ptr(p), ptr(m), ptr(v), L.F32, ptr(g_true), CODE[gdt], n, adam_ranges(a_specs), 2, nptr("true"), clip or 0.0, None, stream())
+    torch.cuda.synchronize()
+    assert torch.equal(p, out["plain"][0]) and torch.equal(v, out["plain"][2])
+
+
 def test_step_sgd_without_momentum_needs_no_buffer(lib):
     rng = np.random.default_rng(7)
     n = 9000
