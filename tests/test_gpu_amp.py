@@ -6,6 +6,7 @@ scaler.update at every aggregation boundary) is written out below with plain tor
 repo's context, which folds 1/S into its kernels instead of running GradScaler.unscale_ as a pass of its own.
 Scale values and Adam's step counters are integers / powers of two: exact.  Parameters: fp32 tolerance of the
 other parity tests."""
+import contextlib
 import copy
 import math
 
@@ -246,3 +247,78 @@ def test_scaler_passed_to_step_optimizer(lib, kind, mode):
         runs.append(out)
     assert_same_run(runs[0], runs[1])
     assert min(runs[1]["scale"]) < 1024.0 or max(runs[1]["scale"]) > 1024.0
+
+
+# ---- two slots: an inf on ONE rank must make EVERY rank skip (the check runs on the all-reduced gradients) ---------
+def _free_port() -> int:
+    import socket
+
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _amp_rank_main(rank: int, size: int, ports, init_port: int) -> None:
+    import torch.distributed as dist
+
+    from determined_clone_b200 import core
+
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{init_port}", rank=rank, world_size=size,
+                            device_id=torch.device("cuda", rank))
+    dctx = core.DistributedContext(rank=rank, size=size, local_rank=rank, local_size=size, cross_rank=0, cross_size=1,
+                                   pub_port=ports[0], pull_port=ports[1])
+    try:
+        agg, clip = 2, 0.5
+        torch.manual_seed(5)
+        base = Net()
+        g = torch.Generator().manual_seed(300 + rank)  # every rank trains on its own batches
+        data = [(torch.randn(8, 12, generator=g).cuda(), torch.randn(8, 5, generator=g).cuda()) for _ in range(8 * agg)]
+        if rank == 1:
+            data[4][0][0, 0] = float("inf")  # first micro-batch of the third window, on rank 1 only
+
+        # reference protocol over torch DDP (reference _pytorch_context.py:295-296, :802-816 no_sync off the boundary)
+        ref_model = torch.nn.parallel.DistributedDataParallel(copy.deepcopy(base).cuda())
+        ref_opt, ref_scaler = make_opt("adamw", ref_model), new_scaler()
+        ref = {"params": [], "scale": [], "adam_steps": [], "norms": []}
+        params = [p for grp in ref_opt.param_groups for p in grp["params"]]
+        for i, (x, y) in enumerate(data):
+            boundary = (i + 1) % agg == 0
+            with contextlib.nullcontext() if boundary else ref_model.no_sync():
+                ref_scaler.scale(torch.nn.functional.mse_loss(ref_model(x), y)).backward()
+            if not boundary:
+                continue
+            for p in params:
+                p.grad.div_(float(agg))
+            ref_scaler.unscale_(ref_opt)
+            ref["norms"].append(float(torch.nn.utils.clip_grad_norm_(params, clip)))
+            ref_scaler.step(ref_opt)
+            ref_opt.zero_grad()
+            ref_scaler.update()
+            snapshot(ref_model, ref_opt, ref_scaler, ref)
+
+        out = {"params": [], "scale": [], "adam_steps": [], "norms": []}
+        ctx = pytorch.PyTorchTrialContext(distributed=dctx, hparams={"global_batch_size": 16}, slots_per_trial=size,
+                                          aggregation_frequency=agg)
+        trial = AmpTrial(ctx, base, "adamw", clip, out)
+        ctl = pytorch._PyTorchTrialController(trial, ctx, max_length=len(data), reporting_period=len(data))
+        for i, batch in enumerate(data):
+            ctx._current_batch_idx = i
+            ctl._train_batch(batch, 0, i)
+            if (i + 1) % agg == 0:
+                snapshot(trial.model, trial.opt, ctx._scaler, out)
+        out["norms"] = [float(v) for v in out["norms"]]
+        assert ref["scale"][:3] == [1024.0, 2048.0, 1024.0] and ref["adam_steps"][2] == ref["adam_steps"][1]  # 3rd step skipped
+        assert_same_run(out, ref)
+        ctx.close()
+    finally:
+        dctx.close()
+        dist.destroy_process_group()
+
+
+def test_two_slot_auto_amp_matches_torch_ddp_with_grad_scaler(lib):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run with gpurun --gpus 2)")
+    import torch.multiprocessing as mp
+
+    mp.spawn(_amp_rank_main, args=(2, (_free_port(), _free_port()), _free_port()), nprocs=2, join=True)
