@@ -352,17 +352,17 @@ class PyTorchTrialContext(_PyTorchReducerContext):
                 "only one optimizer's flat buffers"
             )
         self._owned_params |= mine
-        if True:  # managed or not (Trainer / Core API use): the same engine carries the step
-            self._engines[optimizer] = _gradsync.GradSyncEngine(
-                optimizer,
-                device=self.device,
-                comm=self._get_comm(),
-                aggregation_frequency=self._aggregation_frequency,
-                average_aggregated_gradients=bool(average_aggregated_gradients),
-                backward_passes_per_step=backward_passes_per_step,
-                fp16_compression=bool(fp16_compression) and self.distributed.size > 1,
-                sharded_step=((self._exp_conf or {}).get("optimizations", {}) or {}).get("sharded_step"),
-            )
+        # managed or not (Trainer / Core API use): the same engine carries the step
+        self._engines[optimizer] = _gradsync.GradSyncEngine(
+            optimizer,
+            device=self.device,
+            comm=self._get_comm(),
+            aggregation_frequency=self._aggregation_frequency,
+            average_aggregated_gradients=bool(average_aggregated_gradients),
+            backward_passes_per_step=backward_passes_per_step,
+            fp16_compression=bool(fp16_compression) and self.distributed.size > 1,
+            sharded_step=((self._exp_conf or {}).get("optimizations", {}) or {}).get("sharded_step"),
+        )
         self.optimizers.append(optimizer)
         return optimizer
 

@@ -623,3 +623,50 @@ def test_checkpoints_from_old_reference_releases_load(ckpt, trial_id, want):
     ctl._load(ANCIENT / ckpt)
     assert vars(ctl.state) == want and ctl.batches_trained == 1
     assert torch.equal(ctl.context.models[0].weight, saved["weight"])
+
+
+def test_autocast_forward_wrapper_keeps_the_module_and_widens_fp16_outputs():
+    """experimental.use_amp() before wrap_model (reference _pytorch_context.py:235-282, :307-308): the model the user
+    gets back is their own module (attributes, state_dict keys), forward runs under autocast, and fp16 tensors in
+    the output -- bare, or inside dicts / lists / tuples / named tuples -- come back as fp32."""
+    import collections
+
+    Pair = collections.namedtuple("Pair", ["half", "full"])
+
+    class Out(dict):
+        def __init__(self, **kw):
+            super().__init__(**kw)
+
+    class M(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.lin = torch.nn.Linear(3, 2)
+            self.tag = "mine"
+            self.autocast_seen = []
+
+        def forward(self, x, kind):
+            self.autocast_seen.append(torch.is_autocast_enabled("cpu"))
+            h, f = torch.ones(2, dtype=torch.float16), torch.ones(2, dtype=torch.float64)
+            return {"bare": h, "dict": {"h": h, "f": f}, "list": [h, f], "tuple": (h, 3), "named": Pair(h, f), "sub": Out(h=h)}[kind]
+
+    ctx = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 4})
+    ctx.experimental.use_amp()
+    assert ctx.experimental._auto_amp and ctx._scaler is not None
+    m = M()
+    wrapped = ctx.wrap_model(m)
+    assert wrapped is m and wrapped.tag == "mine" and list(wrapped.state_dict()) == ["lin.weight", "lin.bias"]
+    x = torch.zeros(1, 3)
+    assert wrapped(x, "bare").dtype == torch.float32
+    d = wrapped(x, "dict")
+    assert d["h"].dtype == torch.float32 and d["f"].dtype == torch.float64  # only fp16 is widened
+    lst, tup, named, sub = wrapped(x, "list"), wrapped(x, "tuple"), wrapped(x, "named"), wrapped(x, "sub")
+    assert isinstance(lst, list) and lst[0].dtype == torch.float32
+    assert isinstance(tup, tuple) and tup[0].dtype == torch.float32 and tup[1] == 3
+    assert isinstance(named, Pair) and named.half.dtype == torch.float32 and named.full.dtype == torch.float64
+    assert isinstance(sub, Out) and sub["h"].dtype == torch.float32
+    assert all(m.autocast_seen)
+    # a model wrapped BEFORE use_amp() is left alone (the reference checks the flag inside wrap_model)
+    ctx2 = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 4})
+    m2 = ctx2.wrap_model(M())
+    ctx2.experimental.use_amp()
+    assert m2(x, "bare").dtype == torch.float16 and not any(m2.autocast_seen)
