@@ -37,9 +37,15 @@ class PyTorchExperimentalContext:
         self._parent = parent
         self._auto_amp = False
         self._auto_to_device = True
+        self._data_repro_checks_disabled = False
 
     def disable_auto_to_device(self) -> None:
         self._auto_to_device = False
+
+    def disable_dataset_reproducibility_checks(self) -> None:
+        """Allow build_*_data_loader to return a plain torch DataLoader (reference _experimental.py:38-61); sharding
+        and resuming at the right batch are then the user's responsibility."""
+        self._data_repro_checks_disabled = True
 
     def use_amp(self) -> None:
         """Automatic mixed precision with a default GradScaler (reference _experimental.py:24-36): forward passes
@@ -161,6 +167,11 @@ class PyTorchTrialContext(_PyTorchReducerContext):
         self._fp16_compression_default = False
         self._average_aggregated_gradients_default = True
         self._is_pre_trainer = False
+        self._enable_tensorboard_logging = bool(enable_tensorboard_logging)
+        self._stop_requested = False
+        self._tensorboard_path: Any = None
+        self._tbd_writer: Any = None
+        self._determined_profiler: Any = None
 
         # grad-sync state
         self._engines: Dict[torch.optim.Optimizer, _gradsync.GradSyncEngine] = {}
@@ -228,7 +239,91 @@ class PyTorchTrialContext(_PyTorchReducerContext):
         return self._steps_completed
 
     def get_enable_tensorboard_logging(self) -> bool:
-        return False  # TensorBoard upload belongs to the control plane; metrics go to on_report
+        return self._enable_tensorboard_logging
+
+    def set_enable_tensorboard_logging(self, enable_tensorboard_logging: bool) -> None:
+        """Whether the controller also writes the reported metrics as TensorBoard scalars (reference :220-229).
+        Uploading the files is the control plane's job and does not exist here; they stay in
+        get_tensorboard_path()."""
+        if not isinstance(enable_tensorboard_logging, bool):
+            raise AssertionError("enable_tensorboard_logging must be a boolean")
+        self._enable_tensorboard_logging = enable_tensorboard_logging
+
+    def get_stop_requested(self) -> bool:
+        return self._stop_requested
+
+    def set_stop_requested(self, stop_requested: bool) -> None:
+        """Ask the training loop to stop after the current batch (reference :200-218; the controller checks it where
+        the reference checks preemption, _pytorch_trial.py:521-525)."""
+        if not isinstance(stop_requested, bool):
+            raise AssertionError("stop_requested must be a boolean")
+        if stop_requested:
+            logger.info("A trial stoppage has requested. The trial will be stopped at the end of the current step.")
+        self._stop_requested = stop_requested
+
+    def get_experiment_id(self) -> int:
+        return int(getattr(getattr(self._core, "train", None), "_exp_id", None) or _info_field("experiment_id"))
+
+    def get_trial_id(self) -> int:
+        return int(getattr(getattr(self._core, "train", None), "_trial_id", None) or _info_field("trial_id"))
+
+    def get_tensorboard_path(self) -> Any:
+        """Directory for TensorBoard files (reference :993-997 asks the core context; without one: a per-trial
+        directory under DET_TENSORBOARD_PATH or the system temp dir)."""
+        import os
+        import pathlib
+        import tempfile
+
+        train = getattr(self._core, "train", None)
+        if train is not None and hasattr(train, "get_tensorboard_path"):
+            return train.get_tensorboard_path()
+        if self._tensorboard_path is None:
+            base = os.environ.get("DET_TENSORBOARD_PATH") or os.path.join(tempfile.gettempdir(), "determined-tensorboard")
+            self._tensorboard_path = pathlib.Path(base) / f"trial-{self.get_trial_id()}" / f"rank-{self.distributed.rank}"
+            self._tensorboard_path.mkdir(parents=True, exist_ok=True)
+        return self._tensorboard_path
+
+    def get_tensorboard_writer(self) -> Any:
+        """A torch.utils.tensorboard.SummaryWriter on get_tensorboard_path(), created on first use (:999-1030)."""
+        if self._tbd_writer is None:
+            from torch.utils.tensorboard import SummaryWriter
+
+            self._tbd_writer = SummaryWriter(str(self.get_tensorboard_path()))
+        return self._tbd_writer
+
+    def _maybe_reset_tbd_writer(self) -> None:
+        """Close the writer so that its event file is complete; the next get_tensorboard_writer() opens a new one."""
+        if self._tbd_writer is not None:
+            self._tbd_writer.close()
+            self._tbd_writer = None
+
+    def set_profiler(self, *args: Any, **kwargs: Any) -> None:
+        """torch.profiler.profile(*args, **kwargs) with on_trace_ready pointed at the TensorBoard directory; the
+        training loop enters it and calls .step() after every batch (reference :424-458, _pytorch_trial.py:891-901)."""
+        self.profiler = torch.profiler.profile(
+            *args, on_trace_ready=torch.profiler.tensorboard_trace_handler(str(self.get_tensorboard_path())), **kwargs
+        )
+
+    def _set_determined_profiler(self, prof: Any) -> None:
+        self._determined_profiler = prof
+
+    @contextlib.contextmanager
+    def _record_timing(self, metric_name: str, accumulate: bool = False) -> Iterator[None]:
+        """Host-clock timing regions of the reference's system profiler (:464-470); a pass-through unless a profiler
+        object with record_timing() was attached.  Device-side timing of the optimizer kernels is dgs_timer_*."""
+        if not self._determined_profiler:
+            yield
+            return
+        with self._determined_profiler.record_timing(metric_name, accumulate):
+            yield
+
+    def _filter_named_parameters(self, optimizer: torch.optim.Optimizer) -> List:
+        """(name, parameter) of the wrapped models' parameters that this optimizer owns (:472-479)."""
+        mine = {p for group in optimizer.param_groups for p in group.get("params", [])}
+        return [(name, p) for name, p in self._main_model.named_parameters() if p in mine]
+
+    def _set_is_pre_trainer(self) -> None:
+        self._is_pre_trainer = True
 
     def configure_apex_amp(self, *args: Any, **kwargs: Any) -> Any:
         # deprecated in the reference (_pytorch_context.py:635-640) and apex is not installed here
@@ -659,6 +754,15 @@ class PyTorchTrialContext(_PyTorchReducerContext):
     def close(self) -> None:
         for eng in self._engines.values():
             eng.close()
+
+
+def _info_field(name: str) -> int:
+    """experiment_id / trial_id from the cluster info the launcher exported (DET_* environment), else 0."""
+    from determined_clone_b200 import _info
+
+    info = _info.get_cluster_info()
+    trial = getattr(info, "trial", None) if info is not None else None
+    return int(getattr(trial, name, 0) or 0)
 
 
 def _fold_back_replaced_grads(eng: _gradsync.GradSyncEngine, present: List[List[bool]]) -> None:

@@ -13,6 +13,7 @@ What changes on the hot path: scalar device metrics are not pulled to the host e
 ranks by kernels once per reporting period (_metric_utils.DeviceMetricBuffer).
 """
 import abc
+import contextlib
 import json
 import logging
 import pathlib
@@ -161,6 +162,12 @@ class _PyTorchTrialController:
         previous: Any = None
         samples = 0
         t0 = time.time()
+        with contextlib.ExitStack() as stack:
+            if self.context.profiler:
+                stack.enter_context(self.context.profiler)  # torch.profiler set through context.set_profiler()
+            self._train_loop(it, pending, previous, samples, t0)
+
+    def _train_loop(self, it: Any, pending: List[Dict[str, Any]], previous: Any, samples: int, t0: float) -> None:
         while self.batches_trained < self.max_length:
             batch_idx = self.batches_trained
             try:
@@ -171,11 +178,16 @@ class _PyTorchTrialController:
             self.context._current_batch_idx = batch_idx
             epoch_idx = batch_idx // self.context._epoch_len if self.context._epoch_len else 0
             metrics = self._train_batch(batch, epoch_idx, batch_idx)
+            if self.context.profiler:
+                self.context.profiler.step()
             samples += self.trial.get_batch_length(batch)
             if metrics is not None:
                 pending.append(metrics)
             self.batches_trained += 1
-            if self.batches_trained % self.reporting_period == 0 or self.batches_trained == self.max_length:
+            # context.set_stop_requested(True) from user code ends training after the current batch (reference
+            # _pytorch_trial.py:521-525 raises ShouldExit there); what has been trained is still reported
+            stopping = self._stop_requested()
+            if self.batches_trained % self.reporting_period == 0 or self.batches_trained == self.max_length or stopping:
                 # the reduction of this period is enqueued now and read one period later (or at the end), so
                 # the host keeps launching batches instead of waiting for the GPU to drain
                 finish = self._begin_report(pending)
@@ -183,7 +195,14 @@ class _PyTorchTrialController:
                 previous = (finish, self.batches_trained, samples, time.time() - t0)
                 pending, samples, t0 = [], 0, time.time()
                 self.context.reset_reducers()
+            if stopping:
+                break
         self._deliver(previous)
+
+    def _stop_requested(self) -> bool:
+        """As in the reference, the flag is per rank: user code must make the same request on every rank (the next
+        batch starts with collectives)."""
+        return bool(self.context.get_stop_requested())
 
     def _begin_report(self, training_metrics: List[Dict]) -> Callable[[], Dict]:
         """Start aggregating the period's metrics; returns the function that completes it."""

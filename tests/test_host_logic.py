@@ -670,3 +670,73 @@ def test_autocast_forward_wrapper_keeps_the_module_and_widens_fp16_outputs():
     m2 = ctx2.wrap_model(M())
     ctx2.experimental.use_amp()
     assert m2(x, "bare").dtype == torch.float16 and not any(m2.autocast_seen)
+
+
+def test_context_host_side_surface(tmp_path, monkeypatch):
+    """The host-only members of PyTorchTrialContext that trial code calls (reference _pytorch_context.py:200-229,
+    :424-479, :981-1030): argument checks with the reference's texts, stop requests ending the loop after the
+    current batch with everything trained so far reported, the torch profiler entered and stepped by the loop."""
+    monkeypatch.setenv("DET_TENSORBOARD_PATH", str(tmp_path))
+    ctx = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 4})
+    assert ctx.get_trial_id() == 0 and ctx.get_experiment_id() == 0  # no master, no launcher
+    assert ctx.get_stop_requested() is False and ctx.get_enable_tensorboard_logging() is False
+    with pytest.raises(AssertionError, match="stop_requested must be a boolean"):
+        ctx.set_stop_requested(1)
+    with pytest.raises(AssertionError, match="enable_tensorboard_logging must be a boolean"):
+        ctx.set_enable_tensorboard_logging("yes")
+    ctx.set_enable_tensorboard_logging(True)
+    assert ctx.get_enable_tensorboard_logging() is True
+    tb = ctx.get_tensorboard_path()
+    assert tb.is_dir() and str(tb).startswith(str(tmp_path)) and ctx.get_tensorboard_path() == tb
+    with ctx._record_timing("anything", accumulate=True):
+        pass
+    ctx.experimental.disable_dataset_reproducibility_checks()
+    assert ctx.experimental._data_repro_checks_disabled
+    ctx._set_is_pre_trainer()
+    assert ctx._is_pre_trainer
+
+    m = ctx.wrap_model(torch.nn.Linear(2, 2))
+    other = torch.nn.Linear(2, 2)
+    opt = torch.optim.SGD([m.bias, other.weight], lr=0.1)  # never wrapped: only the name filter is exercised
+    assert [n for n, _ in ctx._filter_named_parameters(opt)] == ["model_0.bias"]
+
+    class Prof:
+        entered = exited = steps = 0
+
+        def __enter__(self):
+            Prof.entered += 1
+            return self
+
+        def __exit__(self, *a):
+            Prof.exited += 1
+
+        def step(self):
+            Prof.steps += 1
+
+    class Trial(pytorch.PyTorchTrial):
+        def __init__(self, context):
+            self.context = context
+
+        def build_training_data_loader(self):
+            return pytorch.DataLoader(torch.utils.data.TensorDataset(torch.arange(40).float()), batch_size=4)
+
+        def train_batch(self, batch, epoch_idx, batch_idx):
+            if batch_idx == 4:
+                self.context.set_stop_requested(True)
+            return {"loss": float(batch_idx)}
+
+    ctx.profiler = Prof()
+    got = []
+    ctl = pytorch._PyTorchTrialController(Trial(ctx), ctx, max_length=100, reporting_period=3, on_report=lambda n, r: got.append((n, r)))
+    ctl.run()
+    assert ctl.batches_trained == 5 and [n for n, _ in got] == [3, 5]
+    assert [r["avg_metrics"]["loss"] for _, r in got] == [1.0, 3.5]  # batches 3 and 4 are reported although the period is 3
+    assert (Prof.entered, Prof.exited, Prof.steps) == (1, 1, 5)
+
+    # set_profiler builds a torch.profiler.profile that writes its traces into the TensorBoard directory
+    ctx.set_profiler(activities=[torch.profiler.ProfilerActivity.CPU], schedule=torch.profiler.schedule(wait=0, warmup=0, active=1))
+    assert isinstance(ctx.profiler, torch.profiler.profile)
+    with ctx.profiler as prof:
+        torch.ones(4).sum()
+        prof.step()
+    assert any(f.name.endswith(".pt.trace.json") for f in tb.iterdir())
