@@ -32,7 +32,22 @@ def main(argv: List[str]) -> int:
     with _trainer.init() as context:
         trial = trial_class(context)
         trainer = _trainer.Trainer(trial, context)
-        reports = trainer.fit()
+        conf = context.get_experiment_config()
+        gbs = context._global_batch_size
+
+        def period(key: str) -> Any:  # {"batches": n} | {"epochs": n} | {"records": n}; absent or 0 = never
+            spec = {k: v for k, v in (conf.get(key) or {}).items() if v}
+            return _trainer.TrainUnit._from_values(**spec, global_batch_size=gbs) if spec else None
+
+        context._set_is_pre_trainer()
+        reports = trainer.fit(
+            checkpoint_period=period("min_checkpoint_period"),
+            validation_period=period("min_validation_period"),
+            reporting_period=_trainer.Batch(int(conf.get("scheduling_unit", 100))),
+            checkpoint_policy=conf.get("checkpoint_policy", "best"),
+            latest_checkpoint=_info.get_cluster_info().latest_checkpoint,
+            step_zero_validation=bool(conf.get("perform_initial_validation", False)),
+        )
         if context.distributed.rank == 0:
             for report in reports:
                 print({k: report[k] for k in ("steps_completed", "avg_metrics", "samples_per_second") if k in report}, flush=True)

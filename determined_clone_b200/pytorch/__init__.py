@@ -9,6 +9,7 @@ from determined_clone_b200.pytorch._reducer import (
 from determined_clone_b200.pytorch._metric_utils import (
     DeviceMetricBuffer,
     _average_training_metrics,
+    _log_tb_metrics,
     _combine_and_average_training_metrics,
     _combine_metrics_across_processes,
     _convert_metrics_to_numpy,
@@ -17,9 +18,10 @@ from determined_clone_b200.pytorch._metric_utils import (
     _reduce_metrics,
 )
 from determined_clone_b200.pytorch._lr_scheduler import LRScheduler
+from determined_clone_b200.pytorch._callback import PyTorchCallback
 from determined_clone_b200.pytorch._data import DataLoader, data_length
 from determined_clone_b200.pytorch._comm import Comm
 from determined_clone_b200.pytorch._gradsync import GradSyncEngine
 from determined_clone_b200.pytorch._pytorch_context import PyTorchExperimentalContext, PyTorchTrialContext
-from determined_clone_b200.pytorch._pytorch_trial import PyTorchTrial, TorchData, _PyTorchTrialController
+from determined_clone_b200.pytorch._pytorch_trial import PyTorchTrial, TorchData, _PyTorchTrialController, _TrialState
 from determined_clone_b200.pytorch._trainer import Batch, Epoch, Record, Trainer, TrainUnit, init

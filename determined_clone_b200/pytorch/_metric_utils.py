@@ -317,3 +317,26 @@ class PendingMetrics:
             per_batch.append(row)
         avg = {name: (float(host[b * m + j]) if counts[j] else None) for j, name in enumerate(self._names)}
         return per_batch, avg, counts
+
+
+def _log_tb_metrics(writer: Any, metric_type: str, steps_completed: int, metrics: Dict[str, Any],
+                    batch_metrics: Optional[List[Dict[str, Any]]] = None) -> None:
+    """Scalars for TensorBoard under "Determined/<name>" (reference _metric_utils.py:179-211): every per-batch
+    training value at the batch it belongs to; reduced values that have no per-batch series (custom reducers,
+    validation metrics -- the latter prefixed "val_" unless they already are) at steps_completed."""
+    if metric_type not in ("train", "val"):
+        logger.warning("Unrecognized tensorboard metric type: " + metric_type)
+    have_series = set()
+    first = steps_completed - len(batch_metrics or [])
+    for k, batch in enumerate(batch_metrics or []):
+        for name, value in batch.items():
+            have_series.add(name)
+            if util.is_numerical_scalar(value):
+                writer.add_scalar("Determined/" + name, value, first + k)
+    for name, value in metrics.items():
+        if name in have_series:
+            continue
+        if metric_type == "val" and not name.startswith("val"):
+            name = "val_" + name
+        if util.is_numerical_scalar(value):
+            writer.add_scalar("Determined/" + name, value, steps_completed)

@@ -14,19 +14,25 @@ ranks by kernels once per reporting period (_metric_utils.DeviceMetricBuffer).
 """
 import abc
 import contextlib
+import inspect
 import json
 import logging
+import os
 import pathlib
 import pickle
 import random
+import tempfile
 import time
+import uuid
+import warnings
 from typing import Any, Callable, Dict, List, Optional, Union
 
 import numpy as np
 import torch
 
-from determined_clone_b200 import util
+from determined_clone_b200 import errors, util
 from determined_clone_b200.pytorch import _metric_utils
+from determined_clone_b200.pytorch._callback import PyTorchCallback
 from determined_clone_b200.pytorch._data import DataLoader, data_length
 from determined_clone_b200.pytorch._lr_scheduler import LRScheduler
 from determined_clone_b200.pytorch._pytorch_context import PyTorchTrialContext
@@ -64,7 +70,13 @@ class PyTorchTrial(abc.ABC):
     def get_batch_length(self, batch: Any) -> int:
         return data_length(batch)
 
+    def evaluate_full_dataset(self, data_loader: Any) -> Dict[str, Any]:
+        """Alternative to evaluate_batch: the chief alone computes the validation metrics over the whole loader
+        (reference :1616-1633).  Exactly one of the two is overridden."""
+        pass
+
     def build_callbacks(self) -> Dict[str, Any]:
+        """name -> PyTorchCallback; see _callback.py for the hooks and when the loop calls them."""
         return {}
 
 
@@ -105,7 +117,22 @@ class _PyTorchTrialController:
         test_mode: bool = False,
         trial_id: int = 1,
         val_from_previous_run: int = 0,
+        validation_period: Optional[int] = None,
+        checkpoint_period: Optional[int] = None,
+        checkpoint_policy: str = "none",
+        searcher_metric_name: Optional[str] = None,
+        smaller_is_better: bool = True,
+        step_zero_validation: bool = False,
+        checkpoint_dir: Optional[Any] = None,
+        latest_checkpoint: Optional[str] = None,
+        final_validation: bool = False,
+        final_checkpoint: bool = False,
+        on_validation: Optional[Callable[[int, Dict[str, Any]], None]] = None,
     ) -> None:
+        """max_length / reporting_period / validation_period / checkpoint_period are in batches (Trainer.fit converts
+        epochs and records).  The loop of the reference (_pytorch_trial.py:626-820) without a master: checkpoints go
+        to directories named by a fresh uuid under `checkpoint_dir`, reports go to on_report / on_validation and are
+        kept in .reports / .validation_reports.  With the defaults nothing but training and reporting happens."""
         self.trial = trial_inst
         self.context = context
         # test_mode trains exactly one batch (reference _pytorch_trial.py:742-743,755-756)
@@ -122,6 +149,33 @@ class _PyTorchTrialController:
         self.trial_id = trial_id
         self.state = _TrialState(trial_id=trial_id, batches_trained=steps_completed)
         self.val_from_previous_run = val_from_previous_run
+        self.test_mode = test_mode
+        self.validation_period = validation_period
+        self.checkpoint_period = checkpoint_period
+        if checkpoint_policy not in ("all", "best", "none"):
+            raise ValueError(f"checkpoint_policy must be one of 'all', 'best', 'none'; got {checkpoint_policy!r}")
+        self.ckpt_policy = checkpoint_policy
+        self.searcher_metric_name = searcher_metric_name
+        self.smaller_is_better = smaller_is_better
+        self.step_zero_validation = step_zero_validation
+        self.checkpoint_dir = checkpoint_dir
+        self.latest_checkpoint = latest_checkpoint
+        self.final_validation = final_validation
+        self.final_checkpoint = final_checkpoint
+        self.on_validation = on_validation
+        self.validation_reports: List[Dict[str, Any]] = []
+        self.checkpoints: List[str] = []  # uuids written in this run, oldest first
+        self._best_validation: Optional[float] = None
+        self.callbacks: Dict[str, Any] = (trial_inst.build_callbacks() if trial_inst is not None else None) or {}
+        for name, cb in self.callbacks.items():
+            if not isinstance(cb, PyTorchCallback):
+                raise TypeError(f"build_callbacks() must map names to PyTorchCallback objects; '{name}' is a {type(cb).__name__}")
+            if util.is_overridden(cb.on_checkpoint_end, PyTorchCallback):
+                warnings.warn(
+                    "The on_checkpoint_end callback is deprecated, please use on_checkpoint_write_end instead.",
+                    FutureWarning, stacklevel=2,
+                )
+        self._workload_end_hooks = any(util.is_overridden(cb.on_training_workload_end, PyTorchCallback) for cb in self.callbacks.values())
 
     # ---- set-up -------------------------------------------------------------------------------------
     @classmethod
@@ -154,20 +208,31 @@ class _PyTorchTrialController:
 
     # ---- training loop ------------------------------------------------------------------------------
     def run(self) -> None:
-        if self.training_loader is None:
-            self._set_data_loaders()
-        it = iter(self.training_loader)
-        self.context.reset_reducers()
-        pending: List[Dict[str, Any]] = []
-        previous: Any = None
-        samples = 0
-        t0 = time.time()
         with contextlib.ExitStack() as stack:
+            for cb in self.callbacks.values():
+                cb.on_trial_startup(self.batches_trained, self.latest_checkpoint)
+                stack.callback(cb.on_trial_shutdown)  # also on an exception or a stop request
+            if self.latest_checkpoint is not None:
+                # before the loaders are built: they skip the batches the restored trial has already seen
+                self._load(self._checkpoint_path(self.latest_checkpoint))
+            if self.training_loader is None:
+                self._set_data_loaders()
+            for cb in self.callbacks.values():
+                cb.on_training_start()
             if self.context.profiler:
                 stack.enter_context(self.context.profiler)  # torch.profiler set through context.set_profiler()
-            self._train_loop(it, pending, previous, samples, t0)
+            if self.step_zero_validation and not self.val_from_previous_run and self.batches_trained == 0:
+                self._validation_step()
+            self.context.reset_reducers()
+            self._train_loop(iter(self.training_loader), [], None, 0, time.time())
+            # end of training: the reference validates and checkpoints whatever is not current (:810-814)
+            if self.final_validation and self.state.last_val != self.batches_trained:
+                self._validation_step()
+            if self.final_checkpoint and self.state.last_ckpt != self.batches_trained:
+                self._checkpoint()
 
     def _train_loop(self, it: Any, pending: List[Dict[str, Any]], previous: Any, samples: int, t0: float) -> None:
+        epoch_len = self.context._epoch_len
         while self.batches_trained < self.max_length:
             batch_idx = self.batches_trained
             try:
@@ -176,7 +241,9 @@ class _PyTorchTrialController:
                 it = iter(self.training_loader)
                 batch = next(it)
             self.context._current_batch_idx = batch_idx
-            epoch_idx = batch_idx // self.context._epoch_len if self.context._epoch_len else 0
+            epoch_idx = batch_idx // epoch_len if epoch_len else 0
+            if self.callbacks and epoch_len and batch_idx % epoch_len == 0:
+                self._on_epoch_start(epoch_idx)
             metrics = self._train_batch(batch, epoch_idx, batch_idx)
             if self.context.profiler:
                 self.context.profiler.step()
@@ -184,20 +251,44 @@ class _PyTorchTrialController:
             if metrics is not None:
                 pending.append(metrics)
             self.batches_trained += 1
+            n = self.batches_trained
+            if self.callbacks and epoch_len and n % epoch_len == 0:
+                for cb in self.callbacks.values():
+                    cb.on_training_epoch_end(epoch_idx)
             # context.set_stop_requested(True) from user code ends training after the current batch (reference
             # _pytorch_trial.py:521-525 raises ShouldExit there); what has been trained is still reported
             stopping = self._stop_requested()
-            if self.batches_trained % self.reporting_period == 0 or self.batches_trained == self.max_length or stopping:
-                # the reduction of this period is enqueued now and read one period later (or at the end), so
-                # the host keeps launching batches instead of waiting for the GPU to drain
+            validate_due = bool(self.validation_period) and n % self.validation_period == 0
+            checkpoint_due = bool(self.checkpoint_period) and n % self.checkpoint_period == 0
+            if n % self.reporting_period == 0 or n == self.max_length or stopping or validate_due or checkpoint_due:
                 finish = self._begin_report(pending)
                 self._deliver(previous)
-                previous = (finish, self.batches_trained, samples, time.time() - t0)
+                previous = (finish, n, samples, time.time() - t0)
+                if self._workload_end_hooks or validate_due or checkpoint_due:
+                    # callbacks want the metrics now, or a validation / checkpoint (which drain the GPU anyway) comes next
+                    self._deliver(previous)
+                    previous = None
+                # otherwise the reduction of this period is enqueued now and read one period later (or at the end),
+                # so the host keeps launching batches instead of waiting for the GPU to drain
                 pending, samples, t0 = [], 0, time.time()
                 self.context.reset_reducers()
+                if validate_due and self.state.last_val != n:
+                    self._validation_step()
+                if checkpoint_due and self.state.last_ckpt != n:
+                    self._checkpoint()
+                if validate_due or checkpoint_due:
+                    t0 = time.time()
             if stopping:
                 break
         self._deliver(previous)
+
+    def _on_epoch_start(self, epoch_idx: int) -> None:
+        for cb in self.callbacks.values():
+            if inspect.signature(cb.on_training_epoch_start).parameters:
+                cb.on_training_epoch_start(epoch_idx)
+            else:  # the pre-0.17.8 signature, still accepted by the reference (:378-386)
+                logger.warning("on_training_epoch_start() without parameters is deprecated since 0.17.8. Please add epoch_idx parameter.")
+                cb.on_training_epoch_start()
 
     def _stop_requested(self) -> bool:
         """As in the reference, the flag is per rank: user code must make the same request on every rank (the next
@@ -223,10 +314,17 @@ class _PyTorchTrialController:
             return
         finish, steps, samples, dur = previous
         report = finish()
+        if self._workload_end_hooks:
+            d = self.context.distributed
+            everyone = d.broadcast(report) if d.size > 1 else report  # non-chief ranks hold {} (:771)
+            for cb in self.callbacks.values():
+                cb.on_training_workload_end(avg_metrics=everyone["avg_metrics"], batch_metrics=everyone["batch_metrics"])
         if self.is_chief:
             report["samples_per_second"] = samples / dur * self.context.distributed.size if dur > 0 else 0.0
             report["steps_completed"] = steps
             self.reports.append(report)
+            if self.context.get_enable_tensorboard_logging():
+                _metric_utils._log_tb_metrics(self.context.get_tensorboard_writer(), "train", steps, report["avg_metrics"], report["batch_metrics"])
             if self.on_report:
                 self.on_report(steps, report)
 
@@ -302,6 +400,44 @@ class _PyTorchTrialController:
         return metrics
 
     # ---- checkpoints ----------------------------------------------------------------------------------
+    def _storage_dir(self) -> pathlib.Path:
+        """Where this run's checkpoints live, one directory per uuid: the checkpoint_dir argument, else the
+        experiment config's shared_fs checkpoint_storage, else DET_CHECKPOINT_DIR, else the system temp dir."""
+        if self.checkpoint_dir is not None:
+            return pathlib.Path(self.checkpoint_dir)
+        storage = (self.context._exp_conf or {}).get("checkpoint_storage") or {}
+        if storage.get("type", "shared_fs") == "shared_fs" and storage.get("host_path"):
+            return pathlib.Path(storage["host_path"]) / (storage.get("storage_path") or "")
+        return pathlib.Path(os.environ.get("DET_CHECKPOINT_DIR") or os.path.join(tempfile.gettempdir(), "determined-checkpoints"))
+
+    def _checkpoint_path(self, uuid_or_path: str) -> pathlib.Path:
+        direct = pathlib.Path(uuid_or_path)
+        return direct if direct.is_dir() else self._storage_dir() / uuid_or_path
+
+    def _checkpoint(self) -> str:
+        """Write a checkpoint now (reference :395-423): the chief saves into <storage>/<uuid>/, every rank learns
+        the uuid and runs on_checkpoint_upload_end.  Returns the uuid."""
+        self.state.last_ckpt = self.batches_trained
+        d = self.context.distributed
+        name = ""
+        collective_state = any(eng.sharded for eng in self.context._engines.values())
+        if self.is_chief:
+            name = str(uuid.uuid4())
+            path = self._storage_dir() / name
+            self._save(path)
+            with (path / "metadata.json").open("w") as f:
+                json.dump({"steps_completed": self.batches_trained, "framework": f"torch-{torch.__version__}", "format": "pickle"}, f)
+        elif collective_state:
+            # sharded step: optimizer.state_dict() gathers the other ranks' slices, so every rank has to ask for it
+            for opt in self.context.optimizers:
+                opt.state_dict()
+        if d.size > 1:
+            name = d.broadcast(name)
+        self.checkpoints.append(name)
+        for cb in self.callbacks.values():
+            cb.on_checkpoint_upload_end(uuid=name)
+        return name
+
     def _save(self, path: Any) -> None:
         """Write state_dict.pth + trial_state.pkl + load_data.json with the reference's keys
         (_pytorch_trial.py:1312-1385), so that checkpoints move between the two harnesses.  Parameters and
@@ -320,11 +456,13 @@ class _PyTorchTrialController:
             "models_state_dict": [{k: v.detach().clone() for k, v in m.state_dict().items()} for m in self.context.models],
             "optimizers_state_dict": [_clone_tensors(o.state_dict()) for o in self.context.optimizers],
             "lr_schedulers_state_dict": [s.state_dict() for s in self.context.lr_schedulers],
-            "callbacks": {},
+            "callbacks": {name: cb.state_dict() for name, cb in self.callbacks.items()},
             "rng_state": rng_state,
         }
         if self.context._scaler:
             checkpoint["scaler_state_dict"] = self.context._scaler.state_dict()
+        for cb in self.callbacks.values():
+            cb.on_checkpoint_save_start(checkpoint)
         torch.save(checkpoint, str(path / "state_dict.pth"))
         self.state.batches_trained = self.batches_trained
         self.state.epochs_trained = self._get_epoch_idx(self.batches_trained)
@@ -340,6 +478,9 @@ class _PyTorchTrialController:
                 "trial_cls_spec": f"{cls.__module__}:{cls.__qualname__}",
                 "is_trainer": True,
             }, f)
+        for cb in self.callbacks.values():
+            cb.on_checkpoint_end(str(path))
+            cb.on_checkpoint_write_end(str(path))
 
     # where state_dict.pth has lived over the reference's releases, newest first (:1118-1125)
     _CHECKPOINT_FILES = (("state_dict.pth",), ("determined", "state_dict.pth"), ("pedl", "state_dict.pth"), ("checkpoint.pt",))
@@ -364,6 +505,8 @@ class _PyTorchTrialController:
                 break
         if not isinstance(checkpoint, dict):
             return  # same as the reference: nothing to restore, not an error
+        for cb in self.callbacks.values():
+            cb.on_checkpoint_load_start(checkpoint)
 
         targets = {"model": self.context.models, "optimizer": self.context.optimizers, "LR scheduler": self.context.lr_schedulers}
         for plural, singular, what in self._CHECKPOINT_PARTS:
@@ -407,6 +550,17 @@ class _PyTorchTrialController:
         else:
             logger.warning("The checkpoint has no random state to restore.")
 
+        saved_callbacks = checkpoint.get("callbacks", {})
+        for name, cb in self.callbacks.items():
+            if name in saved_callbacks:
+                cb.load_state_dict(saved_callbacks[name])
+            elif util.is_overridden(cb.load_state_dict, PyTorchCallback):
+                logger.warning(
+                    f"Callback '{name}' implements load_state_dict(), but no callback state "
+                    "was found for that name when restoring from checkpoint. This "
+                    "callback will be initialized from scratch."
+                )
+
         if (path / "trial_state.pkl").exists():
             with (path / "trial_state.pkl").open("rb") as f:
                 self._load_state(pickle.load(f))
@@ -445,37 +599,126 @@ class _PyTorchTrialController:
         ))
 
     # ---- validation ---------------------------------------------------------------------------------
+    def _validation_step(self) -> Dict[str, Any]:
+        """One validation as the loop runs it (reference _validate :941-1115 around the metric computation): the
+        callbacks, the report, and a checkpoint if the policy asks for one."""
+        if self.validation_loader is None:
+            self.state.last_val = self.batches_trained
+            return {}
+        for cb in self.callbacks.values():
+            cb.on_validation_start()
+        metrics = self._validate()
+        d = self.context.distributed
+        if d.size > 1 and any(util.is_overridden(cb.on_validation_end, PyTorchCallback) for cb in self.callbacks.values()):
+            metrics = d.broadcast(metrics)  # every rank's callbacks see the chief's metrics (:1040-1048)
+        for cb in self.callbacks.values():
+            cb.on_validation_end(metrics)
+        self.state.last_val = n = self.batches_trained
+        should_checkpoint = False
+        if self.is_chief:
+            self.validation_reports.append({"steps_completed": n, "validation_metrics": metrics})
+            if self.context.get_enable_tensorboard_logging():
+                _metric_utils._log_tb_metrics(self.context.get_tensorboard_writer(), "val", n, metrics)
+            if self.on_validation:
+                self.on_validation(n, metrics)
+            searcher_metric = self._check_searcher_metric(metrics) if self.searcher_metric_name else None
+            if self.state.last_ckpt != n:
+                if self.ckpt_policy == "all":
+                    should_checkpoint = True
+                elif self.ckpt_policy == "best":
+                    assert self.searcher_metric_name, "checkpoint policy 'best' but searcher metric name not defined"
+                    should_checkpoint = self._is_best_validation(searcher_metric, self._best_validation)
+            if searcher_metric is not None and self._is_best_validation(searcher_metric, self._best_validation):
+                self._best_validation = float(searcher_metric)
+        if d.size > 1:
+            should_checkpoint = d.broadcast(should_checkpoint)
+        if should_checkpoint:
+            self._checkpoint()
+        return metrics
+
+    def _is_best_validation(self, now: float, before: Optional[float]) -> bool:
+        if before is None:
+            return True
+        return (now < before) if self.smaller_is_better else (now > before)
+
+    def _check_searcher_metric(self, val_metrics: Dict) -> Any:
+        if self.searcher_metric_name not in val_metrics:
+            raise RuntimeError(
+                f"Search method is configured to use metric '{self.searcher_metric_name}' but "
+                f"model definition returned validation metrics {list(val_metrics.keys())}. The "
+                f"metric used by the search method must be one of the validation "
+                "metrics returned by the model definition."
+            )
+        searcher_metric = val_metrics[self.searcher_metric_name]
+        if not util.is_numerical_scalar(searcher_metric):
+            raise RuntimeError(
+                f"Searcher validation metric '{self.searcher_metric_name}' returned "
+                f"a non-scalar value: {searcher_metric}."
+            )
+        return searcher_metric
+
     @torch.no_grad()
     def _validate(self) -> Dict[str, Any]:
-        """Per-rank evaluate_batch loop, reduce over batches then ranks (weighted by batches per rank)."""
+        """The metric computation of a validation: per-rank evaluate_batch loop, reduce over batches then ranks
+        (weighted by batches per rank); or evaluate_full_dataset on the chief."""
         if self.validation_loader is None:
             raise RuntimeError("no validation data loader")
         for model in self.context.models:
             model.eval()
         self.context.reset_reducers()
-        batch_metrics: List[Dict[str, Any]] = []
-        keys = None
-        device_buf = _metric_utils.DeviceMetricBuffer(self.context.device) if self._device_metrics else None
-        for idx, batch in enumerate(self.validation_loader):
-            if self.context.experimental._auto_to_device:
-                batch = self.context.to_device(batch)
-            vld = self.trial.evaluate_batch(batch=batch, batch_idx=idx)
-            if keys is None:
-                keys = vld.keys()
-            if device_buf is not None and not batch_metrics and device_buf.accepts(vld) and all(v is not None for v in vld.values()):
-                device_buf.append(vld)  # stays on the GPU (the reference converts every batch: :999)
-                continue
-            if device_buf is not None and len(device_buf):
-                raise RuntimeError("evaluate_batch() must return the same kind of metrics for every batch")
-            batch_metrics.append(_metric_utils._convert_metrics_to_numpy(vld))
         d = self.context.distributed
-        keys = d.broadcast(list(keys) if keys is not None else None) if d.size > 1 else keys
-        reducers = _metric_utils._prepare_metrics_reducers(self.trial.evaluation_reducer(), keys=keys or [])
-        if device_buf is not None and len(device_buf):
-            metrics = _metric_utils.reduce_validation_on_device(device_buf, d, reducers)
+        if util.is_overridden(self.trial.evaluate_full_dataset, PyTorchTrial):
+            if util.is_overridden(self.trial.evaluate_batch, PyTorchTrial):
+                raise errors.InvalidExperimentException(
+                    "Please define exactly one of: `evaluate_batch()` or `evaluate_full_dataset()`. "
+                    "For most use cases `evaluate_batch()` is recommended because "
+                    "it can be parallelized across all devices.",
+                )
+            metrics: Dict[str, Any] = {}
+            if self.is_chief:
+                metrics = self.trial.evaluate_full_dataset(data_loader=self.validation_loader)
+                if not isinstance(metrics, dict):
+                    raise TypeError(f"eval() must return a dictionary, got {type(metrics).__name__}.")
+                metrics = _metric_utils._convert_metrics_to_numpy(metrics)
         else:
-            metrics = _metric_utils._reduce_metrics(d, batch_metrics=batch_metrics, keys=keys, metrics_reducers=reducers)
+            metrics = self._evaluate_batches()
         metrics.update(_metric_utils._convert_metrics_to_numpy(self.context.reduce_metrics(for_training=False)))
         for model in self.context.models:
             model.train()
         return metrics if self.is_chief else {}
+
+    def _evaluate_batches(self) -> Dict[str, Any]:
+        batch_metrics: List[Dict[str, Any]] = []
+        keys = None
+        # a callback that wants every batch's results gets them as host values, as the reference produces them
+        wants_outputs = any(util.is_overridden(cb.on_validation_epoch_end, PyTorchCallback) for cb in self.callbacks.values())
+        device_buf = _metric_utils.DeviceMetricBuffer(self.context.device) if self._device_metrics and not wants_outputs else None
+        takes_idx = util.has_param(self.trial.evaluate_batch, "batch_idx", 2)
+        for cb in self.callbacks.values():
+            cb.on_validation_epoch_start()
+        for idx, batch in enumerate(self.validation_loader):
+            if self.context.experimental._auto_to_device:
+                batch = self.context.to_device(batch)
+            vld = self.trial.evaluate_batch(batch=batch, batch_idx=idx) if takes_idx else self.trial.evaluate_batch(batch=batch)
+            if not isinstance(vld, dict):
+                raise TypeError(f"validation_metrics() must return a dictionary of string names to Tensor metrics; got {vld}.")
+            if keys is None:
+                keys = vld.keys()
+            elif keys != vld.keys():
+                raise ValueError(f"Validation metric names must match across all batches of data: {keys} != {vld.keys()}.")
+            if device_buf is not None and not batch_metrics and device_buf.accepts(vld) and all(v is not None for v in vld.values()):
+                device_buf.append(vld)  # stays on the GPU (the reference converts every batch: :999)
+            else:
+                if device_buf is not None and len(device_buf):
+                    raise RuntimeError("evaluate_batch() must return the same kind of metrics for every batch")
+                batch_metrics.append(_metric_utils._convert_metrics_to_numpy(vld))
+            if self.test_mode:
+                break
+        for cb in self.callbacks.values():
+            cb.on_validation_epoch_end(batch_metrics)
+        d = self.context.distributed
+        keys = d.broadcast(list(keys) if keys is not None else None) if d.size > 1 else keys
+        reducers = _metric_utils._prepare_metrics_reducers(self.trial.evaluation_reducer(), keys=keys or [])
+        if device_buf is not None and len(device_buf):
+            return _metric_utils.reduce_validation_on_device(device_buf, d, reducers)
+        return _metric_utils._reduce_metrics(d, batch_metrics=batch_metrics, keys=keys, metrics_reducers=reducers)

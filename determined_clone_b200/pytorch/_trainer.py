@@ -4,6 +4,7 @@
 preemption belong to the control plane and are not rebuilt: fit() trains for max_length (or the
 searcher.max_length of the experiment config) and returns the chief's reports."""
 import contextlib
+import logging
 import os
 from typing import Any, Dict, Iterator, List, Optional
 
@@ -11,6 +12,8 @@ from determined_clone_b200 import _info, core
 from determined_clone_b200._trial_controller import _DistributedBackend
 from determined_clone_b200.pytorch._pytorch_context import PyTorchTrialContext
 from determined_clone_b200.pytorch._pytorch_trial import PyTorchTrial, _PyTorchTrialController
+
+logger = logging.getLogger("determined.pytorch")
 
 
 class TrainUnit:
@@ -108,6 +111,8 @@ class Trainer:
     def __init__(self, trial: PyTorchTrial, context: PyTorchTrialContext) -> None:
         self._trial, self._context = trial, context
         self.reports: List[Dict[str, Any]] = []
+        self.validation_reports: List[Dict[str, Any]] = []
+        self.checkpoints: List[str] = []
 
     def _to_batches(self, unit: TrainUnit, loader_len: Optional[int]) -> int:
         if isinstance(unit, Batch):
@@ -119,27 +124,73 @@ class Trainer:
             raise ValueError("max_length in epochs needs a training data loader with a length")
         return unit.value * loader_len
 
-    def fit(self, max_length: Optional[TrainUnit] = None, reporting_period: TrainUnit = Batch(100),
-            latest_checkpoint: Optional[str] = None, **_ignored: Any) -> List[Dict[str, Any]]:
-        """Train for max_length; without it (on-cluster style) for searcher.max_length of the experiment
-        config.  Returns the chief's per-period reports."""
+    def fit(
+        self,
+        checkpoint_period: Optional[TrainUnit] = None,
+        validation_period: Optional[TrainUnit] = None,
+        max_length: Optional[TrainUnit] = None,
+        reporting_period: TrainUnit = Batch(100),
+        checkpoint_policy: str = "best",
+        latest_checkpoint: Optional[str] = None,
+        step_zero_validation: bool = False,
+        test_mode: bool = False,
+        checkpoint_dir: Optional[str] = None,
+    ) -> List[Dict[str, Any]]:
+        """Train, validate every validation_period, checkpoint every checkpoint_period (and after validations, per
+        checkpoint_policy), report every reporting_period; validate and checkpoint once more at the end if the last
+        batch was not covered (reference _trainer.py:83-213 -> _pytorch_trial.py:626-820).
+
+        Launched with an experiment config (DET_EXPERIMENT_CONFIG): max_length, the searcher metric and
+        smaller_is_better come from its `searcher` block, as on a cluster.  Otherwise ("local training") max_length
+        is required and checkpoint_policy "best" falls back to "all", as in the reference.  Checkpoints are
+        directories <checkpoint_dir>/<uuid>; latest_checkpoint is such a uuid, or a path.  Returns the chief's
+        training reports; validation reports are in .validation_reports, checkpoint uuids in .checkpoints."""
         ctx = self._context
-        if max_length is None:
-            conf = ctx._exp_conf or {}
-            ml = (conf.get("searcher", {}) or {}).get("max_length")
+        conf = (ctx._exp_conf or {}) if _info.get_cluster_info() is not None else {}
+        searcher = conf.get("searcher", {}) or {}
+        searcher_metric_name, smaller_is_better = None, True
+        if conf:
+            if test_mode:
+                raise ValueError("test_mode is only supported in local training mode.")
+            if max_length is not None:
+                logger.warning("max_length is ignored when training on-cluster. Please configure the searcher instead.")
+            ml = searcher.get("max_length")
             if isinstance(ml, int):
                 max_length = Batch(ml)
             elif isinstance(ml, dict) and len(ml) == 1:
                 (unit, length), = ml.items()
                 max_length = TrainUnit._from_searcher_unit(int(length), unit, ctx._global_batch_size)
             else:
-                raise ValueError("fit() needs max_length, or an experiment config with searcher.max_length")
-            if "scheduling_unit" in conf:
-                reporting_period = Batch(int(conf["scheduling_unit"]))
-        controller = _PyTorchTrialController(self._trial, ctx, max_length=0, reporting_period=1)
+                raise ValueError("the experiment config needs searcher.max_length")
+            searcher_metric_name = searcher.get("metric")
+            smaller_is_better = bool(searcher.get("smaller_is_better", True))
+        else:
+            if checkpoint_policy == "best":
+                logger.warning("checkpoint_policy='best' is not supported in local training mode. Falling back to 'all'.")
+                checkpoint_policy = "all"
+            if max_length is None:
+                raise ValueError("max_length must be defined in local training mode.")
+            if not isinstance(max_length.value, int):
+                raise TypeError("max_length must be configured in TrainUnit(int) types.")
+        controller = _PyTorchTrialController(
+            self._trial, ctx, max_length=0, reporting_period=1, test_mode=False,
+            checkpoint_policy=checkpoint_policy, searcher_metric_name=searcher_metric_name,
+            smaller_is_better=smaller_is_better, step_zero_validation=step_zero_validation, checkpoint_dir=checkpoint_dir,
+            latest_checkpoint=latest_checkpoint, final_validation=True, final_checkpoint=True,
+            trial_id=ctx.get_trial_id(),
+        )
+        if latest_checkpoint is not None:
+            controller._load(controller._checkpoint_path(latest_checkpoint))  # before the loaders: they skip what was trained
+            controller.latest_checkpoint = None
         controller._set_data_loaders()
-        controller.max_length = self._to_batches(max_length, ctx._epoch_len)
-        controller.reporting_period = max(self._to_batches(reporting_period, ctx._epoch_len), 1)
+        epoch_len = ctx._epoch_len
+        controller.max_length = controller.batches_trained + 1 if test_mode else self._to_batches(max_length, epoch_len)
+        controller.test_mode = test_mode
+        controller.reporting_period = max(self._to_batches(reporting_period, epoch_len), 1)
+        controller.validation_period = self._to_batches(validation_period, epoch_len) if validation_period is not None else None
+        controller.checkpoint_period = self._to_batches(checkpoint_period, epoch_len) if checkpoint_period is not None else None
         controller.run()
         self.reports = controller.reports
+        self.validation_reports = controller.validation_reports
+        self.checkpoints = controller.checkpoints
         return controller.reports

@@ -78,3 +78,33 @@ def calculate_batch_sizes(hparams: Dict[str, Any], slots_per_trial: int, trialna
             f"{slots_per_trial} slots."
         )
     return per_slot, effective
+
+
+def is_overridden(method: Any, parent_class: Any) -> bool:
+    """Whether `method` (looked up on an instance or subclass) is a redefinition of parent_class's method
+    (reference util.py:84-92 compares qualified names; here: the underlying function objects).  Anything that is
+    not a function -- e.g. a user attribute shadowing the name -- counts as not overridden."""
+    fn = getattr(method, "__func__", method)
+    name = getattr(fn, "__name__", None)
+    if not callable(fn) or name is None:
+        return False
+    return getattr(parent_class, name, None) is not fn
+
+
+def has_param(fn: Any, name: str, pos: Optional[int] = None) -> bool:
+    """Whether fn accepts an argument called `name`, or -- failing that -- has a positional argument at index `pos`
+    (counting `self` for unbound methods exactly as inspect.getfullargspec does; reference util.py:95-104)."""
+    import inspect
+
+    args = inspect.getfullargspec(fn)[0]
+    return name in args or (pos is not None and pos < len(args))
+
+
+def is_numerical_scalar(n: Any) -> bool:
+    """int / float, numpy scalars and 0-d numeric numpy arrays: what can be written to TensorBoard as a scalar or
+    compared as a searcher metric (reference util.py:462-485)."""
+    import numpy as np
+
+    if isinstance(n, (int, float, np.number)):
+        return True
+    return isinstance(n, np.ndarray) and n.ndim == 0 and bool(np.issubdtype(n.dtype, np.number))

@@ -93,6 +93,58 @@ def _worker(rank: int, size: int, port: int, zmq_ports, out_dir: str) -> None:
         for b in range(rank, 7, size):  # batches dealt round-robin
             r.update(b)
         assert rc.reduce_metrics(for_training=True) == {"total": 21}
+
+        # ---- 4. the training loop around the path on 2 ranks: callbacks, validation, checkpoints -------------
+        class Hooks(pytorch.PyTorchCallback):
+            def __init__(self):
+                self.workloads, self.validations, self.uploads, self.written = [], [], [], 0
+
+            def on_training_workload_end(self, avg_metrics, batch_metrics):
+                self.workloads.append((float(avg_metrics["loss"]), len(batch_metrics)))
+
+            def on_validation_end(self, metrics):
+                self.validations.append(float(metrics["v"]))
+
+            def on_checkpoint_write_end(self, checkpoint_dir):
+                self.written += 1
+
+            def on_checkpoint_upload_end(self, uuid):
+                self.uploads.append(uuid)
+
+        class LoopTrial(pytorch.PyTorchTrial):
+            def __init__(self, context):
+                self.context = context  # no wrap_model: with several slots that brings up NCCL, and this is a CPU test
+                self.hooks = Hooks()
+
+            def build_callbacks(self):
+                return {"hooks": self.hooks}
+
+            def build_training_data_loader(self):
+                return pytorch.DataLoader(torch.utils.data.TensorDataset(torch.arange(32).float()), batch_size=2)
+
+            def build_validation_data_loader(self):
+                return pytorch.DataLoader(torch.utils.data.TensorDataset(torch.arange(8).float()), batch_size=2)
+
+            def train_batch(self, batch, epoch_idx, batch_idx):
+                return {"loss": float(batch[0][0])}  # first record of this rank's batch
+
+            def evaluate_batch(self, batch, batch_idx):
+                return {"v": float(batch[0].sum())}
+
+        lctx = pytorch.PyTorchTrialContext(distributed=dctx, hparams={"global_batch_size": 4}, slots_per_trial=size)
+        ltrial = LoopTrial(lctx)
+        trainer = pytorch.Trainer(ltrial, lctx)
+        reports = trainer.fit(max_length=pytorch.Batch(4), validation_period=pytorch.Batch(2), reporting_period=pytorch.Batch(2),
+                              checkpoint_policy="all", checkpoint_dir=os.path.join(out_dir, "ckpt"))
+        h = ltrial.hooks
+        # rank r sees global batches r, r+2, ...: batch k of rank r starts at record 2*(2k + r); mean over ranks = 4k + 1
+        assert h.workloads == [(np.mean([1.0, 5.0]), 2), (np.mean([9.0, 13.0]), 2)]  # every rank gets the chief's averages
+        # 4 validation batches dealt over 2 ranks; AVG over all of them = mean of (1, 5, 9, 13)
+        assert h.validations == [7.0, 7.0]
+        assert len(h.uploads) == 2 and h.uploads == dctx.broadcast(h.uploads)  # same uuids on every rank
+        assert h.written == (2 if rank == 0 else 0)  # only the chief writes
+        assert (len(reports), len(trainer.validation_reports)) == ((2, 2) if rank == 0 else (0, 0))
+        assert sorted(os.listdir(os.path.join(out_dir, "ckpt"))) == sorted(h.uploads)
         open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
     finally:
         dctx.close()

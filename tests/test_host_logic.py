@@ -740,3 +740,184 @@ def test_context_host_side_surface(tmp_path, monkeypatch):
         torch.ones(4).sum()
         prof.step()
     assert any(f.name.endswith(".pt.trace.json") for f in tb.iterdir())
+
+
+class _CountingCallback(pytorch.PyTorchCallback):
+    """Counts hook calls like the reference's test fixture does (harness/tests/experiment/fixtures/
+    pytorch_counter_callback.py), and keeps a picklable state."""
+
+    def __init__(self):
+        self.counts = {k: 0 for k in (
+            "trial_startups", "validation_steps_started", "validation_steps_ended", "checkpoints_written",
+            "checkpoints_uploaded", "training_started_times", "training_epochs_started", "training_epochs_ended",
+            "training_workloads_ended", "trial_shutdowns")}
+        self.workloads, self.val_outputs, self.loaded_from = [], [], None
+
+    def on_trial_startup(self, first_batch_idx, checkpoint_uuid):
+        self.counts["trial_startups"] += 1
+        self.started_at = (first_batch_idx, checkpoint_uuid)
+
+    def on_trial_shutdown(self):
+        self.counts["trial_shutdowns"] += 1
+
+    def on_training_start(self):
+        self.counts["training_started_times"] += 1
+
+    def on_training_epoch_start(self, epoch_idx):
+        self.counts["training_epochs_started"] += 1
+
+    def on_training_epoch_end(self, epoch_idx):
+        self.counts["training_epochs_ended"] += 1
+
+    def on_training_workload_end(self, avg_metrics, batch_metrics):
+        self.counts["training_workloads_ended"] += 1
+        self.workloads.append((dict(avg_metrics), len(batch_metrics)))
+
+    def on_validation_start(self):
+        self.counts["validation_steps_started"] += 1
+
+    def on_validation_epoch_end(self, outputs):
+        self.val_outputs.append(len(outputs))
+
+    def on_validation_end(self, metrics):
+        self.counts["validation_steps_ended"] += 1
+
+    def on_checkpoint_write_end(self, checkpoint_dir):
+        self.counts["checkpoints_written"] += 1
+        assert (pathlib.Path(checkpoint_dir) / "state_dict.pth").exists() and (pathlib.Path(checkpoint_dir) / "trial_state.pkl").exists()
+
+    def on_checkpoint_upload_end(self, uuid):
+        self.counts["checkpoints_uploaded"] += 1
+
+    def state_dict(self):
+        return {"workloads_seen": self.counts["training_workloads_ended"]}
+
+    def load_state_dict(self, state):
+        self.loaded_from = state
+
+
+class _LegacyEpochCallback(pytorch.PyTorchCallback):
+    calls = 0
+
+    def on_training_epoch_start(self):  # the signature from before epoch_idx existed; still accepted
+        _LegacyEpochCallback.calls += 1
+
+
+class _HostTrial(pytorch.PyTorchTrial):
+    """No optimizer (so it runs without a GPU): train_batch nudges the one weight by hand."""
+
+    def __init__(self, context):
+        self.context = context
+        self.model = context.wrap_model(torch.nn.Linear(1, 1, bias=False))
+        with torch.no_grad():
+            self.model.weight.fill_(0.0)
+        self.counter = _CountingCallback()
+        self.seen = []
+
+    def build_callbacks(self):
+        return {"counter": self.counter, "legacy": _LegacyEpochCallback()}
+
+    def build_training_data_loader(self):
+        return pytorch.DataLoader(torch.utils.data.TensorDataset(torch.arange(16).float()), batch_size=2)  # epoch = 8 batches
+
+    def build_validation_data_loader(self):
+        return pytorch.DataLoader(torch.utils.data.TensorDataset(torch.arange(6).float()), batch_size=2)
+
+    def train_batch(self, batch, epoch_idx, batch_idx):
+        self.seen.append((epoch_idx, batch_idx, float(batch[0][0])))
+        with torch.no_grad():
+            self.model.weight.add_(1.0)
+        return {"loss": float(batch_idx)}
+
+    def evaluate_batch(self, batch):  # no batch_idx parameter: the older signature
+        return {"val_loss": float(self.model.weight) + float(batch[0].sum())}
+
+
+def test_trainer_loop_periods_callbacks_and_resume(tmp_path):
+    """Trainer.fit as the reference's local training loop (_pytorch_trial.py:626-820): hook counts for the three
+    period settings of the reference's test_callbacks (test_pytorch_trial.py:401-497), checkpoint contents,
+    and continuing from a checkpoint at the right batch with the weights, counters and callback state restored."""
+    _LegacyEpochCallback.calls = 0
+    base = dict(trial_startups=1, training_started_times=1, training_epochs_started=2, training_epochs_ended=2, trial_shutdowns=1)
+    cases = [
+        # (validation_period, checkpoint_period) -> validations, checkpoints, workloads
+        ((None, None), dict(validation_steps_started=1, validation_steps_ended=1, checkpoints_written=1, checkpoints_uploaded=1, training_workloads_ended=1)),
+        ((pytorch.Batch(8), None), dict(validation_steps_started=2, validation_steps_ended=2, checkpoints_written=2, checkpoints_uploaded=2, training_workloads_ended=2)),
+        ((None, pytorch.Epoch(1)), dict(validation_steps_started=1, validation_steps_ended=1, checkpoints_written=2, checkpoints_uploaded=2, training_workloads_ended=2)),
+    ]
+    for k, ((val_p, ckpt_p), want) in enumerate(cases):
+        ctx = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 2})
+        trial = _HostTrial(ctx)
+        trainer = pytorch.Trainer(trial, ctx)
+        reports = trainer.fit(max_length=pytorch.Epoch(2), validation_period=val_p, checkpoint_period=ckpt_p,
+                              reporting_period=pytorch.Batch(10 ** 9), checkpoint_policy="all", checkpoint_dir=str(tmp_path / f"case{k}"))
+        assert trial.counter.counts == dict(base, **want), (k, trial.counter.counts)
+        assert _LegacyEpochCallback.calls == 2 * (k + 1)
+        assert [r["steps_completed"] for r in reports] == ([16] if k == 0 else [8, 16])
+        assert len(trainer.checkpoints) == want["checkpoints_written"]
+        assert [v["steps_completed"] for v in trainer.validation_reports] == ([16] if k != 1 else [8, 16])
+        assert trial.counter.val_outputs == [3] * want["validation_steps_started"]  # 3 validation batches, as host values
+        # avg over 3 batches of (weight + x0 + x1): weight = batches trained
+        last = trainer.validation_reports[-1]["validation_metrics"]["val_loss"]
+        assert last == 16.0 + (1 + 5 + 9) / 3.0
+        assert trial.counter.workloads[-1][0]["loss"] == (np.mean(range(8, 16)) if k else np.mean(range(16)))
+        assert [s[1] for s in trial.seen] == list(range(16)) and trial.seen[8][0] == 1 and trial.seen[8][2] == 0.0  # epoch 1 restarts the data
+
+    # checkpoint_policy "best" falls back to "all" off-cluster; "none" leaves only the end-of-training checkpoint
+    ctx = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 2})
+    trial = _HostTrial(ctx)
+    trainer = pytorch.Trainer(trial, ctx)
+    trainer.fit(max_length=pytorch.Batch(6), validation_period=pytorch.Batch(2), checkpoint_policy="none", checkpoint_dir=str(tmp_path / "none"))
+    assert trial.counter.counts["validation_steps_ended"] == 3 and trial.counter.counts["checkpoints_written"] == 1
+    uuid = trainer.checkpoints[-1]
+    ckpt = tmp_path / "none" / uuid
+    assert sorted(p.name for p in ckpt.iterdir()) == ["load_data.json", "metadata.json", "state_dict.pth", "trial_state.pkl"]
+    saved = torch.load(ckpt / "state_dict.pth", weights_only=False)
+    assert saved["callbacks"]["counter"] == {"workloads_seen": 3} and float(saved["models_state_dict"][0]["weight"]) == 6.0
+
+    # continue from it: same trial id -> counters continue, the loader resumes at batch 6, callback state comes back
+    ctx2 = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 2})
+    trial2 = _HostTrial(ctx2)
+    trainer2 = pytorch.Trainer(trial2, ctx2)
+    reports = trainer2.fit(max_length=pytorch.Batch(10), reporting_period=pytorch.Batch(2), latest_checkpoint=uuid,
+                           checkpoint_policy="none", checkpoint_dir=str(tmp_path / "none"))
+    assert [s[1] for s in trial2.seen] == [6, 7, 8, 9] and trial2.seen[0][2] == 12.0 and trial2.seen[2][2] == 0.0
+    assert float(trial2.model.weight) == 10.0 and trial2.counter.loaded_from == {"workloads_seen": 3}
+    assert [r["steps_completed"] for r in reports] == [8, 10]
+    assert trial2.counter.counts["training_epochs_started"] == 1 and trial2.counter.counts["training_epochs_ended"] == 1  # epoch 0 ends at batch 8
+
+    # misuse
+    with pytest.raises(ValueError, match="max_length must be defined in local training mode"):
+        pytorch.Trainer(trial2, ctx2).fit()
+    with pytest.raises(ValueError, match="checkpoint_policy"):
+        pytorch._PyTorchTrialController(trial2, ctx2, max_length=1, checkpoint_policy="sometimes")
+
+    class BothEval(_HostTrial):
+        def evaluate_full_dataset(self, data_loader):
+            return {"val_loss": 0.0}
+
+    ctx3 = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 2})
+    with pytest.raises(det.errors.InvalidExperimentException, match="exactly one of"):
+        pytorch.Trainer(BothEval(ctx3), ctx3).fit(max_length=pytorch.Batch(1), checkpoint_dir=str(tmp_path / "x"))
+
+    class FullEval(pytorch.PyTorchTrial):
+        def __init__(self, context):
+            self.context = context
+            context.wrap_model(torch.nn.Linear(1, 1))
+
+        def build_training_data_loader(self):
+            return pytorch.DataLoader(torch.utils.data.TensorDataset(torch.arange(4).float()), batch_size=2)
+
+        def build_validation_data_loader(self):
+            return pytorch.DataLoader(torch.utils.data.TensorDataset(torch.arange(4).float()), batch_size=2)
+
+        def train_batch(self, batch, epoch_idx, batch_idx):
+            return {"loss": 1.0}
+
+        def evaluate_full_dataset(self, data_loader):
+            return {"n": sum(len(b[0]) for b in data_loader)}
+
+    ctx4 = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 2})
+    t4 = pytorch.Trainer(FullEval(ctx4), ctx4)
+    t4.fit(max_length=pytorch.Batch(1), checkpoint_dir=str(tmp_path / "full"))
+    assert t4.validation_reports == [{"steps_completed": 1, "validation_metrics": {"n": 4}}]
