@@ -54,7 +54,7 @@ def test_train_units():
         t._to_batches(pytorch.Epoch(1), None)
 
 
-def _run_experiment(config: str, tmp_path: pathlib.Path) -> list:
+def _run_experiment(config: str, tmp_path: pathlib.Path, FIX: pathlib.Path = FIX, extra_env=None) -> list:
     """Run the experiment's own `entrypoint:` the way a container would, on this box."""
     conf = yaml.safe_load((FIX / config).read_text())
     entry = conf["entrypoint"]
@@ -63,7 +63,7 @@ def _run_experiment(config: str, tmp_path: pathlib.Path) -> list:
     report = tmp_path / "reports.json"
     env = dict(os.environ, DET_EXPERIMENT_CONFIG=str(FIX / config), DET_REPORT_FILE=str(report),
                PYTHONPATH=os.pathsep.join([str(ROOT / "determined_clone_b200" / "compat"), str(ROOT), os.environ.get("PYTHONPATH", "")]),
-               C10D_PORT="29433")
+               C10D_PORT="29433", **(extra_env or {}))
     subprocess.run(argv, cwd=FIX, env=env, check=True, timeout=600)
     return json.loads(report.read_text())
 
@@ -85,3 +85,31 @@ def test_identity_experiment_matches_closed_form(lib, config, tmp_path):
     want = O.identity_expected_weights()[:16]
     np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-9)
     assert got[0] == 0.0 and got[1] == got[2] != 0.0  # no update on non-boundary batches
+
+
+def test_legacy_entrypoint_drives_validation_and_checkpoint_policy_from_the_config(tmp_path):
+    """`entrypoint: model_def:Trial` with min_validation_period, checkpoint_policy: best, perform_initial_validation and
+    scheduling_unit read from the experiment YAML as the reference's harness does (exec/harness.py:186-200).  The
+    trial has no optimizer, so this runs on the CPU.  The validation metric |w| goes 2.0 (initial, at batch 0, where
+    the reference too considers the checkpoint current), 1.0, 0.0, 1.0: 'best' checkpoints after the validations at
+    batches 2 and 4 but not after the one at 6; the checkpoint at 6 is the end-of-training one."""
+    import pickle
+
+    host = FIX.parent / "host_only"
+    ckpts = tmp_path / "ckpts"
+    reports = _run_experiment("const.yaml", tmp_path, FIX=host, extra_env={"DET_CHECKPOINT_DIR": str(ckpts)})
+    # reports at scheduling_unit (3, 6) and wherever a validation closes the period (2, 4)
+    assert [r["steps_completed"] for r in reports] == [2, 3, 4, 6]
+    assert [b["loss"] for r in reports for b in r["batch_metrics"]] == [1.5, 1.0, 0.5, 0.0, -0.5, -1.0]
+    saved = sorted(ckpts.iterdir(), key=lambda d: d.stat().st_mtime)
+    steps = []
+    for d in saved:
+        with (d / "trial_state.pkl").open("rb") as f:
+            state = pickle.load(f)
+        steps.append((state["batches_trained"], state["last_val"]))
+    assert steps == [(2, 2), (4, 4), (6, 6)]  # (6, 6): not "best" (|w| = 1.0 again), written because training ended
+    meta = json.loads((saved[-1] / "metadata.json").read_text())
+    assert meta["steps_completed"] == 6 and meta["format"] == "pickle"
+    load_data = json.loads((saved[-1] / "load_data.json").read_text())
+    assert load_data["trial_cls_spec"] == "model_def:HostOnlyTrial" and load_data["hparams"]["start"] == 2.0
+    assert load_data["experiment_config"]["searcher"]["metric"] == "distance"
