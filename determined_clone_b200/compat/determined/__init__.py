@@ -5,6 +5,7 @@ import sys
 
 import determined_clone_b200 as _impl
 from determined_clone_b200 import core, errors, pytorch, util  # noqa: F401
+from determined_clone_b200._import import import_from_path  # noqa: F401
 from determined_clone_b200._info import ClusterInfo, get_cluster_info  # noqa: F401
 from determined_clone_b200._trial_controller import _DistributedBackend  # noqa: F401
 

@@ -8,3 +8,10 @@ class InternalException(Exception):
 
 class InvalidExperimentException(Exception):
     """The user's experiment or trial code misuses the API."""
+
+
+class InvalidCheckpointException(Exception):
+    """A checkpoint directory does not hold what its format promises (reference errors.py:45-51)."""
+
+    def __init__(self) -> None:
+        super().__init__("Invalid checkpoint.")

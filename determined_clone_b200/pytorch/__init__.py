@@ -25,3 +25,4 @@ from determined_clone_b200.pytorch._gradsync import GradSyncEngine
 from determined_clone_b200.pytorch._pytorch_context import PyTorchExperimentalContext, PyTorchTrialContext
 from determined_clone_b200.pytorch._pytorch_trial import PyTorchTrial, TorchData, _PyTorchTrialController, _TrialState
 from determined_clone_b200.pytorch._trainer import Batch, Epoch, Record, Trainer, TrainUnit, init
+from determined_clone_b200.pytorch._load import CheckpointLoadContext, load_trial_from_checkpoint_path

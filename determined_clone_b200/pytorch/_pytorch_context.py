@@ -167,6 +167,7 @@ class PyTorchTrialContext(_PyTorchReducerContext):
         self._fp16_compression_default = False
         self._average_aggregated_gradients_default = True
         self._is_pre_trainer = False
+        self._load_only = False
         self._enable_tensorboard_logging = bool(enable_tensorboard_logging)
         self._stop_requested = False
         self._tensorboard_path: Any = None
@@ -447,6 +448,9 @@ class PyTorchTrialContext(_PyTorchReducerContext):
                 "only one optimizer's flat buffers"
             )
         self._owned_params |= mine
+        if self._load_only:  # CheckpointLoadContext: the optimizer is registered so that its state can be restored
+            self.optimizers.append(optimizer)
+            return optimizer
         # managed or not (Trainer / Core API use): the same engine carries the step
         self._engines[optimizer] = _gradsync.GradSyncEngine(
             optimizer,
@@ -669,6 +673,8 @@ class PyTorchTrialContext(_PyTorchReducerContext):
             return
         eng = self._engines.get(optimizer)
         if eng is None:
+            if self._load_only:
+                raise errors.InvalidExperimentException("a CheckpointLoadContext only loads trials; use pytorch.init() to train")
             raise errors.InvalidExperimentException("step_optimizer() needs an optimizer returned by wrap_optimizer()")
 
         present = eng.finish_window()

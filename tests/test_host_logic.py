@@ -5,6 +5,7 @@ import ctypes
 import pathlib
 import re
 import socket
+import sys
 import threading
 import traceback
 from typing import Any, Callable, List
@@ -921,3 +922,78 @@ def test_trainer_loop_periods_callbacks_and_resume(tmp_path):
     t4 = pytorch.Trainer(FullEval(ctx4), ctx4)
     t4.fit(max_length=pytorch.Batch(1), checkpoint_dir=str(tmp_path / "full"))
     assert t4.validation_reports == [{"steps_completed": 1, "validation_metrics": {"n": 4}}]
+
+
+def test_load_trial_from_checkpoint_path_round_trip(tmp_path):
+    """A checkpoint written by this harness comes back as a trial object with the trained weights, without a GPU
+    and without a training context (reference _load.py:68-237)."""
+    ctx = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 2})
+    trainer = pytorch.Trainer(_HostTrial(ctx), ctx)
+    trainer.fit(max_length=pytorch.Batch(5), checkpoint_policy="none", checkpoint_dir=str(tmp_path))
+    ckpt = tmp_path / trainer.checkpoints[-1]
+    trial = pytorch.load_trial_from_checkpoint_path(str(ckpt), trial_class=_HostTrial, torch_load_kwargs={"map_location": "cpu"})
+    assert isinstance(trial, _HostTrial) and isinstance(trial.context, pytorch.CheckpointLoadContext)
+    assert float(trial.model.weight.detach()) == 5.0
+    with pytest.warns(FutureWarning, match="torch_load_kwargs"):
+        pytorch.load_trial_from_checkpoint_path(str(ckpt), trial_class=_HostTrial, map_location="cpu")
+    with pytest.raises(ValueError, match="kwargs may not be set"):
+        pytorch.load_trial_from_checkpoint_path(str(ckpt), trial_class=_HostTrial, torch_load_kwargs={"map_location": "cpu"}, map_location="cpu")
+    # without trial_class the class named in load_data.json is imported (here: this very test module) ...
+    import json
+
+    again = pytorch.load_trial_from_checkpoint_path(str(ckpt))
+    assert type(again).__name__ == "_HostTrial" and float(again.model.weight.detach()) == 5.0
+    # ... and a name that cannot be imported fails loudly
+    info = json.loads((ckpt / "load_data.json").read_text())
+    (ckpt / "load_data.json").write_text(json.dumps(dict(info, trial_cls_spec="no_such_module_anywhere:Trial")))
+    with pytest.raises(ValueError, match="Automatic import logic failed to import Trial class"):
+        pytorch.load_trial_from_checkpoint_path(str(ckpt))
+    (ckpt / "load_data.json").unlink()
+    (ckpt / "metadata.json").unlink()
+    with pytest.raises(AssertionError, match="does not have either load_data.json or metadata.json"):
+        pytorch.load_trial_from_checkpoint_path(str(ckpt), trial_class=_HostTrial)
+    # a load-only context registers optimizers but cannot train
+    lctx = pytorch.CheckpointLoadContext()
+    m = lctx.wrap_model(torch.nn.Linear(1, 1))
+    opt = lctx.wrap_optimizer(torch.optim.SGD(m.parameters(), lr=0.1))
+    assert lctx.optimizers == [opt] and not lctx._engines
+    with pytest.raises(det.errors.InvalidExperimentException, match="only loads trials"):
+        lctx.step_optimizer(opt)
+
+
+@pytest.mark.skipif(not ANCIENT.exists(), reason="the reference tree is only present in the build container")
+@pytest.mark.parametrize("ckpt,istrial,trial_spec,trial_kwargs", [
+    # the cases of the reference's test_trial_checkpoint_loading (test_pytorch_trial.py:1367-1405)
+    ("0.13.13-pytorch-old", False, None, {}),
+    ("0.13.13-pytorch-flex", True, None, {}),
+    ("0.17.6-pytorch", True, None, {}),
+    ("0.17.7-pytorch", True, None, {}),
+    ("0.20.0-pytorch", True, None, {}),
+    ("0.21.0-pytorch", True, None, {"lr": 0.001}),
+    ("0.21.0-pytorch-main", True, "train:OneVarPytorchTrial", {"lr": 0.001}),
+    ("0.21.0-pytorch", True, "model_def:OneVarPytorchTrial", {"lr": 0.001}),
+])
+def test_trials_load_from_checkpoints_of_old_reference_releases(monkeypatch, ckpt, istrial, trial_spec, trial_kwargs):
+    """The reference's own old checkpoints, read in place, with the user code stored inside them (`code/`, written
+    against `import determined`) importing this repo through the compat package."""
+    import importlib
+
+    monkeypatch.syspath_prepend(str(pathlib.Path(det.__file__).parent / "compat"))
+    for name in [n for n in sys.modules if n == "determined" or n.startswith("determined.")]:
+        monkeypatch.delitem(sys.modules, name)
+    directory = ANCIENT / ckpt
+    trial_class = None
+    if trial_spec:
+        with det.import_from_path(directory / "code"):
+            module, cls = trial_spec.split(":")
+            trial_class = getattr(importlib.import_module(module), cls)
+    loaded = pytorch.load_trial_from_checkpoint_path(str(directory), trial_class=trial_class, trial_kwargs=trial_kwargs,
+                                                      torch_load_kwargs={"map_location": "cpu"})
+    saved = torch.load(directory / "state_dict.pth", map_location="cpu", weights_only=False)["models_state_dict"][0]
+    if istrial:
+        assert isinstance(loaded, pytorch.PyTorchTrial), type(loaded)
+        assert torch.equal(loaded.context.models[0].weight, saved["weight"])
+    else:
+        assert isinstance(loaded, torch.nn.Module) and not isinstance(loaded, pytorch.PyTorchTrial)
+        assert torch.equal(loaded.weight, saved["weight"])
+    assert "model_def" not in sys.modules and "train" not in sys.modules  # nothing of the checkpoint's code stays imported
