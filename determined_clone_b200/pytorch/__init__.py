@@ -19,7 +19,8 @@ from determined_clone_b200.pytorch._metric_utils import (
 )
 from determined_clone_b200.pytorch._lr_scheduler import LRScheduler
 from determined_clone_b200.pytorch._callback import PyTorchCallback
-from determined_clone_b200.pytorch._data import DataLoader, data_length
+from determined_clone_b200.pytorch import samplers
+from determined_clone_b200.pytorch._data import DataLoader, _dataset_repro_warning, adapt_batch_sampler, data_length, to_device
 from determined_clone_b200.pytorch._comm import Comm
 from determined_clone_b200.pytorch._gradsync import GradSyncEngine
 from determined_clone_b200.pytorch._pytorch_context import PyTorchExperimentalContext, PyTorchTrialContext

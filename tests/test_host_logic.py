@@ -997,3 +997,129 @@ def test_trials_load_from_checkpoints_of_old_reference_releases(monkeypatch, ckp
         assert isinstance(loaded, torch.nn.Module) and not isinstance(loaded, pytorch.PyTorchTrial)
         assert torch.equal(loaded.weight, saved["weight"])
     assert "model_def" not in sys.modules and "train" not in sys.modules  # nothing of the checkpoint's code stays imported
+
+
+def test_samplers_reference_vectors():
+    """Known answers of the reference's sampler tests (harness/tests/experiment/pytorch/test_pytorch_data.py:27-135):
+    which records / batches each stage lets through, and the two permutations RandomState(777) produces."""
+    from torch.utils import data as tud
+
+    S = pytorch.samplers
+    seq = tud.SequentialSampler(range(15))
+    assert len(S.SkipSampler(seq, 2)) == 15 and list(S.SkipSampler(seq, 2)) == list(range(2, 15))
+    batches = tud.BatchSampler(seq, batch_size=2, drop_last=False)
+    skipped = S.SkipBatchSampler(batches, 2)
+    assert len(skipped) == 8 and list(skipped) == list(batches)[2:]
+    assert list(S.SkipBatchSampler(batches, 100)) == []
+
+    ten = tud.SequentialSampler(range(10))
+    rep = iter(S.RepeatSampler(ten))
+    assert len(S.RepeatSampler(ten)) == 10 and [next(rep) for _ in range(30)] == list(range(10)) * 3
+    threes = tud.BatchSampler(ten, 3, False)
+    rep = iter(S.RepeatBatchSampler(threes))
+    assert len(S.RepeatBatchSampler(threes)) == 4 and [next(rep) for _ in range(12)] == list(threes) * 3
+
+    nineteen = tud.SequentialSampler(range(19))
+    want = [[0, 4, 8, 12, 16], [1, 5, 9, 13, 17], [2, 6, 10, 14, 18], [3, 7, 11, 15]]
+    for rank in range(4):
+        d = S.DistributedSampler(nineteen, 4, rank)
+        assert list(d) == want[rank] and len(d) == len(want[rank])
+    pairs = tud.BatchSampler(nineteen, batch_size=2, drop_last=False)
+    want = [[[0, 1], [8, 9], [16, 17]], [[2, 3], [10, 11], [18]], [[4, 5], [12, 13]], [[6, 7], [14, 15]]]
+    for rank in range(4):
+        d = S.DistributedBatchSampler(pairs, 4, rank)
+        assert list(d) == want[rank] and len(d) == len(want[rank])
+    assert list(S.DistributedBatchSampler(pairs, 1, 0)) == list(pairs)
+    for bad in ((4, -1, "non-negative"), (0, 0, "greater than zero"), (2, 2, "less than num_workers")):
+        with pytest.raises(ValueError, match=bad[2]):
+            S.DistributedBatchSampler(pairs, bad[0], bad[1])
+
+    shuffled = S.ReproducibleShuffleSampler(tud.SequentialSampler(range(5)), 777)
+    assert list(shuffled) == [0, 4, 1, 2, 3] and list(shuffled) == [2, 0, 1, 3, 4] and len(shuffled) == 5
+    fives = tud.BatchSampler(ten, batch_size=2, drop_last=False)
+    for cls in (S.ReproducibleShuffleSampler, S.ReproducibleShuffleBatchSampler):
+        sb = cls(fives, 777)
+        assert list(sb) == [[0, 1], [8, 9], [2, 3], [4, 5], [6, 7]] and list(sb) == [[4, 5], [0, 1], [2, 3], [6, 7], [8, 9]]
+
+
+def test_data_loader_repeats_shards_and_skips_like_the_reference():
+    """determined.pytorch.DataLoader -> get_data_loader (reference _data.py:244-313): endless, resumable, and dealt to
+    the ranks along the ENDLESS sequence -- with 5 batches and 2 ranks the ranks swap batches every epoch."""
+    from torch.utils import data as tud
+
+    ds = tud.TensorDataset(torch.arange(10).float())
+    dl = pytorch.DataLoader(ds, batch_size=2)
+    assert len(dl) == 5 and [b[0].tolist() for b in dl] == [[0.0, 1.0], [2.0, 3.0], [4.0, 5.0], [6.0, 7.0], [8.0, 9.0]]
+
+    def first(loader, n):
+        it = iter(loader)
+        return [int(next(it)[0][0]) // 2 for _ in range(n)]  # batch numbers
+
+    assert first(dl.get_data_loader(repeat=True, skip=2), 9) == [2, 3, 4, 0, 1, 2, 3, 4, 0]
+    r0 = dl.get_data_loader(repeat=True, num_replicas=2, rank=0)
+    r1 = dl.get_data_loader(repeat=True, num_replicas=2, rank=1)
+    assert (len(r0), len(r1)) == (3, 2)
+    assert first(r0, 7) == [0, 2, 4, 1, 3, 0, 2] and first(r1, 7) == [1, 3, 0, 2, 4, 1, 3]
+    # continuing after 3 batches per rank: exactly the tail of the sequences above
+    assert first(dl.get_data_loader(repeat=True, skip=3, num_replicas=2, rank=0), 4) == [1, 3, 0, 2]
+    assert first(dl.get_data_loader(repeat=True, skip=3, num_replicas=2, rank=1), 4) == [2, 4, 1, 3]
+    # validation: one pass, sharded, ranks may get different counts
+    assert [int(b[0][0]) // 2 for b in dl.get_data_loader(num_replicas=2, rank=1)] == [1, 3]
+    # every rank shuffles alike under the same seed
+    torch.manual_seed(3)
+    a = [b[0].tolist() for b in pytorch.DataLoader(ds, batch_size=2, shuffle=True)]
+    torch.manual_seed(3)
+    b = [b[0].tolist() for b in pytorch.DataLoader(ds, batch_size=2, shuffle=True)]
+    assert a == b and sorted(x for bb in a for x in bb) == list(map(float, range(10)))
+    assert pytorch.DataLoader(ds, drop_last=True, shuffle=True, batch_size=2).get_data_loader() is not None
+
+    # the argument checks of torch's DataLoader, made at construction
+    class Stream(tud.IterableDataset):
+        def __iter__(self):
+            return iter(range(3))
+
+    for kwargs, text in (
+        (dict(dataset=Stream()), "IterableDatasets are not supported"),
+        (dict(batch_size=None), "batch_sampler=None and batch_size=None"),
+        (dict(num_workers=-1), "num_workers option should be non-negative"),
+        (dict(timeout=-1), "timeout option should be non-negative"),
+        (dict(prefetch_factor=2), "prefetch_factor option could only be specified in multiprocessing"),
+        (dict(persistent_workers=True), "persistent_workers option needs num_workers > 0"),
+        (dict(sampler=tud.SequentialSampler(ds), shuffle=True), "sampler option is mutually exclusive with shuffle"),
+        (dict(batch_sampler=tud.BatchSampler(tud.SequentialSampler(ds), 2, False), batch_size=2), "batch_sampler option is mutually exclusive"),
+    ):
+        with pytest.raises(ValueError, match=text):
+            pytorch.DataLoader(**dict(dict(dataset=ds), **kwargs))
+    custom = pytorch.DataLoader(ds, batch_sampler=tud.BatchSampler(tud.SequentialSampler(ds), 5, False))
+    assert [len(b[0]) for b in custom] == [5, 5] and custom.batch_size is None
+
+
+def test_data_length_and_to_device_reference_cases(caplog):
+    """reference test_pytorch_data.py:176-236."""
+    n, t = np.array([0]), torch.Tensor(np.array([0]))
+    for data in ([n], [t], [[n]], (n,), (t,), {"a": t}, {"a": n}, {"a": [[t]]}):
+        assert pytorch.data_length(data) == 1
+    assert pytorch.data_length(torch.zeros(7, 3)) == 7
+    with pytest.raises(ValueError, match="at least one"):
+        pytorch.data_length({})
+    with pytest.raises(ValueError, match="list of inputs"):
+        pytorch.data_length([])
+    with pytest.raises(TypeError, match="Data of incorrect type"):
+        pytorch.data_length(0)
+
+    nested = {"input_1": torch.Tensor(1), "input_3": "str", "input_4": 1}
+    assert pytorch.to_device(nested, "cpu") == nested
+    moved = pytorch.to_device(np.array([0, 1, 2]), "cpu")
+    assert isinstance(moved, torch.Tensor) and moved.tolist() == [0, 1, 2]
+    assert pytorch.to_device((np.array(["a"]), [torch.ones(1)]), "cpu")[0].dtype.kind == "U"  # strings stay numpy
+    import logging
+
+    for keep, want in ((True, 1), (False, 2)):
+        caplog.clear()
+        seen = set() if keep else None
+        with caplog.at_level(logging.WARNING, logger="determined.pytorch"):
+            pytorch.to_device(["string_data", "string_data"], "cpu", seen)
+            pytorch.to_device(["string_data", "string_data"], "cpu", seen)
+        msgs = [r.getMessage() for r in caplog.records]
+        assert len(msgs) == want and all("not able to move data" in m for m in msgs)
+    assert "not a subclass of det.pytorch.DataLoader" in pytorch._dataset_repro_warning("build_training_data_loader", object())
