@@ -208,15 +208,20 @@ class _PyTorchTrialController:
 
     # ---- training loop ------------------------------------------------------------------------------
     def run(self) -> None:
+        restore = self._checkpoint_path(self.latest_checkpoint) if self.latest_checkpoint is not None else None
+        if restore is not None and self.training_loader is None:
+            self.batches_trained = self._peek_batches_trained(restore)  # the loader skips what was trained
         with contextlib.ExitStack() as stack:
             for cb in self.callbacks.values():
                 cb.on_trial_startup(self.batches_trained, self.latest_checkpoint)
                 stack.callback(cb.on_trial_shutdown)  # also on an exception or a stop request
-            if self.latest_checkpoint is not None:
-                # before the loaders are built: they skip the batches the restored trial has already seen
-                self._load(self._checkpoint_path(self.latest_checkpoint))
             if self.training_loader is None:
                 self._set_data_loaders()
+            it = iter(self.training_loader)
+            if restore is not None:
+                # after the training iterator exists, as in the reference (:583-612): creating it draws from torch's
+                # global generator, and a restored run must continue the generator exactly where the checkpoint left it
+                self._load(restore)
             for cb in self.callbacks.values():
                 cb.on_training_start()
             if self.context.profiler:
@@ -224,7 +229,7 @@ class _PyTorchTrialController:
             if self.step_zero_validation and not self.val_from_previous_run and self.batches_trained == 0:
                 self._validation_step()
             self.context.reset_reducers()
-            self._train_loop(iter(self.training_loader), [], None, 0, time.time())
+            self._train_loop(it, [], None, 0, time.time())
             # end of training: the reference validates and checkpoints whatever is not current (:810-814)
             if self.final_validation and self.state.last_val != self.batches_trained:
                 self._validation_step()
@@ -567,6 +572,15 @@ class _PyTorchTrialController:
         elif (path / "workload_sequencer.pkl").exists():
             with (path / "workload_sequencer.pkl").open("rb") as f:
                 self._load_wlsq_state(pickle.load(f))
+
+    def _peek_batches_trained(self, path: pathlib.Path) -> int:
+        """batches_trained a checkpoint will restore, read ahead of _load() because the data loader needs it."""
+        for name, key in (("trial_state.pkl", "batches_trained"), ("workload_sequencer.pkl", "steps_completed")):
+            if (path / name).exists():
+                with (path / name).open("rb") as f:
+                    state = pickle.load(f)
+                return int(state.get(key) or 0) if state.get("trial_id") == self.trial_id else 0
+        return self.batches_trained
 
     def _get_epoch_idx(self, batch_id: int) -> int:
         return batch_id // self.context._epoch_len if self.context._epoch_len else 0

@@ -179,9 +179,8 @@ class Trainer:
             latest_checkpoint=latest_checkpoint, final_validation=True, final_checkpoint=True,
             trial_id=ctx.get_trial_id(),
         )
-        if latest_checkpoint is not None:
-            controller._load(controller._checkpoint_path(latest_checkpoint))  # before the loaders: they skip what was trained
-            controller.latest_checkpoint = None
+        if latest_checkpoint is not None:  # the loaders skip what the restored trial has trained; run() restores the rest
+            controller.batches_trained = controller._peek_batches_trained(controller._checkpoint_path(latest_checkpoint))
         controller._set_data_loaders()
         epoch_len = ctx._epoch_len
         controller.max_length = controller.batches_trained + 1 if test_mode else self._to_batches(max_length, epoch_len)
