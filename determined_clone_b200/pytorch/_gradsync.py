@@ -46,6 +46,10 @@ FIRST_BUCKET_BYTES = 1 << 20
 _BUCKET_MB_ENV = __import__("os").environ.get("DGS_BUCKET_MB")
 BUCKET_BYTES = (int(_BUCKET_MB_ENV) << 20) if _BUCKET_MB_ENV else 0  # 0 = adaptive
 MIN_BUCKET_BYTES, MAX_BUCKET_BYTES = 25 << 20, 128 << 20
+# Experiment switch, off by default: flat sets smaller than this many MiB become ONE bucket --
+# one allreduce per step instead of a 1 MiB bucket plus 25 MiB ones -- for launch-bound small models, where each
+# NCCL enqueue costs the host more than the lost overlap costs the GPU.
+ONE_BUCKET_BELOW_BYTES = int(__import__("os").environ.get("DGS_ONE_BUCKET_BELOW_MB", "0")) << 20
 
 
 def _align(n: int) -> int:
@@ -302,8 +306,11 @@ class GradSyncEngine:
     def _cut_buckets(self, fs: _FlatSet) -> None:
         itemsize = torch.empty(0, dtype=fs.wire_dtype).element_size()
         cap = self.bucket_bytes or adaptive_bucket_cap(fs.total * itemsize)
+        first = self.first_bucket_bytes
+        if fs.total * itemsize < ONE_BUCKET_BELOW_BYTES:
+            first = cap = fs.total * itemsize + 1  # never reached: everything lands in the one trailing bucket
         for begin, end, idxs in plan_buckets([t.off for t in fs.tensors], [t.numel for t in fs.tensors], fs.total, itemsize,
-                                             self.first_bucket_bytes, cap):
+                                             first, cap):
             fs.buckets.append(_Bucket(begin, end, idxs))
         for bi, b in enumerate(fs.buckets):
             b.segs = (_lib.Seg * len(b.tensors))()
