@@ -1193,3 +1193,31 @@ def test_epoch_bookkeeping_agrees_across_ranks(dataset_len):
     per_epoch = (dataset_len + 1) // 2
     want = [(k, k // per_epoch, k // per_epoch, k % per_epoch == 0, k % per_epoch == per_epoch - 1) for k in range(10)]
     assert run_ranks(1, 2, rank_main) == [want, want]
+
+
+def test_lr_scheduler_coupling_matches_rates_recorded_from_the_reference():
+    """tests/golden/lr_schedule.json holds the learning rates the unmodified reference controller produced for every
+    step mode x aggregation_frequency x scheduler frequency (made by tests/golden/make_golden_lr.py).  The same
+    StepLR(gamma=0.5) driven by this repo's _auto_step_lr_scheduler_per_batch must show the same rate at every
+    batch -- powers of two, compared exactly."""
+    import json
+
+    golden = json.loads((pathlib.Path(__file__).parent / "golden" / "lr_schedule.json").read_text())
+    assert len(golden["cases"]) == 36
+    for case in golden["cases"]:
+        agg, freq = case["aggregation_frequency"], case["frequency"]
+        ctx = pytorch.PyTorchTrialContext(aggregation_frequency=agg)
+        ctx._epoch_len = golden["epoch_len"]
+        ctl = pytorch._PyTorchTrialController.__new__(pytorch._PyTorchTrialController)
+        ctl.context = ctx
+        opt = torch.optim.SGD([torch.nn.Parameter(torch.zeros(1))], lr=1.0)
+        opt._opt_called = True  # no optimizer.step() happens in this replay; silences torch's ordering warning
+        sched = pytorch.LRScheduler(torch.optim.lr_scheduler.StepLR(opt, step_size=1, gamma=0.5),
+                                    getattr(pytorch.LRScheduler.StepMode, case["mode"]), freq)
+        got = []
+        for b in range(golden["batches"]):
+            got.append(opt.param_groups[0]["lr"])
+            ctx._current_batch_idx = b
+            ctl._auto_step_lr_scheduler_per_batch(b, sched)
+        got.append(opt.param_groups[0]["lr"])
+        assert got == case["lr"], (case["mode"], agg, freq)
