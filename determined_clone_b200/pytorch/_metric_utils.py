@@ -20,7 +20,7 @@ from typing import Any, Dict, List, Optional, Tuple, Union, cast
 import numpy as np
 import torch
 
-from determined_clone_b200 import _lib, core, util
+from determined_clone_b200 import _lib, core, errors, util
 from determined_clone_b200.pytorch._reducer import Reducer, _simple_reduce_metrics
 
 logger = logging.getLogger("determined.pytorch")
@@ -82,20 +82,23 @@ def _combine_and_average_training_metrics(
 
 
 def _prepare_metrics_reducers(reducer: Union[Reducer, Dict[str, Any]], keys: Any) -> Dict[str, Reducer]:
+    """One Reducer per validation metric, from what evaluation_reducer() returned: a single Reducer for all of
+    them, or a dict naming every metric (reference _metric_utils.py:105-127, same exception type and texts)."""
     if isinstance(reducer, dict):
         table = dict(reducer)
         if table.keys() != set(keys):
-            raise ValueError(
-                "Please provide a single evaluation reducer or provide a reducer for every validation "
-                f"metric. Expected keys: {keys}, provided keys: {table.keys()}."
+            raise errors.InvalidExperimentException(
+                "Please provide a single evaluation reducer or "
+                "provide a reducer for every validation metric. "
+                f"Expected keys: {keys}, provided keys: {table.keys()}.",
             )
-    elif isinstance(reducer, Reducer):
-        table = {k: reducer for k in keys}
     else:
-        raise ValueError(f"evaluation_reducer() returned an invalid reducer: {reducer!r}")
-    for k, r in table.items():
+        table = {k: reducer for k in keys}
+    for r in table.values():
         if not isinstance(r, Reducer):
-            raise ValueError(f"Please select `determined.pytorch.Reducer` for reducing validation metrics; got {r!r} for {k}.")
+            raise errors.InvalidExperimentException(
+                "Please select `determined.pytorch.Reducer` for reducing validation metrics.",
+            )
     return table
 
 

@@ -256,8 +256,20 @@ def test_metric_utils_reference_vectors():
     R = pytorch.Reducer
     assert metric_utils._prepare_metrics_reducers(R.AVG, ["a", "b"]) == {"a": R.AVG, "b": R.AVG}
     assert metric_utils._prepare_metrics_reducers({"a": R.SUM, "b": R.MAX}, ["a", "b"]) == {"a": R.SUM, "b": R.MAX}
-    with pytest.raises(ValueError):
+    # reference test_metric_utils.py:88-115: both misuses are InvalidExperimentException
+    with pytest.raises(det.errors.InvalidExperimentException, match="reducer for every validation metric"):
         metric_utils._prepare_metrics_reducers({"a": R.SUM}, ["a", "b"])
+    with pytest.raises(det.errors.InvalidExperimentException, match="reducer for every validation metric"):
+        metric_utils._prepare_metrics_reducers({}, {"loss1": 1, "loss2": 2}.keys())
+    with pytest.raises(det.errors.InvalidExperimentException, match="Please select `determined.pytorch.Reducer`"):
+        metric_utils._prepare_metrics_reducers({"loss1": R.AVG, "loss2": 2}, {"loss1": 1, "loss2": 2}.keys())
+    with pytest.raises(det.errors.InvalidExperimentException, match="Please select `determined.pytorch.Reducer`"):
+        metric_utils._prepare_metrics_reducers("avg", ["a"])
+    converted = metric_utils._convert_metrics_to_numpy({"loss1": 1, "loss2": torch.tensor(2)})
+    assert converted == {"loss1": 1, "loss2": np.array(2)} and isinstance(converted["loss2"], np.ndarray)
+    scaler = torch.amp.GradScaler("cpu")
+    ctx = pytorch.PyTorchTrialContext()
+    assert ctx.wrap_scaler(scaler) is scaler and ctx._scaler is scaler  # reference test_pytorch_context.py:54-57
 
 
 @pytest.mark.parametrize("size", [2, 3])
