@@ -39,6 +39,36 @@ def _stale() -> bool:
     return newest > LIB.stat().st_mtime
 
 
+def host_ext_path() -> pathlib.Path:
+    import sysconfig
+
+    return CSRC / ("_dgs_host" + (sysconfig.get_config_var("EXT_SUFFIX") or ".so"))
+
+
+def build_host(force: bool = False) -> pathlib.Path:
+    """g++ csrc/dgs_host.cpp -> csrc/_dgs_host.<abi>.so: the optional native host loop of the engine (a torch C++
+    extension; no CUDA code in it).  About 40 s of compile time, almost all of it torch's headers."""
+    import sysconfig
+
+    import torch
+    from torch.utils import cpp_extension
+
+    out, src = host_ext_path(), CSRC / "dgs_host.cpp"
+    if not force and out.exists() and out.stat().st_mtime >= src.stat().st_mtime:
+        return out
+    tmp = out.with_suffix(".tmp")
+    libs = cpp_extension.library_paths()
+    cmd = ["g++", "-O2", "-std=c++17", "-shared", "-fPIC", str(src), "-o", str(tmp), "-DTORCH_EXTENSION_NAME=_dgs_host",
+           f"-D_GLIBCXX_USE_CXX11_ABI={int(torch._C._GLIBCXX_USE_CXX11_ABI)}", "-I" + sysconfig.get_paths()["include"],
+           *("-I" + d for d in cpp_extension.include_paths()), *("-L" + d for d in libs),
+           "-ltorch", "-ltorch_cpu", "-ltorch_python", "-lc10", *("-Wl,-rpath," + d for d in libs)]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"g++ failed on dgs_host.cpp:\n{r.stdout}\n{r.stderr}")
+    os.replace(tmp, out)
+    return out
+
+
 def build(force: bool = False, verbose: bool = False) -> pathlib.Path:
     """Compile every CUDA source for sm_100a and link csrc/libdgs.so."""
     if not force and not _stale():

@@ -52,6 +52,27 @@ MIN_BUCKET_BYTES, MAX_BUCKET_BYTES = 25 << 20, 128 << 20
 ONE_BUCKET_BELOW_BYTES = int(__import__("os").environ.get("DGS_ONE_BUCKET_BELOW_MB", "0")) << 20
 
 
+def _load_host_ext() -> Any:
+    """The native host loop (csrc/dgs_host.cpp), only when asked for with DGS_HOST_EXT=1: it has been checked on
+    CPU tensors (tests/test_host_logic.py) but not yet measured on a GPU box, so the Python loops stay the default."""
+    if __import__("os").environ.get("DGS_HOST_EXT", "0") != "1":
+        return None
+    import importlib.util
+
+    from determined_clone_b200 import _build
+
+    path = _build.host_ext_path()
+    if not path.exists():
+        raise _lib.DgsError(f"DGS_HOST_EXT=1 but {path} is not built (python -c 'from determined_clone_b200 import _build; _build.build_host()')")
+    spec = importlib.util.spec_from_file_location("_dgs_host", str(path))
+    mod = importlib.util.module_from_spec(spec)  # type: ignore
+    spec.loader.exec_module(mod)  # type: ignore
+    return mod
+
+
+_host = _load_host_ext()
+
+
 def _align(n: int) -> int:
     return (n + ALIGN_ELEMS - 1) // ALIGN_ELEMS * ALIGN_ELEMS
 
@@ -120,13 +141,15 @@ class _Tensor:
 
 
 class _Bucket:
-    __slots__ = ("begin", "end", "tensors", "flushed", "reduced", "norm_off", "norm_n", "norm_done", "segs")
+    __slots__ = ("begin", "end", "tensors", "flushed", "reduced", "norm_off", "norm_n", "norm_done", "segs", "params", "every_tensor")
 
     def __init__(self, begin: int, end: int, tensors: List[int]) -> None:
         self.begin, self.end, self.tensors = begin, end, tensors
         self.norm_off = self.norm_n = 0  # this bucket's slots in the engine's norm partials
         self.norm_done = False  # pass 1 of the norm already ran on this bucket in this window
         self.segs: Any = None  # prebuilt dgs_seg[len(tensors)] (dst_off, numel fixed; src set per flush)
+        self.params: List[Any] = []  # the bucket's parameters, in table order
+        self.every_tensor: Dict[int, Any] = {}  # {tensor index: None}: "all of them" for _flush_bucket
         self.flushed = False  # wire produced for this window
         self.reduced = False  # allreduce issued for this window
 
@@ -152,6 +175,7 @@ class _FlatSet:
         self.acc_ptr: Any = None
         self.wire_ptr: Any = None
         self.segs_all: Any = None  # prebuilt dgs_seg[len(tensors)] for whole-set launches (single GPU)
+        self.params: List[Any] = []  # every parameter of the set, in table order
         self.group_runs: Optional[List[Tuple[int, int, int, List[_Tensor]]]] = None
         self.steady = False  # last step covered every parameter and left every state tensor as our view
         self.uniform_step: Optional[int] = None  # Adam: the common step count while all parameters move together
@@ -283,6 +307,7 @@ class GradSyncEngine:
             fs.dtype_code, fs.wire_code = _lib.dtype_code(fs.dtype), _lib.dtype_code(fs.wire_dtype)
             fs.acc_ptr, fs.wire_ptr = _ptr(fs.acc), _ptr(fs.wire)
             fs.segs_all = (_lib.Seg * len(fs.tensors))()
+            fs.params = [t.param for t in fs.tensors]
             for k, t in enumerate(fs.tensors):
                 fs.segs_all[k].dst_off, fs.segs_all[k].numel = t.off, t.numel
         # norm scratch: [whole-buffer partials of every set | per-bucket partials of every set]
@@ -314,6 +339,8 @@ class GradSyncEngine:
             fs.buckets.append(_Bucket(begin, end, idxs))
         for bi, b in enumerate(fs.buckets):
             b.segs = (_lib.Seg * len(b.tensors))()
+            b.params = [fs.tensors[ti].param for ti in b.tensors]
+            b.every_tensor = dict.fromkeys(b.tensors)
             for k, ti in enumerate(b.tensors):
                 t = fs.tensors[ti]
                 t.bucket = bi
@@ -371,21 +398,28 @@ class GradSyncEngine:
         communication.  Returns False, having touched nothing, when the case does not apply."""
         tensors, in_window = fs.tensors, fs.in_window
         state = in_window[0]
-        grads = [t.param.grad for t in tensors]
-        dtype = fs.dtype
-        for g in grads:
-            if g is None or g.dtype != dtype or g.is_sparse or not g.is_contiguous():
+        segs = fs.segs_all
+        if _host is not None:
+            if any(s != state for s in in_window) or any(b.flushed for b in fs.buckets):
                 return False
-        if any(s != state for s in in_window) or any(b.flushed for b in fs.buckets):
-            return False
+            grads = _host.take_grads(fs.params, ctypes.addressof(segs), fs.dtype_code)  # checks, table and p.grad = None natively
+            if grads is None:
+                return False
+        else:
+            grads = [t.param.grad for t in tensors]
+            dtype = fs.dtype
+            for g in grads:
+                if g is None or g.dtype != dtype or g.is_sparse or not g.is_contiguous():
+                    return False
+            if any(s != state for s in in_window) or any(b.flushed for b in fs.buckets):
+                return False
+            for k, g in enumerate(grads):  # `grads` keeps the tensors alive until the launch below
+                tensors[k].param.grad = None
+                segs[k].src = g.data_ptr()
         to_wire = self._final_pass
         if not to_wire and fs.acc is None:
             fs.acc = torch.zeros(fs.total, dtype=torch.float32, device=self.device)
             fs.acc_ptr = _ptr(fs.acc)
-        segs = fs.segs_all
-        for k, g in enumerate(grads):  # `grads` keeps the tensors alive until the launch below
-            tensors[k].param.grad = None
-            segs[k].src = g.data_ptr()
         mode = (_lib.READ_ACC if state else 0) | (_lib.WRITE_WIRE if to_wire else 0)
         _lib.calls.dgs_flatten_accumulate(segs, len(tensors), fs.dtype_code, fs.acc_ptr, fs.wire_ptr, fs.wire_code, mode,
                                           self.scale * self.unscale, _stream())
@@ -441,6 +475,13 @@ class GradSyncEngine:
         si, bi = self._sentinels[id(p)]  # type: ignore
         fs = self.sets[si]
         b = fs.buckets[bi]
+        if _host is not None and not b.flushed:
+            first_state = fs.in_window[b.tensors[0]]
+            if all(fs.in_window[ti] == first_state for ti in b.tensors):
+                taken = _host.take_grads(b.params, ctypes.addressof(b.segs), fs.dtype_code)
+                if taken is not None:  # else: incomplete bucket or gradients that need converting -> the general path below
+                    self._flush_bucket(si, bi, b.every_tensor, True, table_filled=True)
+                    return
         for ti in b.tensors:
             if fs.tensors[ti].param.grad is None:
                 return  # arrival order changed: leave the bucket to end_pass()
@@ -468,8 +509,10 @@ class GradSyncEngine:
             )
         return out
 
-    def _flush_bucket(self, si: int, bi: int, grads: Dict[int, torch.Tensor], to_wire: bool) -> None:
-        """Launch the flatten kernel over the gradients collected for this bucket in this pass."""
+    def _flush_bucket(self, si: int, bi: int, grads: Dict[int, Any], to_wire: bool, table_filled: bool = False) -> None:
+        """Launch the flatten kernel over the gradients collected for this bucket in this pass.  table_filled: the
+        bucket's prebuilt dgs_seg table already holds the gradients' addresses (native host loop) and `grads` only
+        names the tensors; the caller keeps the gradient tensors alive across this call."""
         fs = self.sets[si]
         b = fs.buckets[bi]
         if not to_wire and fs.acc is None:
@@ -482,8 +525,9 @@ class GradSyncEngine:
         if len(grads) == len(b.tensors) and all(in_window[ti] == first_state for ti in b.tensors):
             # the usual case: the whole bucket, all tensors in the same accumulation state -> prebuilt table
             segs = b.segs
-            for k, ti in enumerate(b.tensors):
-                segs[k].src = grads[ti].data_ptr()
+            if not table_filled:
+                for k, ti in enumerate(b.tensors):
+                    segs[k].src = grads[ti].data_ptr()
             mode = (_lib.READ_ACC if first_state else 0) | (_lib.WRITE_WIRE if to_wire else 0)
             _lib.calls.dgs_flatten_accumulate(
                 segs, len(b.tensors), fs.dtype_code, fs.acc_ptr, fs.wire_ptr, fs.wire_code, mode, self.scale * self.unscale, stream,

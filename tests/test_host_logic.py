@@ -1233,3 +1233,98 @@ def test_lr_scheduler_coupling_matches_rates_recorded_from_the_reference():
             ctl._auto_step_lr_scheduler_per_batch(b, sched)
         got.append(opt.param_groups[0]["lr"])
         assert got == case["lr"], (case["mode"], agg, freq)
+
+
+def test_native_host_loop_equals_the_python_loop(monkeypatch):
+    """csrc/dgs_host.cpp (opt-in with DGS_HOST_EXT=1) against the Python loops it replaces, on CPU tensors: the same
+    dgs_seg tables reach dgs_flatten_accumulate, p.grad ends up None, and cases the fast path does not cover (a
+    missing gradient, a dtype or layout the kernel cannot read directly) leave everything untouched."""
+    import importlib.util
+
+    from determined_clone_b200 import _build
+    from determined_clone_b200.pytorch import _gradsync as G
+
+    path = _build.build_host()
+    spec = importlib.util.spec_from_file_location("_dgs_host", str(path))
+    host = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(host)
+
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Conv2d(3, 4, 3), torch.nn.BatchNorm2d(4), torch.nn.Flatten(), torch.nn.Linear(4 * 36, 7))
+    params = list(model.parameters())
+    launches = []
+
+    def fake_flatten(segs, n, gdt, acc, wire, wdt, mode, scale, stream):
+        launches.append(([(segs[k].src, segs[k].dst_off, segs[k].numel) for k in range(n)], n, gdt, mode, scale))
+        return 0
+
+    monkeypatch.setattr(G, "_stream", lambda: None)
+    monkeypatch.setattr(G._lib.calls, "dgs_flatten_accumulate", fake_flatten, raising=False)
+
+    def engine():
+        eng = G.GradSyncEngine.__new__(G.GradSyncEngine)
+        eng.comm, eng.device, eng.scale, eng.unscale = None, torch.device("cpu"), 0.5, 1.0
+        eng.bucket_bytes, eng.first_bucket_bytes = 0, 64
+        eng._final_pass, eng._next_launch, eng._launch_order, eng._eager_norm = True, 0, [], False
+        fs = G._FlatSet(torch.float32, torch.device("cpu"))
+        offs, fs.total = G.plan_layout([p.numel() for p in params])
+        fs.tensors = [G._Tensor(p, 0, off, i) for i, (p, off) in enumerate(zip(params, offs))]
+        fs.in_window, fs.in_wire = [False] * len(params), [False] * len(params)
+        eng._cut_buckets(fs)
+        assert len(fs.buckets) > 1 and [p for b in fs.buckets for p in b.params] == [fs.tensors[ti].param for b in fs.buckets for ti in b.tensors]
+        fs.dtype_code, fs.wire_code, fs.acc_ptr, fs.wire_ptr = 0, 0, None, None
+        fs.segs_all = (G._lib.Seg * len(params))()
+        fs.params = list(params)
+        for k, t in enumerate(fs.tensors):
+            fs.segs_all[k].dst_off, fs.segs_all[k].numel = t.off, t.numel
+        eng.sets = [fs]
+        return eng, fs
+
+    def run(native, spoil=None):
+        launches.clear()
+        monkeypatch.setattr(G, "_host", host if native else None)
+        grads = [torch.randn_like(p) for p in params]
+        for p, g in zip(params, grads):
+            p.grad = g
+        if spoil == "missing":
+            params[2].grad = None
+        elif spoil == "dtype":
+            params[2].grad = None
+            params[2].data = params[2].data.double()
+            params[2].grad = grads[2].double()
+        elif spoil == "strided":
+            params[0].grad = grads[0].permute(0, 1, 3, 2).contiguous().permute(0, 1, 3, 2)
+        eng, fs = engine()
+        done = eng._flush_whole_set(fs)
+        state = [p.grad is None for p in params]
+        if spoil == "dtype":
+            params[2].grad = None
+            params[2].data = params[2].data.float()
+        return done, state, [(l[0], l[1:]) for l in launches], [g.data_ptr() for g in grads]
+
+    for native in (False, True):
+        done, cleared, calls, ptrs = run(native)
+        assert done and all(cleared) and len(calls) == 1
+        table, rest = calls[0]
+        assert [t[0] for t in table] == ptrs and rest == (len(params), 0, G._lib.WRITE_WIRE, 0.5)
+        for spoil in ("missing", "dtype", "strided"):
+            done, cleared, calls, _ = run(native, spoil)
+            assert not done and not calls and cleared == [spoil == "missing" and i == 2 for i in range(len(params))], (native, spoil)
+
+    # the per-bucket entry used by the sentinel hooks
+    for native in (False, True):
+        monkeypatch.setattr(G, "_host", host if native else None)
+        launches.clear()
+        grads = [torch.randn_like(p) for p in params]
+        for p, g in zip(params, grads):
+            p.grad = g
+        eng, fs = engine()
+        eng._reduce_ready = lambda fs=None: None
+        eng._sentinels = {id(fs.tensors[b.tensors[-1]].param): (0, bi) for bi, b in enumerate(fs.buckets)}
+        for bi, b in enumerate(fs.buckets):
+            eng._on_sentinel(fs.tensors[b.tensors[-1]].param)
+            assert b.flushed and all(fs.in_wire[ti] for ti in b.tensors)
+        assert all(p.grad is None for p in params) and len(launches) == len(fs.buckets)
+        got = {src for table, *_ in launches for src, _, _ in table}
+        assert got == {g.data_ptr() for g in grads}
+    assert host.all_have_grads(params) is False
