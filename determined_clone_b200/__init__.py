@@ -14,6 +14,14 @@ from determined_clone_b200._trial_controller import _DistributedBackend  # noqa:
 
 __version__ = "0.1.0"
 
+# what train.py scripts pass to logging.basicConfig(format=...) (reference determined/__init__.py:26-30)
+LOG_FORMAT = "%(levelname)s: [%(process)s] %(name)s: %(message)s"
+
+
+class InvalidHP(Exception):
+    """Raised by trial code to say that this hyper-parameter combination cannot train (reference
+    determined/_execution.py).  Without a searcher to report to, it simply ends the run."""
+
 
 def __getattr__(name: str):  # lazy: importing the package must not import torch
     if name in ("pytorch", "core"):

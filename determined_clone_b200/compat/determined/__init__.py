@@ -10,6 +10,7 @@ from determined_clone_b200._info import ClusterInfo, get_cluster_info  # noqa: F
 from determined_clone_b200._trial_controller import _DistributedBackend  # noqa: F401
 
 __version__ = _impl.__version__
+LOG_FORMAT, InvalidHP = _impl.LOG_FORMAT, _impl.InvalidHP
 InvalidExperimentException = errors.InvalidExperimentException
 for _name in ("core", "errors", "pytorch", "util"):
     sys.modules[f"determined.{_name}"] = getattr(_impl, _name) if _name in ("core", "pytorch") else globals()[_name]
