@@ -8,6 +8,7 @@ on this path (PyTorchTrial, PyTorchTrialContext, MetricReducer, DistributedConte
 lives in csrc/libdgs.so (hand-written sm_100a kernels + NCCL); see include/dgs.h and DESIGN.md.
 """
 from determined_clone_b200 import errors, util  # noqa: F401
+from determined_clone_b200._execution import _make_local_execution_env  # noqa: F401
 from determined_clone_b200._import import import_from_path  # noqa: F401
 from determined_clone_b200._info import ClusterInfo, get_cluster_info  # noqa: F401
 from determined_clone_b200._trial_controller import _DistributedBackend  # noqa: F401

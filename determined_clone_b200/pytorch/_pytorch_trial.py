@@ -37,6 +37,7 @@ from determined_clone_b200.pytorch._data import DataLoader, data_length
 from determined_clone_b200.pytorch._lr_scheduler import LRScheduler
 from determined_clone_b200.pytorch._pytorch_context import PyTorchTrialContext
 from determined_clone_b200.pytorch._reducer import Reducer
+from determined_clone_b200.pytorch._trainer_utils import to_batches
 
 logger = logging.getLogger("determined.pytorch")
 
@@ -128,11 +129,17 @@ class _PyTorchTrialController:
         final_validation: bool = False,
         final_checkpoint: bool = False,
         on_validation: Optional[Callable[[int, Dict[str, Any]], None]] = None,
+        local_training: bool = True,
+        det_profiler: Any = None,
+        global_batch_size: Optional[int] = None,
     ) -> None:
-        """max_length / reporting_period / validation_period / checkpoint_period are in batches (Trainer.fit converts
-        epochs and records).  The loop of the reference (_pytorch_trial.py:626-820) without a master: checkpoints go
-        to directories named by a fresh uuid under `checkpoint_dir`, reports go to on_report / on_validation and are
-        kept in .reports / .validation_reports.  With the defaults nothing but training and reporting happens."""
+        """max_length / reporting_period / validation_period / checkpoint_period: a number of batches, or the
+        reference's Batch / Epoch / Record units (resolved once the training loader's length is known).  The loop of
+        the reference (_pytorch_trial.py:626-820) without a master: checkpoints go to directories named by a fresh
+        uuid (under `checkpoint_dir`, or wherever the core context's checkpoint storage puts them), reports go to
+        on_report / on_validation and the core context's train reporter, and are kept in .reports /
+        .validation_reports.  With the defaults nothing but training and reporting happens.  local_training and
+        det_profiler are accepted for signature compatibility: there is no other mode and no system profiler here."""
         self.trial = trial_inst
         self.context = context
         # test_mode trains exactly one batch (reference _pytorch_trial.py:742-743,755-756)
@@ -143,7 +150,9 @@ class _PyTorchTrialController:
         self.is_chief = context.distributed.rank == 0
         self.reports: List[Dict[str, Any]] = []
         self._device_metrics = device_metrics and context.device.type == "cuda"
-        self._metric_buffer = _metric_utils.DeviceMetricBuffer(context.device, capacity=max(reporting_period, 1))
+        self._metric_buffer = _metric_utils.DeviceMetricBuffer(
+            context.device, capacity=max(reporting_period, 1) if isinstance(reporting_period, int) else 128)
+        self._global_batch_size = global_batch_size or context._global_batch_size
         self.training_loader: Any = None
         self.validation_loader: Any = None
         self.trial_id = trial_id
@@ -217,6 +226,7 @@ class _PyTorchTrialController:
                 stack.callback(cb.on_trial_shutdown)  # also on an exception or a stop request
             if self.training_loader is None:
                 self._set_data_loaders()
+            self._resolve_units()
             it = iter(self.training_loader)
             if restore is not None:
                 # after the training iterator exists, as in the reference (:583-612): creating it draws from torch's
@@ -235,6 +245,16 @@ class _PyTorchTrialController:
                 self._validation_step()
             if self.final_checkpoint and self.state.last_ckpt != self.batches_trained:
                 self._checkpoint()
+
+    def _resolve_units(self) -> None:
+        """Batch / Epoch / Record lengths -> batches, now that the epoch length is known."""
+        epoch_len, gbs = self.context._epoch_len, self._global_batch_size
+        self.max_length = to_batches(self.max_length, epoch_len, gbs)
+        self.reporting_period = max(to_batches(self.reporting_period, epoch_len, gbs), 1)
+        if self.validation_period is not None:
+            self.validation_period = to_batches(self.validation_period, epoch_len, gbs)
+        if self.checkpoint_period is not None:
+            self.checkpoint_period = to_batches(self.checkpoint_period, epoch_len, gbs)
 
     def _train_loop(self, it: Any, pending: List[Dict[str, Any]], previous: Any, samples: int, t0: float) -> None:
         epoch_len = self.context._epoch_len
@@ -298,6 +318,9 @@ class _PyTorchTrialController:
     def _stop_requested(self) -> bool:
         """As in the reference, the flag is per rank: user code must make the same request on every rank (the next
         batch starts with collectives)."""
+        preempt = getattr(self.context._core, "preempt", None)
+        if preempt is not None and preempt.should_preempt():
+            return True
         return bool(self.context.get_stop_requested())
 
     def _begin_report(self, training_metrics: List[Dict]) -> Callable[[], Dict]:
@@ -328,6 +351,9 @@ class _PyTorchTrialController:
             report["samples_per_second"] = samples / dur * self.context.distributed.size if dur > 0 else 0.0
             report["steps_completed"] = steps
             self.reports.append(report)
+            train = getattr(self.context._core, "train", None)
+            if train is not None:  # a core.Context was given: report where the reference reports (:358-365)
+                train.report_training_metrics(steps_completed=steps, metrics=report["avg_metrics"], batch_metrics=report["batch_metrics"])
             if self.context.get_enable_tensorboard_logging():
                 _metric_utils._log_tb_metrics(self.context.get_tensorboard_writer(), "train", steps, report["avg_metrics"], report["batch_metrics"])
             if self.on_report:
@@ -417,7 +443,13 @@ class _PyTorchTrialController:
 
     def _checkpoint_path(self, uuid_or_path: str) -> pathlib.Path:
         direct = pathlib.Path(uuid_or_path)
-        return direct if direct.is_dir() else self._storage_dir() / uuid_or_path
+        if direct.is_dir():
+            return direct
+        storage = getattr(self.context._core, "checkpoint", None) if self.checkpoint_dir is None else None
+        if storage is not None:
+            with storage.restore_path(uuid_or_path) as path:  # local storage: the path stays valid after the block
+                return pathlib.Path(path)
+        return self._storage_dir() / uuid_or_path
 
     def _checkpoint(self) -> str:
         """Write a checkpoint now (reference :395-423): the chief saves into <storage>/<uuid>/, every rank learns
@@ -427,11 +459,17 @@ class _PyTorchTrialController:
         name = ""
         collective_state = any(eng.sharded for eng in self.context._engines.values())
         if self.is_chief:
-            name = str(uuid.uuid4())
-            path = self._storage_dir() / name
-            self._save(path)
-            with (path / "metadata.json").open("w") as f:
-                json.dump({"steps_completed": self.batches_trained, "framework": f"torch-{torch.__version__}", "format": "pickle"}, f)
+            metadata = {"steps_completed": self.batches_trained, "framework": f"torch-{torch.__version__}", "format": "pickle"}
+            storage = getattr(self.context._core, "checkpoint", None) if self.checkpoint_dir is None else None
+            if storage is not None:  # a core.Context was given: its checkpoint storage decides where (:410-415)
+                with storage.store_path(metadata) as (path, name):
+                    self._save(path)
+            else:
+                name = str(uuid.uuid4())
+                path = self._storage_dir() / name
+                self._save(path)
+                with (path / "metadata.json").open("w") as f:
+                    json.dump(metadata, f)
         elif collective_state:
             # sharded step: optimizer.state_dict() gathers the other ranks' slices, so every rank has to ask for it
             for opt in self.context.optimizers:
@@ -631,6 +669,9 @@ class _PyTorchTrialController:
         should_checkpoint = False
         if self.is_chief:
             self.validation_reports.append({"steps_completed": n, "validation_metrics": metrics})
+            train = getattr(self.context._core, "train", None)
+            if train is not None:
+                train.report_validation_metrics(n, metrics)  # (:1075)
             if self.context.get_enable_tensorboard_logging():
                 _metric_utils._log_tb_metrics(self.context.get_tensorboard_writer(), "val", n, metrics)
             if self.on_validation:

@@ -12,47 +12,9 @@ from determined_clone_b200 import _info, core
 from determined_clone_b200._trial_controller import _DistributedBackend
 from determined_clone_b200.pytorch._pytorch_context import PyTorchTrialContext
 from determined_clone_b200.pytorch._pytorch_trial import PyTorchTrial, _PyTorchTrialController
+from determined_clone_b200.pytorch._trainer_utils import Batch, Epoch, Record, TrainUnit, to_batches  # noqa: F401
 
 logger = logging.getLogger("determined.pytorch")
-
-
-class TrainUnit:
-    def __init__(self, value: int) -> None:
-        self.value = int(value)
-
-    def __repr__(self) -> str:
-        return f"{type(self).__name__}({self.value})"
-
-    @staticmethod
-    def _from_searcher_unit(length: int, unit: str, global_batch_size: Optional[int] = None) -> "TrainUnit":
-        if unit == "records":
-            return Record(length, global_batch_size)
-        return {"batches": Batch, "epochs": Epoch}[unit](length)
-
-    @staticmethod
-    def _from_values(batches: Optional[int] = None, records: Optional[int] = None, epochs: Optional[int] = None,
-                     global_batch_size: Optional[int] = None) -> "TrainUnit":
-        if sum(v is not None for v in (batches, records, epochs)) != 1:
-            raise ValueError(f"invalid config: batches={batches} records={records} epochs={epochs}")
-        if batches is not None:
-            return Batch(batches)
-        if records is not None:
-            return Record(records, global_batch_size)
-        return Epoch(epochs)  # type: ignore
-
-
-class Batch(TrainUnit):
-    pass
-
-
-class Epoch(TrainUnit):
-    pass
-
-
-class Record(TrainUnit):
-    def __init__(self, value: int, global_batch_size: Optional[int] = None) -> None:
-        super().__init__(value)
-        self.global_batch_size = global_batch_size
 
 
 def _initialize_distributed_backend() -> Optional[core.DistributedContext]:
@@ -115,14 +77,7 @@ class Trainer:
         self.checkpoints: List[str] = []
 
     def _to_batches(self, unit: TrainUnit, loader_len: Optional[int]) -> int:
-        if isinstance(unit, Batch):
-            return unit.value
-        if isinstance(unit, Record):
-            gbs = unit.global_batch_size or self._context.get_global_batch_size()
-            return max(unit.value // gbs, 1)
-        if loader_len is None:
-            raise ValueError("max_length in epochs needs a training data loader with a length")
-        return unit.value * loader_len
+        return to_batches(unit, loader_len, self._context._global_batch_size)
 
     def fit(
         self,

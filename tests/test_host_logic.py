@@ -1328,3 +1328,48 @@ def test_native_host_loop_equals_the_python_loop(monkeypatch):
         got = {src for table, *_ in launches for src, _, _ in table}
         assert got == {g.data_ptr() for g in grads}
     assert host.all_have_grads(params) is False
+
+
+def test_controller_with_a_core_context_and_train_units(tmp_path):
+    """The way the reference's own test scaffolding builds a run (harness/tests/experiment/pytorch_utils.py:16-120):
+    core._dummy_init() -> PyTorchTrialContext(core_context=...) -> _PyTorchTrialController with Batch / Epoch units.
+    Reports go through core.train, checkpoints through core.checkpoint (a uuid directory with metadata.json), and a
+    second run continues from that uuid."""
+    from determined_clone_b200 import core as dcore
+
+    cc = dcore._dummy_init(checkpoint_storage=str(tmp_path / "store"), tensorboard_path=tmp_path / "tb")
+    ctx = pytorch.PyTorchTrialContext(core_context=cc, trial_seed=3, hparams={"global_batch_size": 2}, slots_per_trial=1, num_gpus=0,
+                                      exp_conf={"hyperparameters": {"global_batch_size": 2}}, aggregation_frequency=1,
+                                      steps_completed=0, managed_training=True, debug_enabled=False)
+    assert ctx.get_trial_id() == 0 and ctx.get_tensorboard_path() == tmp_path / "tb"
+    trial = _HostTrial(ctx)
+    ctl = pytorch._PyTorchTrialController(
+        trial_inst=trial, context=ctx, max_length=pytorch.Epoch(1), checkpoint_period=pytorch.Batch(sys.maxsize),
+        validation_period=pytorch.Batch(4), reporting_period=pytorch.Batch(3), searcher_metric_name="val_loss",
+        smaller_is_better=True, steps_completed=0, latest_checkpoint=None, local_training=True, test_mode=False,
+        checkpoint_policy="best", step_zero_validation=False, det_profiler=None, global_batch_size=None,
+        final_validation=True, final_checkpoint=True, trial_id=0,
+    )
+    ctl.run()
+    assert (ctl.max_length, ctl.reporting_period, ctl.validation_period) == (8, 3, 4)
+    assert [n for n, _, _ in cc.train.training_reports] == [3, 4, 6, 8] and cc.train.training_reports[0][1]["loss"] == 1.0
+    assert len(cc.train.training_reports[1][2]) == 1  # batch 3 alone: the validation at 4 closed the period early
+    assert [n for n, _ in cc.train.validation_reports] == [4, 8]
+    # val_loss grows with the weight, so only the first validation is "best"; the end of training adds one checkpoint
+    assert len(ctl.checkpoints) == 2
+    first, last = (tmp_path / "store" / u for u in ctl.checkpoints)
+    assert cc.checkpoint.get_metadata(ctl.checkpoints[0])["steps_completed"] == 4 and (first / "state_dict.pth").exists()
+    assert cc.checkpoint.get_metadata(ctl.checkpoints[1])["steps_completed"] == 8 and (last / "trial_state.pkl").exists()
+
+    cc2 = dcore._dummy_init(checkpoint_storage=str(tmp_path / "store"))
+    ctx2 = pytorch.PyTorchTrialContext(core_context=cc2, hparams={"global_batch_size": 2})
+    trial2 = _HostTrial(ctx2)
+    ctl2 = pytorch._PyTorchTrialController(trial_inst=trial2, context=ctx2, max_length=pytorch.Batch(6), reporting_period=pytorch.Batch(100),
+                                           latest_checkpoint=ctl.checkpoints[0], trial_id=0)
+    ctl2.run()
+    assert [s[1] for s in trial2.seen] == [4, 5] and float(trial2.model.weight.detach()) == 6.0
+    assert [n for n, _, _ in cc2.train.training_reports] == [6]
+    with pytest.raises(FileNotFoundError):
+        pytorch._PyTorchTrialController(trial_inst=trial2, context=ctx2, max_length=1, latest_checkpoint="no-such-uuid").run()
+    with cc2 as entered:
+        assert entered is cc2 and cc2.preempt.should_preempt() is False
