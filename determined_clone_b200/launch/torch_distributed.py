@@ -31,11 +31,33 @@ def create_launch_cmd(num_nodes: int, proc_per_node: int, node_rank: int, master
 
 
 def parse_args(args: List[str]) -> Tuple[List[str], List[str]]:
-    """[torchrun overrides ... --] script ..."""
+    """[TORCH_OVERRIDES... --] (--trial module:TrialClass | SCRIPT...)  ->  (overrides, script), with the cases of
+    the reference (launch/torch_distributed.py:108-160, its test_parse_args): `--trial X` stands for the legacy
+    harness entrypoint and takes no further arguments; an empty script and unknown options are usage errors
+    (exit status 1 / 2)."""
+    overrides: List[str] = []
     if "--" in args:
-        split = args.index("--")
-        return args[:split], args[split + 1:]
-    return [], args
+        cut = args.index("--")
+        overrides, args = args[:cut], args[cut + 1:]
+    parser = argparse.ArgumentParser(
+        usage="%(prog)s [[TORCH_OVERRIDES...] --] (--trial TRIAL)|(SCRIPT...)",
+        description="Launch a script under pytorch distributed, one worker per slot of this box",
+    )
+    parser.add_argument("--trial", help="a Trial class (module:Class) to train through the legacy harness entrypoint; excludes SCRIPT")
+    parser.add_argument("script", metavar="SCRIPT...", nargs=argparse.REMAINDER, help="script to launch for training")
+    parsed = parser.parse_args(args)
+    script = list(parsed.script or [])
+    if parsed.trial is not None:
+        if script:
+            parser.print_usage()
+            print("error: extra arguments to --trial:", script, file=sys.stderr)
+            sys.exit(1)
+        script = ["python3", "-m", "determined.exec.harness", parsed.trial]
+    elif not script:
+        parser.print_usage()
+        print("error: empty script is not allowed", file=sys.stderr)
+        sys.exit(1)
+    return overrides, script
 
 
 def main(override_args: List[str], script: List[str]) -> int:
@@ -53,7 +75,4 @@ def main(override_args: List[str], script: List[str]) -> int:
 
 if __name__ == "__main__":
     ov, sc = parse_args(sys.argv[1:])
-    if not sc:
-        print("usage: python -m determined_clone_b200.launch.torch_distributed [torchrun args --] script ...", file=sys.stderr)
-        sys.exit(2)
     sys.exit(main(ov, sc))

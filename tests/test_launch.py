@@ -27,6 +27,20 @@ def test_launch_command_line():
     assert cmd[cmd.index("--master_addr") + 1] == "127.0.0.1" and cmd[-2:] == ["--rdzv_conf", "x=1"]
     assert launch.parse_args(["--a", "1", "--", "python3", "train.py"]) == (["--a", "1"], ["python3", "train.py"])
     assert launch.parse_args(["python3", "train.py"]) == ([], ["python3", "train.py"])
+    # the cases of the reference's test_parse_args (harness/tests/launch/test_torch_distributed.py:9-29)
+    harness = ["python3", "-m", "determined.exec.harness", "my_module:MyTrial"]
+    assert launch.parse_args("--trial my_module:MyTrial".split()) == ([], harness)
+    assert launch.parse_args("script arg".split()) == ([], ["script", "arg"])
+    assert launch.parse_args("-- script -- arg".split()) == ([], ["script", "--", "arg"])
+    assert launch.parse_args("override1 override2 -- script arg".split()) == (["override1", "override2"], ["script", "arg"])
+
+
+@pytest.mark.parametrize("line,complaint", [("--trial my_module:MyTrial script", "extra arguments"), ("", "empty script"),
+                                            ("--asdf 1 script", "unrecognized arguments")])
+def test_launch_command_line_errors(capsys, line, complaint):
+    with pytest.raises(SystemExit) as exit_info:
+        launch.parse_args(line.split())
+    assert exit_info.value.code != 0 and complaint in capsys.readouterr().err
 
 
 def test_cluster_info_from_experiment_yaml(monkeypatch):
