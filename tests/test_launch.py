@@ -127,3 +127,25 @@ def test_legacy_entrypoint_drives_validation_and_checkpoint_policy_from_the_conf
     load_data = json.loads((saved[-1] / "load_data.json").read_text())
     assert load_data["trial_cls_spec"] == "model_def:HostOnlyTrial" and load_data["hparams"]["start"] == 2.0
     assert load_data["experiment_config"]["searcher"]["metric"] == "distance"
+
+
+def test_entrypoint_dispatch_and_launch(tmp_path):
+    """exec/launch.py: a legacy `module:Class` entrypoint becomes the harness (1 slot) or the torch.distributed
+    launcher (several); strings are shell command lines, lists are argvs (reference exec/launch.py:29-46).  Then the
+    host-only experiment runs end to end through `python -m determined.exec.launch`."""
+    from determined_clone_b200.exec import launch as exec_launch
+
+    assert exec_launch.entrypoint_argv("model_def:MyTrial", 1) == ["python3", "-m", "determined.exec.harness", "model_def:MyTrial"]
+    assert exec_launch.entrypoint_argv("pkg.model_def:MyTrial", 8) == ["python3", "-m", "determined.launch.torch_distributed", "--trial", "pkg.model_def:MyTrial"]
+    assert exec_launch.entrypoint_argv("python3 train.py --lr 0.1", 8) == ["sh", "-c", "python3 train.py --lr 0.1"]
+    assert exec_launch.entrypoint_argv(["python3", "train.py"], 2) == ["python3", "train.py"]
+
+    host = FIX.parent / "host_only"
+    report = tmp_path / "reports.json"
+    env = dict(os.environ, DET_EXPERIMENT_CONFIG=str(host / "const.yaml"), DET_REPORT_FILE=str(report), DET_CHECKPOINT_DIR=str(tmp_path / "ckpts"),
+               PYTHONPATH=os.pathsep.join([str(ROOT / "determined_clone_b200" / "compat"), str(ROOT), os.environ.get("PYTHONPATH", "")]))
+    subprocess.run([sys.executable, "-m", "determined.exec.launch"], cwd=host, env=env, check=True, timeout=600)
+    assert [r["steps_completed"] for r in json.loads(report.read_text())] == [2, 3, 4, 6]
+    missing = subprocess.run([sys.executable, "-m", "determined.exec.launch"], cwd=host, capture_output=True, text=True,
+                             env={k: v for k, v in env.items() if k != "DET_EXPERIMENT_CONFIG"})
+    assert missing.returncode == 2 and "DET_EXPERIMENT_CONFIG" in missing.stderr
