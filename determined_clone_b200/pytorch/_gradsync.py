@@ -52,6 +52,11 @@ MIN_BUCKET_BYTES, MAX_BUCKET_BYTES = 25 << 20, 128 << 20
 ONE_BUCKET_BELOW_BYTES = int(__import__("os").environ.get("DGS_ONE_BUCKET_BELOW_MB", "0")) << 20
 
 
+def _check_device(device: torch.device) -> None:
+    if device.type != "cuda":
+        raise _lib.DgsError("GradSyncEngine needs a CUDA device: the grad-sync path has no CPU implementation")
+
+
 def _load_host_ext() -> Any:
     """The native host loop (csrc/dgs_host.cpp), only when asked for with DGS_HOST_EXT=1: it has been checked on
     CPU tensors (tests/test_host_logic.py) but not yet measured on a GPU box, so the Python loops stay the default."""
@@ -196,8 +201,7 @@ class GradSyncEngine:
         sharded_step: Optional[bool] = None,
     ) -> None:
         _lib.load()  # fail now, loudly, if libdgs.so is missing
-        if device.type != "cuda":
-            raise _lib.DgsError("GradSyncEngine needs a CUDA device: the grad-sync path has no CPU implementation")
+        _check_device(device)
         self.optimizer = optimizer
         self.device = device
         self.comm = comm
