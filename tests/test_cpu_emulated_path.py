@@ -187,3 +187,202 @@ def test_resume_from_the_reference_checkpoint_through_trainer_fit(monkeypatch, t
         np.testing.assert_array_equal(_np(p), rec["params"][-1][i])
         assert float(plain_opt.state[p]["step"]) == CK_SAVE_AT + CK_RESUME
     ctx.close()
+
+
+# ---- AMP protocol (tests/test_gpu_amp.py on the CPU: torch.amp.GradScaler("cpu"), fp32 forward) --------------------
+class Net(torch.nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.a = torch.nn.Linear(12, 32)
+        self.norm = torch.nn.LayerNorm(32)
+        self.b = torch.nn.Linear(32, 5)
+
+    def forward(self, x):
+        return self.b(torch.tanh(self.norm(self.a(x))))
+
+
+def _amp_opt(kind, model):
+    decay = [p for p in model.parameters() if p.ndim >= 2]
+    rest = [p for p in model.parameters() if p.ndim < 2]
+    groups = [{"params": decay, "weight_decay": 0.05}, {"params": rest, "weight_decay": 0.0}]
+    if kind == "adamw":
+        return torch.optim.AdamW(groups, lr=1e-2, betas=(0.9, 0.95))
+    return torch.optim.SGD(groups, lr=0.05, momentum=0.9, nesterov=True)
+
+
+def _amp_data(n, poison):
+    g = torch.Generator().manual_seed(77)
+    data = [(torch.randn(8, 12, generator=g), torch.randn(8, 5, generator=g)) for _ in range(n)]
+    for i in poison:
+        data[i][0][0, 0] = float("inf")
+    return data
+
+
+def _scaler():
+    return torch.amp.GradScaler("cpu", init_scale=1024.0, growth_interval=2)
+
+
+def _snap(model, opt, scaler, out):
+    out["params"].append([_np(p) for p in model.parameters()])
+    out["scale"].append(scaler.get_scale())
+    out["adam_steps"].append([float(opt.state[p]["step"]) for p in model.parameters() if "step" in opt.state.get(p, {})])
+
+
+def _same_run(ours, ref):
+    assert ours["scale"] == ref["scale"] and ours["adam_steps"] == ref["adam_steps"] and len(ours["norms"]) == len(ref["norms"])
+    for a, b in zip(ours["norms"], ref["norms"]):
+        assert math.isfinite(a) == math.isfinite(b)
+        if math.isfinite(b):
+            np.testing.assert_allclose(a, b, rtol=1e-5)
+    for s, (pa, pb) in enumerate(zip(ours["params"], ref["params"])):
+        for a, b in zip(pa, pb):
+            np.testing.assert_allclose(a, b, rtol=1e-5, atol=1e-7, err_msg=f"after optimizer step {s}")
+
+
+@pytest.mark.parametrize("kind,agg,clip,poison", [
+    ("adamw", 1, 0.5, (2,)), ("adamw", 2, 0.5, (5,)), ("adamw", 2, None, (2,)), ("sgd", 1, None, (0,)), ("sgd", 1, 0.5, ()),
+])
+def test_auto_amp_protocol(monkeypatch, kind, agg, clip, poison):
+    fake = fake_dgs.install(monkeypatch)
+    torch.manual_seed(5)
+    base = Net()
+    data = _amp_data(8 * agg, poison)
+
+    model = copy.deepcopy(base)
+    opt, scaler = _amp_opt(kind, model), _scaler()
+    ref = {"params": [], "scale": [], "adam_steps": [], "norms": []}
+    params = [p for grp in opt.param_groups for p in grp["params"]]
+    for i, (x, y) in enumerate(data):
+        scaler.scale(torch.nn.functional.mse_loss(model(x), y)).backward()
+        if (i + 1) % agg:
+            continue
+        for p in params:
+            p.grad.div_(float(agg))
+        if clip is not None:
+            scaler.unscale_(opt)
+            ref["norms"].append(float(torch.nn.utils.clip_grad_norm_(params, clip)))
+        scaler.step(opt)
+        opt.zero_grad()
+        scaler.update()
+        _snap(model, opt, scaler, ref)
+
+    out = {"params": [], "scale": [], "adam_steps": [], "norms": []}
+
+    class AmpTrial(pytorch.PyTorchTrial):
+        def __init__(self, context):
+            self.context = context
+            self.model = context.wrap_model(copy.deepcopy(base))
+            context.experimental.use_amp()  # after wrap_model: loss scaling without the autocast wrapper
+            context.wrap_scaler(_scaler())
+            self.opt = context.wrap_optimizer(_amp_opt(kind, self.model))
+
+        def build_training_data_loader(self):
+            raise AssertionError("batches are fed by the test")
+
+        def train_batch(self, batch, epoch_idx, batch_idx):
+            loss = torch.nn.functional.mse_loss(self.model(batch[0]), batch[1])
+            self.context.backward(loss)
+            fn = (lambda ps: out["norms"].append(float(torch.nn.utils.clip_grad_norm_(list(ps), clip)))) if clip is not None else None
+            self.context.step_optimizer(self.opt, clip_grads=fn)
+            return {"loss": loss}
+
+    ctx = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 8}, aggregation_frequency=agg)
+    trial = AmpTrial(ctx)
+    assert ctx._prefolds(ctx._engines[trial.opt])
+    ctl = pytorch._PyTorchTrialController(trial, ctx, max_length=len(data), reporting_period=len(data))
+    for i, batch in enumerate(data):
+        ctx._current_batch_idx = i
+        ctl._train_batch(batch, 0, i)
+        if (i + 1) % agg == 0:
+            _snap(trial.model, trial.opt, ctx._scaler, out)
+    assert len(set(ref["scale"])) > 1
+    _same_run(out, ref)
+    # the loss scale went into the flatten call's factor: 1/(A*S) with the S in force for that window
+    factors = [e[3] for e in fake.log if e[0] == "flatten" and e[2] & det._lib.WRITE_WIRE]
+    scales_in_force = [1024.0] + ref["scale"][:-1]
+    assert factors == [1.0 / (agg * s) for s in scales_in_force]
+    ctx.close()
+
+
+@pytest.mark.parametrize("kind", ["adamw", "sgd"])
+@pytest.mark.parametrize("mode", ["no_clip", "clip_after_own_unscale", "clip_without_unscale"])
+def test_scaler_passed_to_step_optimizer(monkeypatch, kind, mode):
+    fake_dgs.install(monkeypatch)
+    torch.manual_seed(8)
+    base = Net()
+    data = _amp_data(8, (3,))
+    runs = []
+    for which in ("ours", "torch"):
+        model, scaler = copy.deepcopy(base), _scaler()
+        out = {"params": [], "scale": [], "adam_steps": [], "norms": []}
+        if which == "ours":
+            ctx = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 8})
+            model = ctx.wrap_model(model)
+            opt = ctx.wrap_optimizer(_amp_opt(kind, model))
+        else:
+            opt = _amp_opt(kind, model)
+
+        def clip_fn(params, opt=opt, scaler=scaler, out=out):
+            if mode == "clip_after_own_unscale":
+                scaler.unscale_(opt)
+            out["norms"].append(float(torch.nn.utils.clip_grad_norm_(list(params), 0.5 if mode == "clip_after_own_unscale" else 300.0)))
+
+        clip = None if mode == "no_clip" else clip_fn
+        for i, (x, y) in enumerate(data):
+            loss = torch.nn.functional.mse_loss(model(x), y)
+            if which == "ours":
+                ctx._current_batch_idx = i
+                ctx.backward(scaler.scale(loss))
+                ctx.step_optimizer(opt, clip_grads=clip, scaler=scaler)
+            else:
+                scaler.scale(loss).backward()
+                if clip is not None:
+                    clip([p for grp in opt.param_groups for p in grp["params"]])
+                scaler.step(opt)
+                opt.zero_grad()
+            scaler.update()
+            _snap(model, opt, scaler, out)
+        if which == "ours":
+            ctx.close()
+        runs.append(out)
+    _same_run(runs[0], runs[1])
+
+
+# ---- the reference's closed-form experiment through the legacy entrypoint, in this process ---------------------------
+def test_identity_experiment_from_its_yaml(monkeypatch, tmp_path):
+    """tests/fixtures/pytorch_identity/const.yaml (16 batches of y = w*x, aggregation_frequency 2, reporting after
+    every batch) run as `determined.exec.harness model_def:IdentityTrial` does it -- context from the experiment
+    config, Trainer.fit with periods and policy from the YAML, final validation and checkpoint -- and compared with
+    the reference's closed form (test_pytorch_trial.py:1604-1642).  tests/test_launch.py runs the same thing as a
+    subprocess on a GPU."""
+    import json
+
+    from oracle import gradsync_oracle as O
+
+    from determined_clone_b200.exec import harness
+
+    fake_dgs.install(monkeypatch)
+    fix = HERE / "fixtures" / "pytorch_identity"
+    report = tmp_path / "reports.json"
+    monkeypatch.setenv("DET_EXPERIMENT_CONFIG", str(fix / "const.yaml"))
+    monkeypatch.setenv("DET_REPORT_FILE", str(report))
+    monkeypatch.setenv("DET_CHECKPOINT_DIR", str(tmp_path / "ckpts"))
+    monkeypatch.chdir(fix)
+    monkeypatch.syspath_prepend(str(pathlib.Path(det.__file__).parent / "compat"))
+    for name in [n for n in sys.modules if n == "determined" or n.startswith("determined.") or n == "model_def"]:
+        monkeypatch.delitem(sys.modules, name)
+    assert harness.main(["model_def:IdentityTrial"]) == 0
+    reports = json.loads(report.read_text())
+    assert [r["steps_completed"] for r in reports] == list(range(1, 17))
+    # avg_metrics, computed when each report was made (one batch per report): on the CPU the per-batch entries are
+    # numpy views of the live parameter, exactly as `metric.cpu().detach().numpy()` gives them in the reference
+    got = [r["avg_metrics"]["weight"] for r in reports]
+    np.testing.assert_allclose(got, O.identity_expected_weights()[:16], rtol=1e-5, atol=1e-9)
+    assert got[0] == 0.0 and got[1] == got[2] != 0.0  # no update on non-boundary batches
+    # searcher.metric validation_loss, checkpoint_policy best (the default): the end-of-training validation is the
+    # best (only) one, so exactly one checkpoint exists, taken at batch 16
+    (ckpt,) = list((tmp_path / "ckpts").iterdir())
+    assert json.loads((ckpt / "metadata.json").read_text())["steps_completed"] == 16
+    saved = torch.load(ckpt / "state_dict.pth", weights_only=False)
+    np.testing.assert_allclose(float(saved["models_state_dict"][0]["weight"]), got[-1], rtol=1e-6)
+    sys.modules.pop("model_def", None)
