@@ -70,11 +70,27 @@ class GoldenTrial(pytorch.PyTorchTrial):
 FP32_ONE_SLOT = [n for n, sc in SCENARIOS.items() if sc["slots"] == 1 and sc["dtype"] == "float32"]
 
 
-@pytest.mark.parametrize("name", FP32_ONE_SLOT)
-def test_single_slot_scenarios_through_the_whole_python_path(monkeypatch, name):
+def _native_host_loop():
+    import importlib.util
+
+    from determined_clone_b200 import _build
+
+    spec = importlib.util.spec_from_file_location("_dgs_host", str(_build.build_host()))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+@pytest.mark.parametrize("name,native", [(n, False) for n in FP32_ONE_SLOT] + [("sgd_n1_a1", True), ("adamw_n1_a4_clip", True)])
+def test_single_slot_scenarios_through_the_whole_python_path(monkeypatch, name, native):
     """The reference's recorded runs (10 optimizer steps each) reproduced by this harness with emulated kernels:
-    synchronized gradients, clip norm, parameters, optimizer state, step counters, reported metrics."""
+    synchronized gradients, clip norm, parameters, optimizer state, step counters, reported metrics.  native: with
+    the C++ host loop (csrc/dgs_host.cpp, what DGS_HOST_EXT=1 selects) taking the gradients instead of Python."""
     fake = fake_dgs.install(monkeypatch)
+    if native:
+        from determined_clone_b200.pytorch import _gradsync
+
+        monkeypatch.setattr(_gradsync, "_host", _native_host_loop())
     g = Golden(name)
     rec = {"avg": [], "norm": [], "params": [], "state": []}
     reports = []
