@@ -1,5 +1,5 @@
-"""TEST INFRASTRUCTURE ONLY: a host-memory stand-in for the part of libdgs.so's C ABI that the single-rank path calls,
-so that the Python side of the path -- engine bookkeeping, context, training loop, checkpoints, AMP protocol -- can
+"""TEST INFRASTRUCTURE ONLY: a host-memory stand-in for the part of libdgs.so's C ABI that the training path calls
+(the communicator entry points over torch.distributed/gloo), so that the Python side of the path -- engine bookkeeping, context, training loop, checkpoints, AMP protocol -- can
 be exercised end to end in the CPU test suite, where no kernel can run.
 
 `install(monkeypatch)` swaps `determined_clone_b200._lib.calls` for this emulator and lifts the engine's "CUDA device
@@ -16,7 +16,8 @@ import torch
 
 from determined_clone_b200 import _lib
 
-_TORCH = {_lib.F32: torch.float32, _lib.BF16: torch.bfloat16, _lib.F16: torch.float16, _lib.F64: torch.float64, _lib.I64: torch.int64}
+_U8 = -1  # raw bytes
+_TORCH = {_U8: torch.uint8, _lib.F32: torch.float32, _lib.BF16: torch.bfloat16, _lib.F16: torch.float16, _lib.F64: torch.float64, _lib.I64: torch.int64}
 
 
 def _addr(p: Any) -> int:
@@ -162,13 +163,90 @@ class FakeCalls:
         self.dgs_step_sgd(p, buf, sdt, g, gdt, n, ranges, n_ranges, total_norm, max_norm, stream, inv_scale=inv_scale)
 
 
-def install(monkeypatch: Any) -> FakeCalls:
-    """Route the engine's C-ABI calls to the emulator for the current test and let engines be built on the CPU."""
-    from determined_clone_b200.pytorch import _gradsync, _pytorch_context
+    # ---- communicator: torch.distributed (gloo) on host memory stands in for NCCL; everything completes at once ----
+    def dgs_comm_unique_id(self, out128: Any) -> None:
+        pass
+
+    def dgs_comm_init(self, ident: Any, rank: int, nranks: int, device: int, out_handle: Any) -> None:
+        import torch.distributed as dist
+
+        if not dist.is_initialized() or dist.get_world_size() != nranks or dist.get_rank() != rank:
+            raise _lib.DgsError("fake communicator: torch.distributed (gloo) must be initialised with the same rank / size")
+        out_handle._obj.value = 1
+
+    def dgs_comm_destroy(self, handle: Any) -> None:
+        pass
+
+    def dgs_comm_allreduce_async(self, handle: Any, buf: Any, count: int, dt: int, stream: Any) -> None:
+        import torch.distributed as dist
+
+        self.log.append(("allreduce", count))
+        dist.all_reduce(_view(buf, dt, count))
+
+    def dgs_comm_reduce_scatter_async(self, handle: Any, buf: Any, count_per_rank: int, dt: int, stream: Any) -> None:
+        import torch.distributed as dist
+
+        self.log.append(("reduce_scatter", count_per_rank))
+        n, r = dist.get_world_size(), dist.get_rank()
+        whole = _view(buf, dt, count_per_rank * n)
+        summed = whole.clone()
+        dist.all_reduce(summed)
+        # in place, as ncclReduceScatter with recvbuff inside sendbuff: only this rank's slice is written
+        whole[r * count_per_rank:(r + 1) * count_per_rank] = summed[r * count_per_rank:(r + 1) * count_per_rank]
+
+    def dgs_comm_broadcast_async(self, handle: Any, buf: Any, nbytes: int, root: int, stream: Any) -> None:
+        import torch.distributed as dist
+
+        self.log.append(("broadcast", nbytes))
+        dist.broadcast(_view(buf, _U8, nbytes), src=root)
+
+    def dgs_comm_allgather_async(self, handle: Any, send: Any, recv: Any, nbytes: int, stream: Any) -> None:
+        import torch.distributed as dist
+
+        self.log.append(("allgather", nbytes))
+        n = dist.get_world_size()
+        mine = _view(send, _U8, nbytes).clone()  # send may alias this rank's slice of recv (in-place all-gather)
+        parts = [torch.empty(nbytes, dtype=torch.uint8) for _ in range(n)]
+        dist.all_gather(parts, mine)
+        out = _view(recv, _U8, nbytes * n)
+        for k, part in enumerate(parts):
+            out[k * nbytes:(k + 1) * nbytes] = part
+
+    def dgs_comm_l2norm_partial_async(self, handle: Any, x: Any, dt: int, n: int, partials: Any) -> None:
+        self.dgs_l2norm_partial(x, dt, n, partials, None)
+
+    def dgs_comm_wait(self, handle: Any, stream: Any) -> None:
+        pass
+
+    def dgs_l2norm_final_sumsq(self, partials: Any, n_partials: int, out: Any, stream: Any) -> None:
+        self.launches += 1
+        _view(out, _lib.F32, 1)[0] = float(_view(partials, _lib.F32, n_partials).double().sum()) if n_partials else 0.0
+
+    def dgs_sqrt_inplace(self, x: Any, stream: Any) -> None:
+        v = _view(x, _lib.F32, 1)
+        v[0] = float(v[0]) ** 0.5 if float(v[0]) >= 0 else float("nan")
+
+
+class _NoStream:
+    cuda_stream = 0
+
+    def synchronize(self) -> None:
+        pass
+
+
+def install(monkeypatch: Any = None) -> FakeCalls:
+    """Route the engine's C-ABI calls to the emulator and let engines be built on the CPU: for the current test
+    when given pytest's monkeypatch, for the rest of the process otherwise (spawned rank processes)."""
+    from determined_clone_b200.pytorch import _comm, _gradsync, _pytorch_context
 
     fake = FakeCalls()
-    monkeypatch.setattr(_lib, "calls", fake)
-    monkeypatch.setattr(_gradsync, "_check_device", lambda device: None)
-    monkeypatch.setattr(_gradsync, "_stream", lambda: None)
-    assert _gradsync._lib is _lib and _pytorch_context._lib is _lib  # both reach `calls` through the module attribute
+    patches = [(_lib, "calls", fake), (_gradsync, "_check_device", lambda device: None), (_gradsync, "_stream", lambda: None),
+               (_comm, "_stream", lambda: None), (torch.cuda, "current_device", lambda: 0),
+               (torch.cuda, "current_stream", lambda *a, **k: _NoStream())]
+    for obj, name, value in patches:
+        if monkeypatch is not None:
+            monkeypatch.setattr(obj, name, value)
+        else:
+            setattr(obj, name, value)
+    assert _gradsync._lib is _lib and _pytorch_context._lib is _lib and _comm._lib is _lib  # all reach `calls` through the module
     return fake

@@ -1,0 +1,136 @@
+"""Two ranks, the N>1 Python logic of the engine -- one hook per bucket, buckets flushed and "all-reduced" while
+backward runs, the learned launch order, the parameter broadcast from rank 0, norm partials per bucket, the opt-in
+sharded step -- in the CPU suite: two processes, torch.distributed over gloo standing in for NCCL through the
+emulated communicator entry points of tests/fake_dgs.py (test infrastructure), the control plane being the real
+DistributedContext over ZeroMQ.  Compared with the fixtures recorded from the reference on 2-rank torch DDP."""
+import os
+import pathlib
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = pathlib.Path(__file__).resolve().parent.parent
+OPT_ORDER_TO_MODEL = [0, 4, 1, 2, 3, 5]
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _np(t):
+    return t.detach().float().cpu().numpy().copy()
+
+
+def _worker(rank: int, size: int, port: int, zmq_ports, name: str, sharded: bool, out_dir: str) -> None:
+    for p in (str(ROOT), str(ROOT / "tests"), str(ROOT / "tests" / "golden")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import torch.distributed as dist
+
+    import fake_dgs
+    from golden_io import N_PARAMS, Golden, assert_close
+    from golden_model import GoldenNet, make_data, make_optimizer
+
+    from determined_clone_b200 import core, pytorch
+
+    torch.set_num_threads(1)
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=size)
+    fake = fake_dgs.install()
+    dctx = core.DistributedContext(rank=rank, size=size, local_rank=rank, local_size=size, cross_rank=0, cross_size=1,
+                                   pub_port=zmq_ports[0], pull_port=zmq_ports[1])
+    try:
+        g = Golden(name)
+        rec = {"avg": [], "norm": [], "params": [], "state": []}
+        reports = []
+
+        class Trial(pytorch.PyTorchTrial):
+            def __init__(self, context):
+                self.context = context
+                torch.manual_seed(1000 + rank)  # different initial weights per rank: rank 0's must win
+                model = GoldenNet()
+                if rank == 0:
+                    with torch.no_grad():
+                        for p, init in zip(model.parameters(), g.init_params()):
+                            p.copy_(torch.from_numpy(init))
+                self.model = context.wrap_model(model)
+                self.plist = list(self.model.parameters())
+                self.opt = context.wrap_optimizer(make_optimizer(self.model, g.hp), average_aggregated_gradients=g.average)
+                x, y = make_data(g.steps * g.agg, g.hp["global_batch_size"])
+                self.ds = torch.utils.data.TensorDataset(x, y)
+
+            def build_training_data_loader(self):
+                return pytorch.DataLoader(self.ds, batch_size=self.context.get_per_slot_batch_size(), shuffle=False)
+
+            def _clip(self, params):
+                params = list(params)
+                if not sharded:
+                    rec["avg"].append([_np(p.grad) for p in params])
+                if g.clip is not None:
+                    rec["norm"].append(float(torch.nn.utils.clip_grad_norm_(params, g.clip[1])))
+
+            def train_batch(self, batch, epoch_idx, batch_idx):
+                x, y = batch
+                loss = torch.nn.functional.mse_loss(self.model(x), y)
+                self.context.backward(loss)
+                self.context.step_optimizer(self.opt, clip_grads=self._clip if (g.clip is not None or not sharded) else None)
+                if (batch_idx + 1) % g.agg == 0:
+                    rec["params"].append([_np(p) for p in self.plist])
+                return {"loss": loss}
+
+        pytorch._PyTorchTrialController.pre_execute_hook(17)
+        conf = {"optimizations": {"sharded_step": True}} if sharded else None
+        ctx = pytorch.PyTorchTrialContext(distributed=dctx, hparams=g.hp, slots_per_trial=size, aggregation_frequency=g.agg,
+                                          trial_seed=17, exp_conf=conf)
+        trial = Trial(ctx)
+        eng = ctx._engines[trial.opt]
+        assert eng.sharded == sharded and eng.comm is not None
+        ctl = pytorch._PyTorchTrialController(trial, ctx, max_length=g.steps * g.agg, reporting_period=g.agg,
+                                              on_report=lambda n, r: reports.append((n, r)))
+        ctl.run()
+        for s in range(g.steps):
+            if not sharded:
+                want_avg = g.per_step("avg_grads", s)
+                for j, i in enumerate(OPT_ORDER_TO_MODEL):
+                    assert_close(rec["avg"][s][j], want_avg[i], "float32", f"{name}: synced grad, step {s}, param {i}")
+            for i in range(N_PARAMS):
+                assert_close(rec["params"][s][i], g.per_step("params", s)[i], "float32", f"{name}: parameter {i} after step {s}")
+            if g.clip is not None:
+                assert_close(rec["norm"][s], g.z["total_norm"][s], "float32", f"{name}: total norm step {s}")
+        key = "momentum_buffer" if g.hp["optimizer"] == "sgd" else "exp_avg"
+        state = trial.opt.state_dict()["state"]  # sharded: gathers the other rank's slices (a collective: every rank asks)
+        for j, i in enumerate(OPT_ORDER_TO_MODEL):
+            assert_close(_np(state[j][key]), g.state(g.steps - 1, i, key), "float32", f"{name}: {key} of param {i}")
+        kinds = [e[0] for e in fake.log]
+        assert ("reduce_scatter" in kinds) == sharded
+        assert any(e[0] == "allreduce" and e[1] > 1 for e in fake.log) != sharded  # sharded: only the norm's one float is all-reduced
+        assert "broadcast" in kinds  # rank 0's parameters at wrap_optimizer; the learned bucket order
+        if rank == 0:
+            assert [n for n, _ in reports] == g.z["reported_steps"].tolist()
+            for (n, r), want in zip(reports, g.z["reported_avg_loss"]):
+                assert_close(r["avg_metrics"]["loss"], want, "float32", f"{name}: reported avg loss at {n}")
+        else:
+            assert reports == []
+        # one allreduce (or reduce-scatter) per bucket per optimizer step, issued in the same order on both ranks
+        n_buckets = sum(len(fs.buckets) for fs in eng.sets)
+        per_step = [e for e in fake.log if e[0] in ("allreduce", "reduce_scatter") and e[1] > 1]
+        assert len(per_step) == n_buckets * g.steps
+        everyone = dctx.allgather([e[1] for e in per_step])
+        assert everyone[0] == everyone[1]
+        ctx.close()
+        open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
+    finally:
+        dctx.close()
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("name,sharded", [("sgd_n2_a2", False), ("adamw_n2_a4_clip", False), ("sgd_n2_a2", True), ("adamw_n2_a4_clip", True)])
+def test_two_rank_scenarios_with_emulated_kernels_and_gloo(tmp_path, name, sharded):
+    import torch.multiprocessing as mp
+
+    mp.spawn(_worker, args=(2, _free_port(), (_free_port(), _free_port()), name, sharded, str(tmp_path)), nprocs=2, join=True)
+    assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
