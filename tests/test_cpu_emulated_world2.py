@@ -26,7 +26,7 @@ def _np(t):
     return t.detach().float().cpu().numpy().copy()
 
 
-def _worker(rank: int, size: int, port: int, zmq_ports, name: str, sharded: bool, out_dir: str) -> None:
+def _worker(rank: int, size: int, port: int, zmq_ports, name: str, sharded: bool, small_buckets: bool, out_dir: str) -> None:
     for p in (str(ROOT), str(ROOT / "tests"), str(ROOT / "tests" / "golden")):
         if p not in sys.path:
             sys.path.insert(0, p)
@@ -41,6 +41,17 @@ def _worker(rank: int, size: int, port: int, zmq_ports, name: str, sharded: bool
     torch.set_num_threads(1)
     dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=size)
     fake = fake_dgs.install()
+    if small_buckets:
+        # the fixture model has ~1500 parameters: shrink the bucket sizes so that it is cut into several buckets and
+        # the per-bucket hooks, the learned launch order and the per-bucket norm slots have something to do
+        from determined_clone_b200.pytorch import _gradsync
+
+        class SmallBuckets(_gradsync.GradSyncEngine):
+            def __init__(self, *args, **kwargs):
+                kwargs.update(bucket_bytes=1024, first_bucket_bytes=256)
+                super().__init__(*args, **kwargs)
+
+        _gradsync.GradSyncEngine = SmallBuckets
     dctx = core.DistributedContext(rank=rank, size=size, local_rank=rank, local_size=size, cross_rank=0, cross_size=1,
                                    pub_port=zmq_ports[0], pull_port=zmq_ports[1])
     try:
@@ -117,6 +128,7 @@ def _worker(rank: int, size: int, port: int, zmq_ports, name: str, sharded: bool
             assert reports == []
         # one allreduce (or reduce-scatter) per bucket per optimizer step, issued in the same order on both ranks
         n_buckets = sum(len(fs.buckets) for fs in eng.sets)
+        assert (n_buckets >= 3) == small_buckets
         per_step = [e for e in fake.log if e[0] in ("allreduce", "reduce_scatter") and e[1] > 1]
         assert len(per_step) == n_buckets * g.steps
         everyone = dctx.allgather([e[1] for e in per_step])
@@ -128,9 +140,12 @@ def _worker(rank: int, size: int, port: int, zmq_ports, name: str, sharded: bool
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("name,sharded", [("sgd_n2_a2", False), ("adamw_n2_a4_clip", False), ("sgd_n2_a2", True), ("adamw_n2_a4_clip", True)])
-def test_two_rank_scenarios_with_emulated_kernels_and_gloo(tmp_path, name, sharded):
+@pytest.mark.parametrize("name,sharded,small_buckets", [
+    ("sgd_n2_a2", False, False), ("adamw_n2_a4_clip", False, True), ("sgd_n2_a2", True, True), ("adamw_n2_a4_clip", True, False),
+    ("sgd_n2_a2", False, True), ("adamw_n2_a4_clip", True, True),
+])
+def test_two_rank_scenarios_with_emulated_kernels_and_gloo(tmp_path, name, sharded, small_buckets):
     import torch.multiprocessing as mp
 
-    mp.spawn(_worker, args=(2, _free_port(), (_free_port(), _free_port()), name, sharded, str(tmp_path)), nprocs=2, join=True)
+    mp.spawn(_worker, args=(2, _free_port(), (_free_port(), _free_port()), name, sharded, small_buckets, str(tmp_path)), nprocs=2, join=True)
     assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
