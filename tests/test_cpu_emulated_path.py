@@ -402,3 +402,102 @@ def test_identity_experiment_from_its_yaml(monkeypatch, tmp_path):
     saved = torch.load(ckpt / "state_dict.pth", weights_only=False)
     np.testing.assert_allclose(float(saved["models_state_dict"][0]["weight"]), got[-1], rtol=1e-6)
     sys.modules.pop("model_def", None)
+
+
+# ---- randomized differential test: engine bookkeeping vs the reference's lines over plain torch --------------------
+class _Branchy(torch.nn.Module):
+    """A trunk plus a side branch that only some batches use: its parameters get no gradient on the others."""
+
+    def __init__(self, width, depth):
+        super().__init__()
+        self.inp = torch.nn.Linear(6, width)
+        self.mid = torch.nn.ModuleList([torch.nn.Linear(width, width) for _ in range(depth)])
+        self.norm = torch.nn.LayerNorm(width)
+        self.side = torch.nn.Linear(width, width, bias=False)
+        self.out = torch.nn.Linear(width, 3)
+
+    def forward(self, x, use_side):
+        h = torch.tanh(self.inp(x))
+        for layer in self.mid:
+            h = torch.tanh(layer(h)) + h
+        h = self.norm(h)
+        if use_side:
+            h = h + self.side(h)
+        return self.out(h)
+
+
+def _random_optimizer(rng, model):
+    decay = [p for p in model.parameters() if p.ndim >= 2]
+    rest = [p for p in model.parameters() if p.ndim < 2]
+    groups = [{"params": decay, "weight_decay": float(rng.choice([0.0, 0.01, 0.1])), "lr": float(rng.choice([0.01, 0.03]))},
+              {"params": rest, "weight_decay": 0.0}]
+    kind = rng.choice(["sgd", "sgd_plain", "adam", "adamw"])
+    if kind == "sgd":
+        return torch.optim.SGD(groups, lr=0.05, momentum=0.9, nesterov=bool(rng.integers(2)), dampening=0.0)
+    if kind == "sgd_plain":
+        return torch.optim.SGD(groups, lr=0.05, momentum=float(rng.choice([0.0, 0.5])), dampening=float(rng.choice([0.0, 0.2])))
+    cls = torch.optim.Adam if kind == "adam" else torch.optim.AdamW
+    return cls(groups, lr=0.01, betas=(0.9, float(rng.choice([0.95, 0.999]))), eps=1e-8)
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_random_trials_match_the_reference_lines(monkeypatch, seed):
+    """Random model shape, optimizer kind and hyper-parameters per group, aggregation frequency, clipping by norm /
+    by value / none, a StepLR stepped every optimizer step, and batches that leave some parameters without a
+    gradient: this harness (emulated kernels) against oracle/torch_port.RefContext, which restates the reference's
+    lines over torch's own optimizers.  Catches bookkeeping slips the fixed fixtures cannot: range tables with gaps,
+    per-parameter Adam step counters drifting apart, momentum buffers created late, rates changing between steps."""
+    from oracle import torch_port
+
+    fake_dgs.install(monkeypatch)
+    rng = np.random.default_rng(seed)
+    torch.manual_seed(seed)
+    base = _Branchy(int(rng.choice([8, 16, 24])), int(rng.integers(1, 4)))
+    agg = int(rng.choice([1, 2, 3]))
+    clip = [None, ("norm", 0.5), ("value", 0.05)][int(rng.integers(3))]
+    steps = 6
+    g = torch.Generator().manual_seed(seed)
+    data = [(torch.randn(5, 6, generator=g), torch.randn(5, 3, generator=g), bool(rng.integers(2))) for _ in range(steps * agg)]
+    # within one aggregation window the side branch is used by all micro-batches or by none (otherwise the reference
+    # itself divides a partial sum by the full window length, which is fine, but then every step has every gradient)
+    data = [(x, y, data[(i // agg) * agg][2]) for i, (x, y, _) in enumerate(data)]
+
+    def clip_fn(params):
+        params = [p for p in params if p.grad is not None]
+        if clip and clip[0] == "norm":
+            torch.nn.utils.clip_grad_norm_(params, clip[1])
+        elif clip:
+            torch.nn.utils.clip_grad_value_(params, clip[1])
+
+    results = []
+    for which in ("ours", "ref"):
+        ctx = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 5}, aggregation_frequency=agg) if which == "ours" \
+            else torch_port.RefContext(aggregation_frequency=agg)
+        model = ctx.wrap_model(copy.deepcopy(base))
+        opt = ctx.wrap_optimizer(_random_optimizer(np.random.default_rng(seed + 100), model))
+        sched = torch.optim.lr_scheduler.StepLR(opt, step_size=2, gamma=0.5)
+        trace = []
+        for i, (x, y, use_side) in enumerate(data):
+            ctx._current_batch_idx = i
+            ctx.backward(torch.nn.functional.mse_loss(model(x, use_side), y))
+            ctx.step_optimizer(opt, clip_grads=clip_fn if clip else None)
+            if (i + 1) % agg == 0:
+                sched.step()
+                trace.append([_np(p) for p in model.parameters()])
+        state = {n: {k: (_np(v) if torch.is_tensor(v) and v.ndim else float(v)) for k, v in opt.state[p].items()}
+                 for n, p in model.named_parameters() if p in opt.state}
+        results.append((trace, state))
+        if which == "ours":
+            ctx.close()
+    (ours, ours_state), (ref, ref_state) = results
+    for s, (pa, pb) in enumerate(zip(ours, ref)):
+        for a, b in zip(pa, pb):
+            assert_close(a, b, "float32", f"seed {seed}: after optimizer step {s}")  # relative to the tensor's magnitude
+    assert ours_state.keys() == ref_state.keys()
+    for name in ref_state:
+        assert ours_state[name].keys() == ref_state[name].keys(), name
+        for k, want in ref_state[name].items():
+            if k == "step":
+                assert ours_state[name][k] == want, f"seed {seed}: {name}.step"  # integer counter: exact
+            else:
+                assert_close(ours_state[name][k], want, "float32", f"seed {seed}: {name}.{k}")
