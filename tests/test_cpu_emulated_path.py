@@ -33,15 +33,16 @@ class GoldenTrial(pytorch.PyTorchTrial):
 
     def __init__(self, context, g, rec):
         self.context, self.g, self.rec = context, g, rec
-        model = GoldenNet()
+        dtype = getattr(torch, g.dtype)
+        model = GoldenNet().to(dtype)
         with torch.no_grad():
             for p, init in zip(model.parameters(), g.init_params()):
-                p.copy_(torch.from_numpy(init))
+                p.copy_(torch.from_numpy(init).to(dtype))
         self.model = context.wrap_model(model)
         self.plist = list(self.model.parameters())
         self.opt = context.wrap_optimizer(make_optimizer(self.model, g.hp), average_aggregated_gradients=g.average)
         x, y = make_data(g.steps * g.agg, g.hp["global_batch_size"])
-        self.ds = torch.utils.data.TensorDataset(x, y)
+        self.ds = torch.utils.data.TensorDataset(x.to(dtype), y.to(dtype))
 
     def build_training_data_loader(self):
         return pytorch.DataLoader(self.ds, batch_size=self.context.get_per_slot_batch_size(), shuffle=False)
@@ -58,7 +59,7 @@ class GoldenTrial(pytorch.PyTorchTrial):
 
     def train_batch(self, batch, epoch_idx, batch_idx):
         x, y = batch
-        loss = torch.nn.functional.mse_loss(self.model(x), y)
+        loss = torch.nn.functional.mse_loss(self.model(x).float(), y.float())
         self.context.backward(loss)
         self.context.step_optimizer(self.opt, clip_grads=self._clip)
         if (batch_idx + 1) % self.g.agg == 0:
@@ -67,7 +68,7 @@ class GoldenTrial(pytorch.PyTorchTrial):
         return {"loss": loss}
 
 
-FP32_ONE_SLOT = [n for n, sc in SCENARIOS.items() if sc["slots"] == 1 and sc["dtype"] == "float32"]
+FP32_ONE_SLOT = [n for n, sc in SCENARIOS.items() if sc["slots"] == 1]  # fp32 and the bf16 scenario
 
 
 def _native_host_loop():
@@ -105,25 +106,26 @@ def test_single_slot_scenarios_through_the_whole_python_path(monkeypatch, name, 
     kinds = {e[0] for e in fake.log}
     assert "flatten" in kinds and (("adam" in kinds or "sgd" in kinds) == fused)  # Adadelta steps in torch, on our gradient views
     opt_order_to_model = [0, 4, 1, 2, 3, 5]
+    dt = g.dtype
     for s in range(g.steps):
         want_avg = g.per_step("avg_grads", s)
         for j, i in enumerate(opt_order_to_model):
-            assert_close(rec["avg"][s][j], want_avg[i], "float32", f"{name}: synced grad, step {s}, param {i}")
+            assert_close(rec["avg"][s][j], want_avg[i], dt, f"{name}: synced grad, step {s}, param {i}")
         for i in range(N_PARAMS):
-            assert_close(rec["params"][s][i], g.per_step("params", s)[i], "float32", f"{name}: parameter {i} after step {s}")
+            assert_close(rec["params"][s][i], g.per_step("params", s)[i], dt, f"{name}: parameter {i} after step {s}")
             st = rec["state"][s][i]
             if g.hp["optimizer"] == "sgd":
-                assert_close(st["momentum_buffer"], g.state(s, i, "momentum_buffer"), "float32", f"{name}: momentum {i} step {s}")
+                assert_close(st["momentum_buffer"], g.state(s, i, "momentum_buffer"), dt, f"{name}: momentum {i} step {s}")
             elif g.hp["optimizer"] in ("adam", "adamw"):
-                assert_close(st["exp_avg"], g.state(s, i, "exp_avg"), "float32", f"{name}: exp_avg {i} step {s}")
-                assert_close(st["exp_avg_sq"], g.state(s, i, "exp_avg_sq"), "float32", f"{name}: exp_avg_sq {i} step {s}")
+                assert_close(st["exp_avg"], g.state(s, i, "exp_avg"), dt, f"{name}: exp_avg {i} step {s}")
+                assert_close(st["exp_avg_sq"], g.state(s, i, "exp_avg_sq"), dt, f"{name}: exp_avg_sq {i} step {s}")
                 assert float(st["step"]) == float(g.state(s, i, "step")) == s + 1
         if g.clip is not None and g.clip[0] == "norm":
-            assert_close(float(rec["norm"][s]), g.z["total_norm"][s], "float32", f"{name}: total norm step {s}")
+            assert_close(float(rec["norm"][s]), g.z["total_norm"][s], dt, f"{name}: total norm step {s}")
     assert [n for n, _ in reports] == g.z["reported_steps"].tolist()
     for (n, r), want_avg, want_batches in zip(reports, g.z["reported_avg_loss"], g.z["reported_batch_loss"]):
-        assert_close(r["avg_metrics"]["loss"], want_avg, "float32", f"{name}: reported avg loss at {n}")
-        assert_close([float(b["loss"]) for b in r["batch_metrics"]], want_batches, "float32", f"{name}: per-batch loss at {n}")
+        assert_close(r["avg_metrics"]["loss"], want_avg, dt, f"{name}: reported avg loss at {n}")
+        assert_close([float(b["loss"]) for b in r["batch_metrics"]], want_batches, dt, f"{name}: per-batch loss at {n}")
     ctx.close()
 
 
