@@ -215,6 +215,7 @@ class GradSyncEngine:
         # extra factor folded into the flatten kernel's scale: 1/S while an auto-AMP GradScaler's loss scale S is
         # in the gradients (PyTorchTrialContext.backward sets it per window), else exactly 1.0
         self.unscale = 1.0
+        self.stepped_in_batch: Optional[int] = None  # batch index of the last optimizer step (PyTorchTrialContext.backward)
         self.needs_acc = self.agg * self.bpps > 1
         self.sets: List[_FlatSet] = []
         self._where: Dict[int, Tuple[int, int]] = {}  # id(param) -> (set index, tensor index)

@@ -514,7 +514,12 @@ class PyTorchTrialContext(_PyTorchReducerContext):
         self._backward_calls += 1
         boundary = self._should_communicate_and_update() if self._engines else False
         unscale = 1.0 / self._loss_scale_on_host() if self._auto_amp_active() else 1.0
-        for eng in self._engines.values():
+        # An optimizer that has already stepped in THIS batch sits the rest of the batch out: gradients that later
+        # passes leave on its parameters (a generator loss flowing through the discriminator) stay in p.grad, as in
+        # the reference, where the trial may clear them or let the next batch accumulate onto them.
+        batch = self._current_batch_idx
+        active = [eng for eng in self._engines.values() if batch is None or eng.stepped_in_batch != batch]
+        for eng in active:
             # auto-AMP: 1/S rides on the 1/(N*A) factor of the flatten kernel, so the wire holds true gradients
             # and GradScaler.unscale_'s read+write pass over every gradient never runs
             eng.unscale = unscale if self._prefolds(eng) else 1.0
@@ -522,7 +527,7 @@ class PyTorchTrialContext(_PyTorchReducerContext):
         try:
             loss.backward(gradient=gradient, retain_graph=retain_graph, create_graph=create_graph)  # type: ignore
         finally:
-            for eng in self._engines.values():
+            for eng in active:
                 eng.end_pass()
 
     @staticmethod
@@ -648,6 +653,7 @@ class PyTorchTrialContext(_PyTorchReducerContext):
         if auto_zero_grads and materialized:
             eng.clear_grads()
         eng.reset_window()
+        eng.stepped_in_batch = self._current_batch_idx
 
     # ---- optimizer step -----------------------------------------------------------------------------
     def step_optimizer(
@@ -713,6 +719,7 @@ class PyTorchTrialContext(_PyTorchReducerContext):
             if materialized:
                 eng.clear_grads()
         eng.reset_window()
+        eng.stepped_in_batch = self._current_batch_idx
 
     def _sharded_step(self, eng: Any, optimizer: Any, parameters: List[Any], present: Any, clip_grads: Any, scaler: Any) -> None:
         """step_optimizer when the engine reduce-scatters (opt-in sharded step): each rank holds only its slice
@@ -734,6 +741,7 @@ class PyTorchTrialContext(_PyTorchReducerContext):
                 )
         eng.fused_step(present, clip_req)
         eng.reset_window()
+        eng.stepped_in_batch = self._current_batch_idx
 
     # ---- epoch helpers the controller maintains ---------------------------------------------------
     def is_epoch_start(self) -> bool:

@@ -503,3 +503,83 @@ def test_random_trials_match_the_reference_lines(monkeypatch, seed):
                 assert ours_state[name][k] == want, f"seed {seed}: {name}.step"  # integer counter: exact
             else:
                 assert_close(ours_state[name][k], want, "float32", f"seed {seed}: {name}.{k}")
+
+
+# ---- usage patterns beyond "one loss, one optimizer" ----------------------------------------------------------------
+@pytest.mark.parametrize("agg,stray", [(1, "clear"), (1, "freeze"), (2, "freeze"), (1, "keep")])
+def test_two_optimizers_two_losses_and_two_backward_passes_per_step(monkeypatch, agg, stray):
+    """A GAN-shaped trial: two models with an optimizer each; the first optimizer's step sees the sum of TWO
+    backward passes per batch (backward_passes_per_step=2, reference _pytorch_context.py:313-378), the second's loss
+    flows through the first model too.  What happens to the gradients that pass leaves on the first model is the
+    trial's business, as in the reference: "clear" them afterwards (they must then not show up in the next window),
+    "freeze" the first model during the pass (none arise), or "keep" them (they add to the next window's gradient).
+    Against the reference's lines over plain torch."""
+    from oracle import torch_port
+
+    fake_dgs.install(monkeypatch)
+    torch.manual_seed(3)
+    gen0, disc0 = torch.nn.Linear(4, 6), torch.nn.Sequential(torch.nn.Linear(6, 5), torch.nn.Tanh(), torch.nn.Linear(5, 1))
+    g = torch.Generator().manual_seed(3)
+    data = [torch.randn(7, 4, generator=g) for _ in range(4 * agg)]
+    results = []
+    for which in ("ours", "ref"):
+        ctx = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 7}, aggregation_frequency=agg) if which == "ours" \
+            else torch_port.RefContext(aggregation_frequency=agg)
+        gen, disc = ctx.wrap_model(copy.deepcopy(gen0)), ctx.wrap_model(copy.deepcopy(disc0))
+        opt_d = ctx.wrap_optimizer(torch.optim.Adam(disc.parameters(), lr=0.01), backward_passes_per_step=2)
+        opt_g = ctx.wrap_optimizer(torch.optim.SGD(gen.parameters(), lr=0.05, momentum=0.9))
+        trace = []
+        for i, z in enumerate(data):
+            ctx._current_batch_idx = i
+            fake_sample = gen(z).detach()
+            ctx.backward(disc(fake_sample).mean())          # discriminator: two losses, two backward passes
+            ctx.backward((disc(z @ torch.ones(4, 6)) - 1).pow(2).mean())
+            ctx.step_optimizer(opt_d)
+            for p in disc.parameters():
+                p.requires_grad_(stray != "freeze")
+            ctx.backward(-disc(gen(z)).mean())               # generator: through the discriminator
+            ctx.step_optimizer(opt_g)
+            for p in disc.parameters():
+                p.requires_grad_(True)
+                if stray == "clear":                         # the generator pass left gradients on the discriminator
+                    p.grad = None
+            if (i + 1) % agg == 0:
+                trace.append([_np(p) for p in list(gen.parameters()) + list(disc.parameters())])
+        results.append(trace)
+        if which == "ours":
+            ctx.close()
+    for s, (pa, pb) in enumerate(zip(*results)):
+        for a, b in zip(pa, pb):
+            assert_close(a, b, "float32", f"after optimizer step {s}")
+
+
+def test_gradients_stay_visible_without_auto_zero_grads(monkeypatch):
+    """step_optimizer(auto_zero_grads=False): after the step p.grad holds the synchronized gradients the step used
+    (reference :923-924 simply does not call zero_grad), until the trial clears them itself."""
+    fake_dgs.install(monkeypatch)
+    torch.manual_seed(4)
+    ctx = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 4})
+    model = ctx.wrap_model(torch.nn.Linear(3, 2))
+    twin = copy.deepcopy(model)
+    opt = ctx.wrap_optimizer(torch.optim.SGD(model.parameters(), lr=0.1))
+    ref_opt = torch.optim.SGD(twin.parameters(), lr=0.1)
+    x = torch.randn(4, 3)
+    for i in range(3):
+        ctx._current_batch_idx = i
+        ctx.backward(model(x).pow(2).mean())
+        ctx.step_optimizer(opt, auto_zero_grads=False)
+        twin(x).pow(2).mean().backward()
+        ref_opt.step()
+        for p, q in zip(model.parameters(), twin.parameters()):
+            assert p.grad is not None
+            assert_close(_np(p.grad), _np(q.grad), "float32", f"gradient left on the parameter, step {i}")
+            assert_close(_np(p), _np(q), "float32", f"parameter, step {i}")
+        for p in list(model.parameters()) + list(twin.parameters()):
+            p.grad = None
+    with pytest.raises(det.errors.InvalidExperimentException, match="auto_zero_grads must be set to true"):
+        ctx2 = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 4}, aggregation_frequency=2)
+        m2 = ctx2.wrap_model(torch.nn.Linear(3, 2))
+        o2 = ctx2.wrap_optimizer(torch.optim.SGD(m2.parameters(), lr=0.1))
+        ctx2._current_batch_idx = 0
+        ctx2.step_optimizer(o2, auto_zero_grads=False)
+    ctx.close()
