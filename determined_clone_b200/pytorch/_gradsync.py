@@ -219,6 +219,8 @@ class GradSyncEngine:
         self.needs_acc = self.agg * self.bpps > 1
         self.sets: List[_FlatSet] = []
         self._where: Dict[int, Tuple[int, int]] = {}  # id(param) -> (set index, tensor index)
+        self._n_group_params = 0  # parameters in the optimizer's groups when it was wrapped
+        self._frozen_at_wrap: List[torch.nn.Parameter] = []  # of those, the ones left out (requires_grad=False)
         self._hooks: List[Any] = []  # autograd hooks (order learning, then one sentinel per bucket)
         self._state_hook: Any = None
         self._sentinels: Optional[Dict[int, Tuple[int, int]]] = None  # id(param) -> (set, bucket); None = not learnt
@@ -275,7 +277,9 @@ class GradSyncEngine:
         by_dtype: Dict[torch.dtype, _FlatSet] = {}
         for gi, group in enumerate(self.optimizer.param_groups):
             for p in group["params"]:
+                self._n_group_params += 1
                 if not p.requires_grad:
+                    self._frozen_at_wrap.append(p)
                     continue
                 if p.device != self.device:
                     raise errors.InvalidExperimentException(
@@ -592,6 +596,19 @@ class GradSyncEngine:
         """Make every wire slice final (stragglers that never came through a final-pass hook), issue the
         remaining allreduces and make the compute stream wait for them.  Returns, per set, which tensors
         received any gradient in this window."""
+        for p in self._frozen_at_wrap:
+            if p.grad is not None:
+                raise errors.InvalidExperimentException(
+                    "a parameter that had requires_grad=False when its optimizer was wrapped has a gradient now: it "
+                    "has no place in the optimizer's flat buffers and would never be synchronized or stepped. Unfreeze "
+                    "parameters before wrap_optimizer() (a frozen phase can use lr 0 or detach() instead)."
+                )
+        if sum(len(g["params"]) for g in self.optimizer.param_groups) != self._n_group_params:
+            raise errors.InvalidExperimentException(
+                "the optimizer's parameters changed after wrap_optimizer() (add_param_group?): its parameters, "
+                "gradients and state live in flat buffers laid out when it was wrapped. Create the optimizer with "
+                "all its parameter groups before wrapping it (groups can start with lr 0 or frozen parameters)."
+            )
         present: List[List[bool]] = []
         self.last_total_norm = None
         for si, fs in enumerate(self.sets):

@@ -583,3 +583,53 @@ def test_gradients_stay_visible_without_auto_zero_grads(monkeypatch):
         ctx2._current_batch_idx = 0
         ctx2.step_optimizer(o2, auto_zero_grads=False)
     ctx.close()
+
+
+def test_optimizer_membership_changes_after_wrapping_fail_loudly(monkeypatch):
+    """The flat buffers are laid out at wrap_optimizer(): a parameter group added later, or a parameter unfrozen
+    later, would silently never be synchronized or stepped -- both are refused when the next step finds them.
+    Parameters that stay frozen, gradients from a plain loss.backward() and steps without any gradient are fine."""
+    fake_dgs.install(monkeypatch)
+    torch.manual_seed(0)
+    x = torch.randn(4, 3)
+
+    def make(freeze_second=False, both=False):
+        ctx = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 4})
+        m = ctx.wrap_model(torch.nn.Sequential(torch.nn.Linear(3, 4), torch.nn.Linear(4, 2)))
+        if freeze_second:
+            for p in m[1].parameters():
+                p.requires_grad_(False)
+        params = list(m.parameters()) if both or freeze_second else list(m[0].parameters())
+        return ctx, m, ctx.wrap_optimizer(torch.optim.SGD(params, lr=0.1, momentum=0.9))
+
+    ctx, m, opt = make()
+    w0 = m[0].weight.detach().clone()
+    ctx._current_batch_idx = 0
+    m(x).pow(2).mean().backward()            # not through context.backward(): picked up by the step
+    ctx.step_optimizer(opt)
+    assert not torch.equal(w0, m[0].weight.detach()) and m[0].weight.grad is None
+    ctx._current_batch_idx = 1
+    w1 = m[0].weight.detach().clone()
+    ctx.step_optimizer(opt)                  # no gradient at all: nothing moves (torch's step skips such parameters)
+    assert torch.equal(w1, m[0].weight.detach())
+    opt.add_param_group({"params": list(m[1].parameters())})
+    ctx._current_batch_idx = 2
+    ctx.backward(m(x).pow(2).mean())
+    with pytest.raises(det.errors.InvalidExperimentException, match="parameters changed after wrap_optimizer"):
+        ctx.step_optimizer(opt)
+    ctx.close()
+
+    ctx, m, opt = make(freeze_second=True)   # frozen parameters in the optimizer are fine as long as they stay frozen
+    for i in range(2):
+        ctx._current_batch_idx = i
+        v0 = m[1].weight.detach().clone()
+        ctx.backward(m(x).pow(2).mean())
+        ctx.step_optimizer(opt)
+        assert torch.equal(v0, m[1].weight.detach())
+    for p in m[1].parameters():
+        p.requires_grad_(True)
+    ctx._current_batch_idx = 2
+    ctx.backward(m(x).pow(2).mean())
+    with pytest.raises(det.errors.InvalidExperimentException, match="requires_grad=False when its optimizer was wrapped"):
+        ctx.step_optimizer(opt)
+    ctx.close()
