@@ -633,3 +633,50 @@ def test_optimizer_membership_changes_after_wrapping_fail_loudly(monkeypatch):
     with pytest.raises(det.errors.InvalidExperimentException, match="requires_grad=False when its optimizer was wrapped"):
         ctx.step_optimizer(opt)
     ctx.close()
+
+
+_OPTIMIZER_VARIANTS = {
+    # name: (constructor, does the fused step stand in for optimizer.step()?)
+    "adam_maximize": (lambda ps: torch.optim.Adam(ps, lr=0.01, maximize=True), True),
+    "adam_decoupled_wd": (lambda ps: torch.optim.Adam(ps, lr=0.01, weight_decay=0.1, decoupled_weight_decay=True), True),
+    "adam_l2_wd": (lambda ps: torch.optim.Adam(ps, lr=0.01, weight_decay=0.1), True),
+    "adam_foreach_off": (lambda ps: torch.optim.Adam(ps, lr=0.01, foreach=False), True),
+    "sgd_maximize": (lambda ps: torch.optim.SGD(ps, lr=0.01, momentum=0.9, maximize=True), True),
+    "sgd_dampening": (lambda ps: torch.optim.SGD(ps, lr=0.01, momentum=0.9, dampening=0.3), True),
+    "sgd_plain": (lambda ps: torch.optim.SGD(ps, lr=0.01), True),
+    # what the kernels do not implement keeps torch's own step, on our gradient views
+    "adam_amsgrad": (lambda ps: torch.optim.Adam(ps, lr=0.01, amsgrad=True), False),
+    "adamw_amsgrad": (lambda ps: torch.optim.AdamW(ps, lr=0.01, amsgrad=True), False),
+    "adam_tensor_lr": (lambda ps: torch.optim.Adam(ps, lr=torch.tensor(0.01)), False),
+    "rmsprop": (lambda ps: torch.optim.RMSprop(ps, lr=0.01), False),
+    "nadam": (lambda ps: torch.optim.NAdam(ps, lr=0.01), False),
+}
+
+
+@pytest.mark.parametrize("name", sorted(_OPTIMIZER_VARIANTS))
+def test_optimizer_options_are_fused_or_left_to_torch(monkeypatch, name):
+    """Every optimizer option either is implemented by the step entry points (same trajectory as torch's own step)
+    or makes the engine leave optimizer.step() to torch -- never a fused step that silently ignores the option."""
+    make, want_fused = _OPTIMIZER_VARIANTS[name]
+    fake = fake_dgs.install(monkeypatch)
+    torch.manual_seed(0)
+    base = torch.nn.Sequential(torch.nn.Linear(3, 4), torch.nn.Tanh(), torch.nn.Linear(4, 2))
+    x, y = torch.randn(6, 3), torch.randn(6, 2)
+    ctx = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 6})
+    model = ctx.wrap_model(copy.deepcopy(base))
+    opt = ctx.wrap_optimizer(make(model.parameters()))
+    twin = copy.deepcopy(base)
+    twin_opt = make(twin.parameters())
+    assert ctx._engines[opt].can_fuse() == want_fused
+    for i in range(5):
+        ctx._current_batch_idx = i
+        ctx.backward(torch.nn.functional.mse_loss(model(x), y))
+        ctx.step_optimizer(opt)
+        torch.nn.functional.mse_loss(twin(x), y).backward()
+        twin_opt.step()
+        twin_opt.zero_grad()
+        for p, q in zip(model.parameters(), twin.parameters()):
+            assert_close(_np(p), _np(q), "float32", f"{name}: step {i}")
+    kinds = {e[0] for e in fake.log}
+    assert "flatten" in kinds and (bool(kinds & {"adam", "sgd"}) == want_fused)
+    ctx.close()
