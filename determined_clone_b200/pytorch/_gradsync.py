@@ -609,6 +609,16 @@ class GradSyncEngine:
                 "gradients and state live in flat buffers laid out when it was wrapped. Create the optimizer with "
                 "all its parameter groups before wrapping it (groups can start with lr 0 or frozen parameters)."
             )
+        for fs in self.sets:
+            base, isz = fs.param.data_ptr(), fs.param.element_size()
+            for t in (fs.tensors[0], fs.tensors[-1]):
+                if t.param.data_ptr() != base + t.off * isz:
+                    raise errors.InvalidExperimentException(
+                        "a wrapped optimizer's parameter no longer lives in the optimizer's flat parameter buffer: its "
+                        ".data was rebound after wrap_optimizer() (model.to(...), .half(), p.data = ...). The step "
+                        "would update memory the model no longer reads. Move or cast the model before wrapping; "
+                        "change values in place (p.data.copy_(...), load_state_dict) afterwards."
+                    )
         present: List[List[bool]] = []
         self.last_total_norm = None
         for si, fs in enumerate(self.sets):

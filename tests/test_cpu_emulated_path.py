@@ -680,3 +680,39 @@ def test_optimizer_options_are_fused_or_left_to_torch(monkeypatch, name):
     kinds = {e[0] for e in fake.log}
     assert "flatten" in kinds and (bool(kinds & {"adam", "sgd"}) == want_fused)
     ctx.close()
+
+
+def test_parameters_moved_out_of_the_flat_buffer_are_noticed(monkeypatch):
+    """Parameters are views of one flat buffer per optimizer; rebinding their .data after wrap_optimizer() (model.to,
+    .half(), p.data = ...) would leave the step updating memory the model no longer reads.  The first and last
+    parameter of every buffer are checked at each step: whole-model moves are caught, in-place changes are fine,
+    and a channels_last model trains to the same weights (its parameters become plain contiguous views)."""
+    fake_dgs.install(monkeypatch)
+    torch.manual_seed(0)
+    base = torch.nn.Sequential(torch.nn.Conv2d(3, 8, 3, padding=1), torch.nn.ReLU(), torch.nn.Conv2d(8, 4, 3, padding=1))
+    base = base.to(memory_format=torch.channels_last)
+    x = torch.randn(2, 3, 8, 8).to(memory_format=torch.channels_last)
+    ctx = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 2})
+    model = ctx.wrap_model(copy.deepcopy(base))
+    opt = ctx.wrap_optimizer(torch.optim.SGD(model.parameters(), lr=0.1, momentum=0.9))
+    twin = copy.deepcopy(base)
+    twin_opt = torch.optim.SGD(twin.parameters(), lr=0.1, momentum=0.9)
+    for i in range(3):
+        ctx._current_batch_idx = i
+        ctx.backward(model(x).pow(2).mean())  # conv weight gradients arrive in channels_last strides
+        ctx.step_optimizer(opt)
+        twin(x).pow(2).mean().backward()
+        twin_opt.step()
+        twin_opt.zero_grad()
+    for p, q in zip(model.parameters(), twin.parameters()):
+        assert_close(_np(p), _np(q), "float32", "channels_last model")
+    with torch.no_grad():
+        model[0].weight.copy_(twin[0].weight * 0.5)  # in place: still the buffer's memory
+    ctx._current_batch_idx = 3
+    ctx.backward(model(x).pow(2).mean())
+    ctx.step_optimizer(opt)
+    model.double()  # rebinds every parameter's .data
+    ctx._current_batch_idx = 4
+    with pytest.raises(det.errors.InvalidExperimentException, match="no longer lives in the optimizer's flat parameter buffer"):
+        ctx.step_optimizer(opt)
+    ctx.close()
