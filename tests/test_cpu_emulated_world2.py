@@ -149,3 +149,111 @@ def test_two_rank_scenarios_with_emulated_kernels_and_gloo(tmp_path, name, shard
 
     mp.spawn(_worker, args=(2, _free_port(), (_free_port(), _free_port()), name, sharded, small_buckets, str(tmp_path)), nprocs=2, join=True)
     assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
+
+
+def _amp_worker(rank: int, size: int, port: int, zmq_ports, out_dir: str) -> None:
+    """tests/test_gpu_amp.py's two-slot case on the CPU: auto-AMP with accumulation and clipping; an inf in ONE rank's
+    data must make EVERY rank skip that step (the check runs on the all-reduced gradients), against torch DDP over
+    gloo with torch's own GradScaler protocol."""
+    for p in (str(ROOT), str(ROOT / "tests"), str(ROOT / "tests" / "golden")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import contextlib
+    import copy
+
+    import torch.distributed as dist
+
+    import fake_dgs
+    from golden_io import assert_close
+
+    from determined_clone_b200 import core, pytorch
+
+    torch.set_num_threads(1)
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=size)
+    fake_dgs.install()
+    dctx = core.DistributedContext(rank=rank, size=size, local_rank=rank, local_size=size, cross_rank=0, cross_size=1,
+                                   pub_port=zmq_ports[0], pull_port=zmq_ports[1])
+    try:
+        agg, clip = 2, 0.5
+        torch.manual_seed(5)
+        base = torch.nn.Sequential(torch.nn.Linear(12, 32), torch.nn.LayerNorm(32), torch.nn.Tanh(), torch.nn.Linear(32, 5))
+        g = torch.Generator().manual_seed(300 + rank)
+        data = [(torch.randn(8, 12, generator=g), torch.randn(8, 5, generator=g)) for _ in range(8 * agg)]
+        if rank == 1:
+            data[4][0][0, 0] = float("inf")  # first micro-batch of the third window, on rank 1 only
+
+        def new_scaler():
+            return torch.amp.GradScaler("cpu", init_scale=1024.0, growth_interval=2)
+
+        def snap(model, opt, scaler, out):
+            out["params"].append([_np(p) for p in model.parameters()])
+            out["scale"].append(scaler.get_scale())
+            out["steps"].append([float(opt.state[p]["step"]) for p in model.parameters() if "step" in opt.state.get(p, {})])
+
+        ref_model = torch.nn.parallel.DistributedDataParallel(copy.deepcopy(base))
+        ref_opt, ref_scaler = torch.optim.AdamW(ref_model.parameters(), lr=1e-2, betas=(0.9, 0.95)), new_scaler()
+        ref = {"params": [], "scale": [], "steps": [], "norms": []}
+        params = list(ref_model.parameters())
+        for i, (x, y) in enumerate(data):
+            boundary = (i + 1) % agg == 0
+            with contextlib.nullcontext() if boundary else ref_model.no_sync():
+                ref_scaler.scale(torch.nn.functional.mse_loss(ref_model(x), y)).backward()
+            if not boundary:
+                continue
+            for p in params:
+                p.grad.div_(float(agg))
+            ref_scaler.unscale_(ref_opt)
+            ref["norms"].append(float(torch.nn.utils.clip_grad_norm_(params, clip)))
+            ref_scaler.step(ref_opt)
+            ref_opt.zero_grad()
+            ref_scaler.update()
+            snap(ref_model, ref_opt, ref_scaler, ref)
+
+        out = {"params": [], "scale": [], "steps": [], "norms": []}
+
+        class Trial(pytorch.PyTorchTrial):
+            def __init__(self, context):
+                self.context = context
+                self.model = context.wrap_model(copy.deepcopy(base))
+                context.experimental.use_amp()
+                context.wrap_scaler(new_scaler())
+                self.opt = context.wrap_optimizer(torch.optim.AdamW(self.model.parameters(), lr=1e-2, betas=(0.9, 0.95)))
+
+            def build_training_data_loader(self):
+                raise AssertionError("batches are fed by the test")
+
+            def train_batch(self, batch, epoch_idx, batch_idx):
+                loss = torch.nn.functional.mse_loss(self.model(batch[0]), batch[1])
+                self.context.backward(loss)
+                self.context.step_optimizer(self.opt, clip_grads=lambda ps: out["norms"].append(float(torch.nn.utils.clip_grad_norm_(list(ps), clip))))
+                return {"loss": loss}
+
+        ctx = pytorch.PyTorchTrialContext(distributed=dctx, hparams={"global_batch_size": 16}, slots_per_trial=size, aggregation_frequency=agg)
+        trial = Trial(ctx)
+        ctl = pytorch._PyTorchTrialController(trial, ctx, max_length=len(data), reporting_period=len(data))
+        for i, batch in enumerate(data):
+            ctx._current_batch_idx = i
+            ctl._train_batch(batch, 0, i)
+            if (i + 1) % agg == 0:
+                snap(trial.model, trial.opt, ctx._scaler, out)
+        assert ref["scale"][:3] == [1024.0, 2048.0, 1024.0] and ref["steps"][2] == ref["steps"][1]  # the third step was skipped
+        assert out["scale"] == ref["scale"] and out["steps"] == ref["steps"]
+        for a, b in zip(out["norms"], ref["norms"]):
+            assert np.isfinite(a) == np.isfinite(b)
+            if np.isfinite(b):
+                np.testing.assert_allclose(a, b, rtol=1e-5)
+        for s, (pa, pb) in enumerate(zip(out["params"], ref["params"])):
+            for a, b in zip(pa, pb):
+                assert_close(a, b, "float32", f"after optimizer step {s}")
+        ctx.close()
+        open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
+    finally:
+        dctx.close()
+        dist.destroy_process_group()
+
+
+def test_two_rank_auto_amp_skips_on_every_rank(tmp_path):
+    import torch.multiprocessing as mp
+
+    mp.spawn(_amp_worker, args=(2, _free_port(), (_free_port(), _free_port()), str(tmp_path)), nprocs=2, join=True)
+    assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
