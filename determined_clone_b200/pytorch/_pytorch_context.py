@@ -56,6 +56,11 @@ class PyTorchExperimentalContext:
         self._auto_amp = True
 
 
+def _same_device(a: torch.device, b: torch.device) -> bool:
+    """cuda == cuda:0 when one side carries no index."""
+    return a.type == b.type and (a.index is None or b.index is None or a.index == b.index)
+
+
 class _BufferSync:
     """DDP's broadcast_buffers=True: before every training forward, rank 0's module buffers (batch-norm
     running statistics, ...) overwrite every other rank's.  All buffers live in one flat byte tensor so
@@ -68,7 +73,7 @@ class _BufferSync:
         seen: Set[int] = set()
         for mod in model.modules():
             for name, buf in list(mod._buffers.items()):
-                if buf is None or id(buf) in seen or not buf.is_cuda:
+                if buf is None or id(buf) in seen or not _same_device(buf.device, comm.device):
                     continue
                 seen.add(id(buf))
                 items.append((mod, name, buf))

@@ -257,3 +257,74 @@ def test_two_rank_auto_amp_skips_on_every_rank(tmp_path):
 
     mp.spawn(_amp_worker, args=(2, _free_port(), (_free_port(), _free_port()), str(tmp_path)), nprocs=2, join=True)
     assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
+
+
+def _bn_worker(rank: int, size: int, port: int, zmq_ports, out_dir: str) -> None:
+    """Module buffers under 2 ranks (tests/test_gpu_trial_parity.py's batch-norm case on the CPU): rank 0's initial
+    weights AND buffers win, rank 0's running statistics overwrite the others' before every training forward
+    (DDP's broadcast_buffers), num_batches_tracked stays an exact integer -- against torch DDP over gloo."""
+    for p in (str(ROOT), str(ROOT / "tests"), str(ROOT / "tests" / "golden")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import copy
+
+    import torch.distributed as dist
+
+    import fake_dgs
+    from oracle import torch_port
+
+    from determined_clone_b200 import core, pytorch
+
+    torch.set_num_threads(1)
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=size)
+    fake = fake_dgs.install()
+    dctx = core.DistributedContext(rank=rank, size=size, local_rank=rank, local_size=size, cross_rank=0, cross_size=1,
+                                   pub_port=zmq_ports[0], pull_port=zmq_ports[1])
+    try:
+        torch.manual_seed(100 + rank)  # different initial weights and buffers per rank
+        base = torch.nn.Sequential(torch.nn.Conv2d(3, 8, 3, padding=1), torch.nn.BatchNorm2d(8), torch.nn.ReLU(),
+                                   torch.nn.AdaptiveAvgPool2d(1), torch.nn.Flatten(), torch.nn.Linear(8, 4))
+        with torch.no_grad():
+            base[1].running_mean.add_(rank + 1.0)
+        g = torch.Generator().manual_seed(7 + rank)
+        data = [(torch.randn(4, 3, 8, 8, generator=g), torch.randn(4, 4, generator=g)) for _ in range(5)]
+
+        ref = torch_port.RefContext()
+        ref_model = torch.nn.parallel.DistributedDataParallel(copy.deepcopy(base))
+        ref.models.append(ref_model)
+        ref_opt = ref.wrap_optimizer(torch.optim.SGD(ref_model.parameters(), lr=0.1, momentum=0.9))
+        ours = pytorch.PyTorchTrialContext(distributed=dctx, hparams={"global_batch_size": 8}, slots_per_trial=size)
+        model = ours.wrap_model(copy.deepcopy(base))
+        opt = ours.wrap_optimizer(torch.optim.SGD(model.parameters(), lr=0.1, momentum=0.9))
+        assert len(ours._buffer_syncs) == 1 and ours._buffer_syncs[0].flats, "the model's buffers were not picked up"
+        for i, (x, y) in enumerate(data):
+            for ctx, mdl, o in ((ref, ref_model, ref_opt), (ours, model, opt)):
+                ctx._current_batch_idx = i
+                ctx.backward(torch.nn.functional.mse_loss(mdl(x), y))
+                ctx.step_optimizer(o)
+        for (name, a), b in zip(model.state_dict().items(), ref_model.module.state_dict().values()):
+            if a.dtype.is_floating_point:
+                np.testing.assert_allclose(a.numpy(), b.numpy(), rtol=1e-5, atol=1e-6, err_msg=name)
+            else:
+                assert torch.equal(a, b), name
+        flat = torch.cat([p.detach().reshape(-1) for p in model.parameters()])
+        gathered = [torch.empty_like(flat) for _ in range(size)]
+        dist.all_gather(gathered, flat)
+        assert all(torch.equal(gathered[0], t) for t in gathered)
+        # one buffer broadcast at wrap_model plus one per training forward; evaluation does not broadcast
+        n_before = sum(1 for e in fake.log if e[0] == "broadcast")
+        model.eval()
+        model(data[0][0])
+        assert sum(1 for e in fake.log if e[0] == "broadcast") == n_before
+        ours.close()
+        open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
+    finally:
+        dctx.close()
+        dist.destroy_process_group()
+
+
+def test_two_rank_module_buffers_follow_rank_zero(tmp_path):
+    import torch.multiprocessing as mp
+
+    mp.spawn(_bn_worker, args=(2, _free_port(), (_free_port(), _free_port()), str(tmp_path)), nprocs=2, join=True)
+    assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
