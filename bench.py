@@ -2,26 +2,31 @@
 """Benchmark of the per-step data-parallel path (BASELINE.json metric: samples/sec at 1/2/4/8 B200;
 grad-sync us/step and % of the HBM/NVLink roofline).
 
-    python bench.py --gpus N --steps K --warmup W            # this repo's path, one process per GPU
-    python bench.py --impl reference --steps K --warmup W    # the reference's CPU path (torch port), host cores
+    python bench.py --gpus N --steps K --warmup W                    # this repo's path, one process per GPU
+    python bench.py --impl reference --gpus N --steps K --warmup W   # the reference's CPU path: N gloo ranks, host cores
 
-Workload (config.workload): BASELINE.json configs[1], the CIFAR-10 ResNet PyTorchTrial, per-slot batch
-128 (weak scaling: global batch 128*N), fp32 SGD+momentum, synthetic data.  One step = one train_batch:
-forward, context.backward (flatten/scale/cast kernels + bucket allreduce on the NCCL side stream),
-context.step_optimizer (fused step kernel).
+Workload (config.workload): BASELINE.json configs[2], the ResNet-50 PyTorchTrial -- the config the metric is written
+on ("slots_per_trial=1/2/4/8") -- per-slot batch 64 (weak scaling: global batch 64*N), synthetic 224x224 batches,
+fp32 SGD + momentum.  One step = one train_batch: forward, context.backward (flatten/scale/cast kernels + bucket
+collectives on the communicator's side stream), context.step_optimizer (fused step kernel).
 
-  value  device-timed: inputs already resident in HBM, CUDA events around exactly K steps, max over ranks
-  e2e    the same trial driven through the public API (_PyTorchTrialController.run): every step copies
-         its batch from pinned host memory and reads the step's metrics back to the host
-  roofline  the fused optimizer kernel (largest HBM mover of the path), CUDA events recorded inside libdgs
-            immediately around each launch (dgs_timer_*) during the timed region, on the launching stream;
-            algorithmic bytes per element as stated in DESIGN.md
-  gradsync_microbench  BASELINE.json configs[4]: one flat 1 GiB fp32 bucket, accumulate + allreduce +
-            clip + AdamW, time per step against max(HBM, NVLink) roofline (N > 1: also the opt-in sharded step)
+  value     device-timed: inputs already resident in HBM, CUDA events around exactly K steps, max over ranks
+  e2e       the same trial driven through the public API (_PyTorchTrialController.run): every step copies its batch
+            from pinned host memory and reads the step's metrics back to the host
+  roofline  the fused optimizer kernel (largest HBM mover of the path; 511 MB per launch, beyond the 126 MB L2),
+            CUDA events recorded inside libdgs immediately around each launch (dgs_timer_*) during the timed
+            region, on the launching stream; algorithmic bytes per element as stated in DESIGN.md; `traffic` is
+            the ncu --set full capture of that kernel in this workload (profiles/, file named in the object)
+  parity    N >= 2 (and N = 1): the workloads of configs[1..3] for 10 optimizer steps under this path and, beside
+            it on the same GPUs and inputs, under torch DDP + torch.optim (the reference's lines,
+            workloads/parity.py); at N >= 2 also the 2-slot fixtures recorded from the unmodified reference on
+            ranks 0-1.  A mismatch makes the run exit non-zero.
+  gradsync_microbench  BASELINE.json configs[4]: flat buckets of 1 MB .. 2 GB, fp32 and bf16, A in {1, 4}:
+            accumulate + collective + clip + AdamW, time per optimizer step against max(HBM, NVLink @ 900 GB/s)
+  configs   configs[3] (GPT-2 medium bf16, AdamW, A=4, clip 1.0) measured the same way as the headline
   cpu_baseline  (N=1, rank 0) the torch port of the reference's path on the host cores, bounded sample
 """
 import argparse
-import ctypes
 import json
 import os
 import pathlib
@@ -29,35 +34,45 @@ import socket
 import sys
 import threading
 import time
-from typing import Any, Dict, List, Optional, Tuple
+from typing import Any, Callable, Dict, List, Optional, Tuple
 
 ROOT = pathlib.Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 
-PER_SLOT_BATCH = 128
-# dram__bytes_read.sum + dram__bytes_write.sum of one sgd_kernel launch in this workload, from the ncu --set full capture
-# profiles/r1_prof_bench_r1_summary.csv (134.19 MB read + 33.32 MB written; the rest of the 89 MB of writes is
-# still in L2 when the kernel ends)
-NCU_TRAFFIC_BYTES = 167.5e6
 METRIC, UNIT = "samples_per_sec", "samples/s"
+NVLINK_GBS = 900.0  # per direction per GPU
+# ncu --set full captures of the step kernels inside these workloads (dram__bytes_read.sum + dram__bytes_write.sum
+# per launch); None until a capture of THIS round's binary is committed under profiles/
+NCU_TRAFFIC: Dict[str, Dict[str, Any]] = {}
+try:
+    NCU_TRAFFIC = json.loads((ROOT / "profiles" / "ncu_traffic.json").read_text())
+except Exception:
+    pass
 
 
-def parse() -> argparse.Namespace:
+def parse(argv: Optional[List[str]] = None) -> argparse.Namespace:
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", choices=["ours", "reference", "torch"], default="ours",
-                    help="ours: this repo; reference: the reference's CPU path; torch: the reference's path on the GPUs "
-                         "(torch DDP on NCCL + torch.optim), the number to beat, for comparison only")
+                    help="ours: this repo; reference: the reference's CPU path (N gloo ranks); torch: the reference's path on "
+                         "the GPUs (torch DDP on NCCL + torch.optim), the number to beat, for comparison only")
+    ap.add_argument("--workload", default="resnet50", choices=["mnist", "cifar_resnet18", "resnet50", "gpt2_medium"],
+                    help="resnet50 = BASELINE.json configs[2] (the default the driver runs)")
+    ap.add_argument("--per-slot-batch", type=int, default=0, help="override the workload's per-slot batch (tests)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-microbench", action="store_true")
-    ap.add_argument("--micro-mb", type=int, default=1024)
-    ap.add_argument("--micro-only", action="store_true", help="run only the grad-sync microbench (both step variants) and print it")
-    ap.add_argument("--micro-bucket-mb", type=int, nargs="*", default=[0], help="bucket caps to try with --micro-only (0 = adaptive)")
-    ap.add_argument("--workload", default="cifar_resnet18", choices=["mnist", "cifar_resnet18", "resnet50", "gpt2_medium"],
-                    help="cifar_resnet18 = BASELINE.json configs[1] (the default the driver runs); the others are configs[2]/[3]")
-    return ap.parse_args()
+    ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the configs[3] (GPT-2 medium) sub-measurement")
+    ap.add_argument("--parity-cases", nargs="*", default=["cifar_resnet18", "resnet50", "gpt2_medium"])
+    ap.add_argument("--parity-steps", type=int, default=10)
+    ap.add_argument("--micro-mb", type=int, nargs="*", default=[1, 4, 16, 64, 256, 1024, 2048])
+    ap.add_argument("--micro-only", action="store_true", help="run only the grad-sync microbench and print it")
+    ap.add_argument("--micro-bucket-mb", type=int, default=0, help="bucket cap for the microbench (0 = one bucket per flat set)")
+    ap.add_argument("--micro-steps", type=int, default=10)
+    ap.add_argument("--cpu-budget-s", type=float, default=20.0)
+    return ap.parse_args(argv)
 
 
 def measured_peaks() -> Tuple[float, str]:
@@ -126,61 +141,161 @@ class ClockSampler:
                 "samples": len(s)}
 
 
+# ---- device plumbing (CUDA; the CPU test suite swaps in host stand-ins to exercise this file's control flow) -------
+class _Cuda:
+    """The few torch.cuda calls bench.py makes.  tests/test_bench_host.py replaces this object with a host-memory
+    stand-in (together with tests/fake_dgs.py for the C ABI) so that the driver's command cannot rot unnoticed;
+    the product and every reported number use this class."""
+
+    emulated = False
+    backend = "nccl"
+
+    def available(self) -> bool:
+        import torch
+
+        return torch.cuda.is_available()
+
+    def device(self, local_rank: int) -> Any:
+        import torch
+
+        torch.cuda.set_device(local_rank)
+        return torch.device("cuda", local_rank)
+
+    def sync(self) -> None:
+        import torch
+
+        torch.cuda.synchronize()
+
+    def event(self) -> Any:
+        import torch
+
+        return torch.cuda.Event(enable_timing=True)
+
+    def stream(self) -> Any:
+        import torch
+
+        return torch.cuda.current_stream()
+
+    def pin(self, t: Any) -> Any:
+        return t.pin_memory()
+
+    def empty_cache(self) -> None:
+        import torch
+
+        torch.cuda.empty_cache()
+
+
+DEV: Any = _Cuda()
+
+
+def _workload(args: argparse.Namespace, name: Optional[str] = None) -> Any:
+    from workloads.trials import WORKLOADS
+
+    cls = WORKLOADS[name or args.workload]
+    if args.per_slot_batch and (name is None or name == args.workload):
+        cls = type(cls.__name__, (cls,), {"PER_SLOT_BATCH": args.per_slot_batch})
+    return cls
+
+
 # ---- reference arm / cpu baseline -----------------------------------------------------------------
-def run_cpu_port(steps: int, warmup: int, budget_s: float, workload: str = "cifar_resnet18") -> Dict[str, Any]:
-    """The reference's per-batch path as it runs on CPU (oracle/torch_port.py), all host threads."""
+def run_cpu_port(trial_cls: Any, steps: int, warmup: int, budget_s: float, world: int = 1, rank: int = 0,
+                 threads: Optional[int] = None) -> Dict[str, Any]:
+    """The reference's per-batch path as it runs on CPU (oracle/torch_port.py; with world > 1: torch DDP over gloo,
+    the process group the reference creates without GPUs, harness/determined/pytorch/_pytorch_trial.py:296-300)."""
     import torch
 
     from oracle import torch_port
-    from workloads.trials import WORKLOADS
+    from workloads.parity import DdpRefContext
 
-    CifarResNetTrial = WORKLOADS[workload]
-    PER_SLOT_BATCH = CifarResNetTrial.PER_SLOT_BATCH
-
+    batch = trial_cls.PER_SLOT_BATCH
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
-    torch.set_num_threads(cores)
+    threads = threads or max(cores // world, 1)
+    torch.set_num_threads(threads)
     torch.manual_seed(17)
-    ctx = torch_port.RefContext(aggregation_frequency=CifarResNetTrial.AGG, device="cpu")
-    trial = CifarResNetTrial(ctx)
-    gen = torch.Generator().manual_seed(1234)
-    batches = [CifarResNetTrial.synthetic_batch(PER_SLOT_BATCH, gen) for _ in range(4)]
+    ctx = DdpRefContext(world, aggregation_frequency=trial_cls.AGG, device="cpu")
+    trial = trial_cls(ctx)
+    gen = torch.Generator().manual_seed(1234 + rank)
+    batches = [trial_cls.synthetic_batch(batch, gen) for _ in range(4)]
+    agg = trial_cls.AGG
     idx = 0
-    for _ in range(max(warmup, 1)):
+
+    def agree(x: float, op: str = "max") -> float:
+        if world == 1:
+            return x
+        import torch.distributed as dist
+
+        t = torch.tensor([x], dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX if op == "max" else dist.ReduceOp.MIN)
+        return float(t)
+
+    one = 0.0
+    for _ in range(max(warmup, 1) * agg):
         t0 = time.perf_counter()
         torch_port.train_batch_like_reference(ctx, trial, batches[idx % 4], idx)
         idx += 1
         one = time.perf_counter() - t0
-    # bounded sample: as many of the requested steps as fit the budget
-    n = max(1, min(steps, int(budget_s / max(one, 1e-3))))
+    # bounded sample: as many of the requested steps as fit the budget (whole aggregation windows; all ranks agree)
+    n = max(agg, min(steps, int(budget_s / max(agree(one), 1e-3))) // agg * agg)
+    n = int(agree(float(n), "min"))
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.barrier()
     t0 = time.perf_counter()
     for _ in range(n):
         torch_port.train_batch_like_reference(ctx, trial, batches[idx % 4], idx)
         idx += 1
-    dt = time.perf_counter() - t0
-    return {"value": n * PER_SLOT_BATCH / dt, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{n} train_batch steps of {CifarResNetTrial.NAME}, batch {PER_SLOT_BATCH}, torch {torch.__version__} CPU, "
-                      f"{cores} threads", "ms_per_step": dt / n * 1e3, "steps": n}
+    if world > 1:
+        dist.barrier()
+    dt = agree(time.perf_counter() - t0)
+    return {"value": n * batch * world / dt, "unit": UNIT, "cores": cores, "threads_per_rank": threads, "ranks": world, "kind": "port",
+            "sample": f"{n} train_batch steps of {trial_cls.NAME}, per-slot batch {batch}, {world} rank(s) x {threads} threads"
+                      f"{' over gloo DDP' if world > 1 else ''}, torch {torch.__version__} CPU",
+            "ms_per_step": dt / n * 1e3, "steps": n}
+
+
+def _reference_rank(rank: int, world: int, port: int, argv: List[str]) -> None:
+    """One gloo rank of the reference arm (spawned when bench.py itself was not started under torchrun)."""
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    run_reference(parse(argv))
 
 
 def run_reference(args: argparse.Namespace) -> None:
-    if int(os.environ.get("RANK", "0")) != 0:
-        return  # the CPU path is timed once, on rank 0
-    from workloads.trials import WORKLOADS
+    """`--impl reference`: the reference's CPU path for the same config -- N processes over gloo (torch DDP), the
+    GPU arm's per-slot batch, OMP threads = floor(cores / N) -- a bounded sample on the host cores."""
+    import torch
 
-    W = WORKLOADS[args.workload]
-    PER_SLOT_BATCH = W.PER_SLOT_BATCH
-    r = run_cpu_port(args.steps, args.warmup, budget_s=150.0, workload=args.workload)
-    line = {
-        "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": r["steps"],
-        "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": W.DTYPE, "data": "synthetic",
-        "config": {"workload": W.NAME, "per_slot_batch": PER_SLOT_BATCH, "global_batch": PER_SLOT_BATCH,
-                   "optimizer": W.OPTIMIZER, "aggregation_frequency": W.AGG, "parallelism": "cpu, 1 process"},
-        "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
-        "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
-    }
-    print(json.dumps(line), flush=True)
+    W = _workload(args)
+    world_env = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.gpus > 1 and world_env == 1:
+        import torch.multiprocessing as mp
+
+        mp.spawn(_reference_rank, args=(args.gpus, _free_port(), sys.argv[1:]), nprocs=args.gpus, join=True)
+        return
+    rank, world = int(os.environ.get("RANK", "0")), world_env
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("gloo")
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    r = run_cpu_port(W, args.steps, args.warmup, budget_s=120.0, world=world, rank=rank, threads=max(cores // world, 1))
+    if rank == 0:
+        line = {
+            "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": r["steps"],
+            "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": W.DTYPE, "data": "synthetic",
+            "config": {"workload": W.NAME, "per_slot_batch": W.PER_SLOT_BATCH, "global_batch": W.PER_SLOT_BATCH * world,
+                       "optimizer": W.OPTIMIZER, "aggregation_frequency": W.AGG,
+                       "parallelism": f"cpu, {world} gloo rank(s) x {r['threads_per_rank']} threads, torch DDP" if world > 1
+                       else f"cpu, 1 process x {r['threads_per_rank']} threads"},
+            "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample", "ranks", "threads_per_rank")},
+            "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
 
 
 # ---- our arm ------------------------------------------------------------------------------------------
@@ -190,30 +305,54 @@ def _free_port() -> int:
         return s.getsockname()[1]
 
 
-def gradsync_microbench(ctx: Any, mb: int, steps: int, peak_gbs: float, sharded: bool = False, bucket_mb: int = 0) -> Dict[str, Any]:
-    """configs[4]: one flat fp32 bucket through the path: flatten*scale -> allreduce -> L2 norm -> clip+AdamW."""
+def _max_over_ranks(dist: Any, device: Any, vals: List[float]) -> List[float]:
+    if dist is None:
+        return vals
+    import torch
+
+    t = torch.tensor(vals, device=device, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return [float(x) for x in t.tolist()]
+
+
+MICRO_BYTES = {  # algorithmic HBM bytes per element per optimizer step, DESIGN.md section 3 (AdamW + clip)
+    ("f32", 1): 8 + 4 + 28, ("f32", 4): 8 + 12 + 12 + 12 + 4 + 28, ("bf16", 1): 4 + 2 + 14, ("bf16", 4): 6 + 10 + 10 + 8 + 2 + 14,
+}
+
+
+def gradsync_microbench(ctx: Any, dist: Any, mb: int, dtype: str, agg: int, steps: int, peak_gbs: float, bucket_mb: int = 0,
+                        route: Optional[str] = None) -> Dict[str, Any]:
+    """configs[4]: one flat parameter set of `mb` MiB through the whole path per optimizer step: `agg` micro-batches of
+    flatten/accumulate, scale 1/(N*A) + cast, bucket collective, global L2 norm, clip + AdamW."""
     import torch
 
     from determined_clone_b200 import pytorch
 
-    pieces = 64  # the flat bucket is made of 64 equal tensors, as a model's would be of many
-    n_piece = mb * (1 << 20) // 4 // pieces
+    tdt = torch.float32 if dtype == "f32" else torch.bfloat16
+    isz = 4 if dtype == "f32" else 2
+    pieces = 64 if mb >= 4 else 8  # the flat set is made of equal tensors, as a model's would be of many
+    n_piece = mb * (1 << 20) // isz // pieces
     n = n_piece * pieces
     world = ctx.distributed.size
-    params = [torch.nn.Parameter(torch.randn(n_piece, device=ctx.device) * 0.02) for _ in range(pieces)]
+    dev = ctx.device
+    params = [torch.nn.Parameter((torch.randn(n_piece, device=dev) * 0.02).to(tdt)) for _ in range(pieces)]
     opt = torch.optim.AdamW(params, lr=3e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
-    eng = pytorch.GradSyncEngine(opt, ctx.device, ctx._get_comm(), aggregation_frequency=1, average_aggregated_gradients=True,
-                                 sharded_step=sharded, bucket_bytes=bucket_mb << 20)
-    grads = [[torch.randn(n_piece, device=ctx.device) * 1e-2 for _ in range(pieces)] for _ in range(2)]
+    kwargs: Dict[str, Any] = {}
+    if route is not None:
+        kwargs["route"] = route
+    eng = pytorch.GradSyncEngine(opt, dev, ctx._get_comm(), aggregation_frequency=agg, average_aggregated_gradients=True,
+                                 bucket_bytes=(bucket_mb << 20) if bucket_mb else n * isz + 1, **kwargs)
+    grads = [[(torch.randn(n_piece, device=dev) * 1e-2).to(tdt) for _ in range(pieces)] for _ in range(2)]
     clip = pytorch._gradsync.ClipRequest()
     clip.max_norm = 1.0
-    st = torch.cuda.current_stream()
+    st = DEV.stream()
 
     def step(i: int) -> None:
-        eng.begin_pass(final=True)
-        for p, g in zip(params, grads[i % 2]):
-            p.grad = g  # what autograd leaves behind when backward produces this gradient
-        eng.end_pass()
+        for m in range(agg):
+            eng.begin_pass(final=(m == agg - 1))
+            for p, g in zip(params, grads[(i + m) % 2]):
+                p.grad = g  # what autograd leaves behind when backward produces this gradient
+            eng.end_pass()
         present = eng.finish_window()
         eng.total_norm()
         eng.fused_step(present, clip)
@@ -221,55 +360,273 @@ def gradsync_microbench(ctx: Any, mb: int, steps: int, peak_gbs: float, sharded:
 
     for i in range(3):
         step(i)
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    DEV.sync()
+    if dist is not None:
+        dist.barrier()
+    e0, e1 = DEV.event(), DEV.event()
     e0.record(st)
     for i in range(steps):
         step(i)
     e1.record(st)
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / steps
-    if world > 1:
-        import torch.distributed as dist
-
-        t = torch.tensor([ms], device=ctx.device)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t)
-    hbm_bytes = (8 + 4 + 28) * n  # flatten (read g, write wire) + norm (read wire) + AdamW (read g,p,m,v; write p,m,v)
+    DEV.sync()
+    ms = _max_over_ranks(dist, dev, [e0.elapsed_time(e1) / steps])[0]
+    hbm_bytes = MICRO_BYTES[(dtype, agg)] * n
     t_hbm = hbm_bytes / (peak_gbs * 1e9)
-    t_nvl = (2 * (world - 1) / world * 4 * n) / 770e9 if world > 1 else 0.0  # measured peer bandwidth per direction
+    t_nvl = (2 * (world - 1) / world * isz * n) / (NVLINK_GBS * 1e9) if world > 1 else 0.0
+    out = {"mib": mb, "dtype": dtype, "aggregation_frequency": agg, "route": eng.route_name(), "us_per_step": ms * 1e3,
+           "roofline_us": max(t_hbm, t_nvl) * 1e6, "frac": max(t_hbm, t_nvl) / (ms * 1e-3) if ms > 0 else None,
+           "bound": "nvlink" if t_nvl > t_hbm else "hbm"}
     eng.close()
-    return {"bucket_mib": mb, "dtype": "f32", "optimizer": "adamw", "aggregation_frequency": 1, "clip": 1.0, "sharded_step": eng.sharded,
-            "us_per_step": ms * 1e3, "hbm_bytes_per_step": hbm_bytes, "roofline_us": max(t_hbm, t_nvl) * 1e6,
-            "frac_of_roofline": max(t_hbm, t_nvl) / (ms * 1e-3), "bound": "nvlink" if t_nvl > t_hbm else "hbm"}
+    del eng, opt, params, grads
+    return out
 
 
-def run_ours(args: argparse.Namespace) -> None:
+def microbench_sweep(ctx: Any, dist: Any, args: argparse.Namespace, peak: float) -> Dict[str, Any]:
+    rows = []
+    for dtype in ("f32", "bf16"):
+        for agg in (1, 4):
+            for mb in args.micro_mb:
+                rows.append(gradsync_microbench(ctx, dist, mb, dtype, agg, args.micro_steps, peak, bucket_mb=args.micro_bucket_mb))
+                DEV.empty_cache()
+    head = [r for r in rows if r["dtype"] == "f32" and r["aggregation_frequency"] == 1]
+    big = max(head, key=lambda r: r["mib"]) if head else None
+    at_1g = next((r for r in head if r["mib"] == 1024), big)
+    return {"optimizer": "adamw + clip_grad_norm_ 1.0", "nvlink_gbs_per_direction": NVLINK_GBS, "hbm_gbs": peak,
+            "bytes_per_element": {f"{d}_A{a}": v for (d, a), v in MICRO_BYTES.items()},
+            "headline": at_1g, "rows": rows}
+
+
+class _StepTimer:
+    """Wraps ctx.step_optimizer with CUDA events on boundary batches: exposed grad-sync tail per optimizer step."""
+
+    def __init__(self, ctx: Any, stream: Any) -> None:
+        self.ctx, self.stream, self.ev, self.orig = ctx, stream, [], ctx.step_optimizer
+
+    def __enter__(self) -> "_StepTimer":
+        def timed(*a: Any, **k: Any) -> None:
+            if not self.ctx._should_communicate_and_update():
+                return self.orig(*a, **k)  # not an optimizer step: nothing to time
+            a0, a1 = DEV.event(), DEV.event()
+            a0.record(self.stream)
+            self.orig(*a, **k)
+            a1.record(self.stream)
+            self.ev.append((a0, a1))
+
+        self.ctx.step_optimizer = timed  # type: ignore
+        return self
+
+    def __exit__(self, *_: Any) -> None:
+        self.ctx.step_optimizer = self.orig  # type: ignore
+
+    def median_us(self) -> Optional[float]:
+        DEV.sync()
+        tails = sorted(a.elapsed_time(b) for a, b in self.ev)
+        return tails[len(tails) // 2] * 1e3 if tails else None
+
+
+def measure_workload(args: argparse.Namespace, W: Any, dctx: Any, dist: Any, device: Any, rank: int, world: int, local_rank: int,
+                     steps: int, warmup: int, with_e2e: bool) -> Dict[str, Any]:
+    """value / roofline / grad-sync tail (/ e2e) of one workload.  `steps` and `warmup` count train_batch calls."""
+    import torch
+
+    from determined_clone_b200 import _lib, pytorch
+
+    batch, agg = W.PER_SLOT_BATCH, W.AGG
+    steps = max(agg, steps // agg * agg)
+    warmup = max(agg, (warmup + agg - 1) // agg * agg)
+    pytorch._PyTorchTrialController.pre_execute_hook(17)
+    ctx = pytorch.PyTorchTrialContext(distributed=dctx, hparams={"global_batch_size": batch * world}, slots_per_trial=world,
+                                      aggregation_frequency=agg, trial_seed=17, device=device)
+
+    class BenchTrial(W, pytorch.PyTorchTrial):  # a real PyTorchTrial: the controller below is the public entry point
+        loader: Any = None
+
+        def build_training_data_loader(self) -> Any:
+            return self.loader
+
+        def build_validation_data_loader(self) -> Any:
+            return None
+
+    ctx.experimental.disable_dataset_reproducibility_checks()  # the loader below is a plain iterable of pinned batches
+    trial = BenchTrial(ctx)
+    eng = ctx._engines[trial.optimizer]
+    p_total = sum(fs.total for fs in eng.sets)
+    gen = torch.Generator().manual_seed(1234 + rank)
+    host_batches = [tuple(DEV.pin(t) for t in W.synthetic_batch(batch, gen)) for _ in range(8)]
+    dev_batches = [tuple(t.to(device) for t in b) for b in host_batches]
+    stream = DEV.stream()
+
+    def one_step(i: int) -> Any:
+        ctx._current_batch_idx = i
+        return trial.train_batch(dev_batches[i % len(dev_batches)], 0, i)
+
+    def barrier() -> None:
+        if dist is not None:
+            dist.barrier()
+        DEV.sync()
+
+    # ---- device-timed region: inputs resident in HBM ----------------------------------------------
+    for i in range(warmup):
+        one_step(i)
+    barrier()
+    eng.enable_step_timing(True)
+    launches0 = _lib.calls.dgs_launch_count()
+    e0, e1 = DEV.event(), DEV.event()
+    with ClockSampler(local_rank) as clocks:
+        e0.record(stream)
+        for i in range(warmup, warmup + steps):
+            one_step(i)
+        e1.record(stream)
+        barrier()
+    launches = _lib.calls.dgs_launch_count() - launches0
+    ms_total = e0.elapsed_time(e1)
+    step_kernel_ms = eng.step_timings_ms()
+    eng.enable_step_timing(False)
+    ms_total = _max_over_ranks(dist, device, [ms_total])[0]
+    if dist is not None:
+        lt = torch.tensor([launches], device=device, dtype=torch.int64)
+        dist.all_reduce(lt)
+        launches = int(lt)
+    value = steps * batch * world / (ms_total * 1e-3)
+
+    # ---- exposed grad-sync tail: from the end of backward's last kernel to the end of the step kernel ----
+    done = warmup + steps
+    with _StepTimer(ctx, stream) as tail:
+        for i in range(8 * agg):
+            one_step(done + i)
+        tail_us = tail.median_us()
+    done += 8 * agg
+
+    # ---- roofline of the dominant kernel of the path (fused optimizer step) --------------------------------
+    peak, peak_src = measured_peaks()
+    k_ms = sorted(step_kernel_ms)[len(step_kernel_ms) // 2] if step_kernel_ms else None
+    roofline = None
+    if k_ms:
+        bpe = W.STEP_BYTES_PER_ELEM
+        n_elem = eng.step_elements()
+        achieved = bpe * n_elem / (k_ms * 1e-3) / 1e9
+        cap = NCU_TRAFFIC.get(W.NAME, {})
+        roofline = {"bound": "hbm", "kernel": W.STEP_KERNEL, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                    "traffic": cap.get("dram_bytes_per_launch"), "traffic_source": cap.get("source"), "peak_source": peak_src,
+                    "elements": n_elem, "algorithmic_bytes_per_element": bpe, "algorithmic_bytes_per_launch": bpe * n_elem,
+                    "us_per_launch": k_ms * 1e3, "launches_timed": len(step_kernel_ms),
+                    "note": "median over the timed region of CUDA events recorded inside libdgs around each launch (dgs_timer_read)"}
+
+    out: Dict[str, Any] = {
+        "value": value, "ms_per_step": ms_total / steps, "steps": steps, "warmup": warmup, "gpu_launches": launches,
+        "clocks": clocks.summary(), "grad_sync_us_per_step": tail_us, "roofline": roofline, "route": eng.route_name(),
+        "config": {"workload": W.NAME, "per_slot_batch": batch, "global_batch": batch * world, "optimizer": W.OPTIMIZER,
+                   "aggregation_frequency": agg, "parallelism": f"dp{world}", "param_elements": p_total,
+                   "l2": "8 distinct input batches cycled; activations and the step kernel's working set exceed the 126 MB L2"},
+    }
+
+    # ---- end to end through the public API: host batches in, metrics out, every step ----------------------
+    if with_e2e:
+        class HostLoader:
+            def __iter__(self) -> Any:
+                i = 0
+                while True:
+                    yield host_batches[i % len(host_batches)]
+                    i += 1
+
+        trial.loader = HostLoader()
+        reports: List[Any] = []
+        base = (done + agg - 1) // agg * agg  # resume on an aggregation boundary
+        warm = pytorch._PyTorchTrialController(trial, ctx, max_length=base + 2 * agg, reporting_period=1, steps_completed=base)
+        warm.run()
+        ctl = pytorch._PyTorchTrialController(trial, ctx, max_length=base + 2 * agg + steps, reporting_period=1,
+                                              steps_completed=base + 2 * agg, on_report=lambda n, r: reports.append(r))
+        barrier()
+        t0 = time.perf_counter()
+        ctl.run()
+        barrier()
+        e2e_s = _max_over_ranks(dist, device, [time.perf_counter() - t0])[0]
+        h2d = sum(t.numel() * t.element_size() for t in host_batches[0])
+        d2h = 1 * 1 * 8 + 8 + 1 + 8  # per-batch mean (1x1 f64) + period mean (f64) + validity byte + int64 count
+        out["e2e"] = {"value": steps * batch * world / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                      "ms_per_step": e2e_s / steps * 1e3, "reports": len(reports) if rank == 0 else None,
+                      "api": "_PyTorchTrialController.run(), reporting_period=1, pinned host batches"}
+    ctx.close()
+    del trial, eng, ctx, dev_batches
+    DEV.empty_cache()
+    return out
+
+
+def run_parity(args: argparse.Namespace, dctx: Any, dist: Any, device: Any, rank: int, world: int) -> Dict[str, Any]:
+    """See the module docstring.  Returns {"n", "ok", "max_rel", "cases": [...]}."""
+    from determined_clone_b200 import core, pytorch
+    from workloads import parity as P
+
+    cases: List[Dict[str, Any]] = []
+
+    def reduce_max(v: List[float]) -> List[float]:
+        return _max_over_ranks(dist, device, v)
+
+    for name in args.parity_cases:
+        W = _workload(args, name)
+        for mode in ("free", "synced"):
+            pytorch._PyTorchTrialController.pre_execute_hook(17)
+            ctx = pytorch.PyTorchTrialContext(distributed=dctx, hparams={"global_batch_size": W.PER_SLOT_BATCH * world},
+                                              slots_per_trial=world, aggregation_frequency=W.AGG, trial_seed=17, device=device)
+            cases.append(P.live_parity(name, W, ctx, device, rank, world, steps=args.parity_steps, mode=mode, reduce_max=reduce_max))
+            DEV.empty_cache()
+    # the 2-slot fixtures recorded from the unmodified reference (real torch DDP over gloo), on ranks 0 and 1
+    if world >= 2 and not DEV.emulated:
+        sys.path.insert(0, str(ROOT / "tests"))
+        ports = [_free_port(), _free_port()] if rank == 0 else [0, 0]
+        ports = dctx.broadcast(ports)
+        failed = ""
+        if rank < 2:
+            from golden_io import SCENARIOS
+            from test_gpu_trial_parity import run_scenario
+
+            sub = core.DistributedContext(rank=rank, size=2, local_rank=rank, local_size=2, cross_rank=0, cross_size=1,
+                                          pub_port=ports[0], pull_port=ports[1])
+            try:
+                for name, sc in SCENARIOS.items():
+                    if sc["slots"] == 2:
+                        try:
+                            run_scenario(name, distributed=sub)
+                        except AssertionError as e:
+                            failed = f"{name}: {str(e)[:200]}"
+                            break
+            finally:
+                sub.close()
+        everyone = dctx.allgather(failed)
+        bad = [f for f in everyone if f]
+        cases.append({"case": "reference-recorded 2-slot fixtures (sgd_n2_a2, adamw_n2_a4_clip, adamw_bf16_n2_a2_clip) on ranks 0-1",
+                      "mode": "fixtures", "ok": not bad, "error": bad[0] if bad else None})
+    free = [c for c in cases if c.get("mode") == "free"]
+    return {"n": world, "ok": all(c["ok"] for c in cases), "max_rel": max((c["max_rel"] for c in free), default=None),
+            "against": "torch DDP (NCCL) + torch.optim on the same GPUs, same seeds and inputs (workloads/parity.py)", "cases": cases}
+
+
+def run_ours(args: argparse.Namespace) -> int:
     import torch
 
     from determined_clone_b200 import _build, _lib, core, pytorch
-    from workloads.trials import WORKLOADS
 
-    CifarResNetTrial = WORKLOADS[args.workload]  # the trial class of the selected workload
-    PER_SLOT_BATCH = CifarResNetTrial.PER_SLOT_BATCH
-    AGG = CifarResNetTrial.AGG
+    W = _workload(args)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
+    if not DEV.available():
         raise SystemExit("bench.py: no CUDA device; the grad-sync path has no CPU implementation (use --impl reference)")
-    torch.cuda.set_device(local_rank)
-    device = torch.device("cuda", local_rank)
+    device = DEV.device(local_rank)
     dist = None
     if world > 1:
         import torch.distributed as dist  # type: ignore
 
-        dist.init_process_group("nccl", device_id=device)
-    if rank == 0 and not _lib.LIB_PATH.exists():
-        _build.build()
-    if dist is not None:
-        dist.barrier()
-    _lib.load()
+        if DEV.emulated:
+            dist.init_process_group(DEV.backend)
+        else:
+            dist.init_process_group(DEV.backend, device_id=device)
+    if not DEV.emulated:
+        if rank == 0 and not _lib.LIB_PATH.exists():
+            _build.build()
+        if dist is not None:
+            dist.barrier()
+        _lib.load()
 
     # control plane for the trial: the reference's DistributedContext (ZeroMQ through the chief)
     if world > 1:
@@ -279,183 +636,58 @@ def run_ours(args: argparse.Namespace) -> None:
                                        pub_port=ports[0], pull_port=ports[1])
     else:
         dctx = core.DummyDistributedContext()
+    peak, _ = measured_peaks()
+    rc = 0
+    try:
+        if args.micro_only:
+            pytorch._PyTorchTrialController.pre_execute_hook(17)
+            ctx = pytorch.PyTorchTrialContext(distributed=dctx, hparams={"global_batch_size": world}, slots_per_trial=world, device=device)
+            sweep = microbench_sweep(ctx, dist, args, peak)
+            if rank == 0:
+                print(json.dumps({"n_gpus": world, "gradsync_microbench": sweep}), flush=True)
+            return 0
 
-    pytorch._PyTorchTrialController.pre_execute_hook(17)
-    ctx = pytorch.PyTorchTrialContext(distributed=dctx, hparams={"global_batch_size": PER_SLOT_BATCH * world}, slots_per_trial=world,
-                                      aggregation_frequency=AGG, trial_seed=17, device=device)
+        parity = None
+        if not args.no_parity:
+            parity = run_parity(args, dctx, dist, device, rank, world)
+            if not parity["ok"]:
+                rc = 3
 
-    class BenchTrial(CifarResNetTrial):
-        loader: Any = None
+        head = measure_workload(args, W, dctx, dist, device, rank, world, local_rank, args.steps, args.warmup, with_e2e=True)
 
-        def build_training_data_loader(self) -> Any:
-            return self.loader
+        extra: Dict[str, Any] = {}
+        if not args.no_extra and args.workload != "gpt2_medium":
+            G = _workload(args, "gpt2_medium")
+            extra[G.NAME] = measure_workload(args, G, dctx, dist, device, rank, world, local_rank, 8 * G.AGG, 2 * G.AGG, with_e2e=False)
+            extra[G.NAME]["unit"] = "sequences/s (4 x 1024 tokens per slot per micro-batch)"
 
-        def build_validation_data_loader(self) -> Any:
-            return None
+        micro = None
+        if not args.no_microbench:
+            pytorch._PyTorchTrialController.pre_execute_hook(17)
+            ctx = pytorch.PyTorchTrialContext(distributed=dctx, hparams={"global_batch_size": world}, slots_per_trial=world, device=device)
+            micro = microbench_sweep(ctx, dist, args, peak)
 
-    if args.micro_only:
-        peak, _ = measured_peaks()
-        out = []
-        for cap in args.micro_bucket_mb:
-            for sharded in ((False, True) if world > 1 else (False,)):
-                m = gradsync_microbench(ctx, args.micro_mb, 12, peak, sharded=sharded, bucket_mb=cap)
-                m["bucket_cap_mib"] = cap or "adaptive"
-                out.append(m)
-                torch.cuda.empty_cache()
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            r = run_cpu_port(W, steps=20, warmup=1, budget_s=args.cpu_budget_s)
+            cpu = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
+
         if rank == 0:
-            print(json.dumps({"n_gpus": world, "gradsync_microbench": out}), flush=True)
-        ctx.close()
+            line = {
+                "metric": METRIC, "value": head["value"], "unit": UNIT, "n_gpus": world, "steps": head["steps"], "warmup": head["warmup"],
+                "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": W.DTYPE, "data": "synthetic", "config": head["config"],
+                "roofline": head["roofline"], "cpu_baseline": cpu, "e2e": head.get("e2e"), "gpu_launches": head["gpu_launches"],
+                "clocks": head["clocks"], "grad_sync_us_per_step": head["grad_sync_us_per_step"], "route": head["route"],
+                "parity": parity, "gradsync_microbench": micro, "configs": extra,
+            }
+            print(json.dumps(line), flush=True)
+    finally:
         dctx.close()
         if dist is not None:
             dist.barrier()
             dist.destroy_process_group()
-        return
-
-    trial = BenchTrial(ctx)
-    eng = ctx._engines[trial.optimizer]
-    p_total = sum(fs.total for fs in eng.sets)
-
-    gen = torch.Generator().manual_seed(1234 + rank)
-    host_batches = [tuple(t.pin_memory() for t in CifarResNetTrial.synthetic_batch(PER_SLOT_BATCH, gen)) for _ in range(8)]
-    dev_batches = [tuple(t.to(device) for t in b) for b in host_batches]
-    stream = torch.cuda.current_stream()
-
-    def one_step(i: int) -> Any:
-        ctx._current_batch_idx = i
-        return trial.train_batch(dev_batches[i % len(dev_batches)], 0, i)
-
-    def barrier() -> None:
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    # ---- device-timed region: inputs resident in HBM ----------------------------------------------
-    for i in range(args.warmup):
-        one_step(i)
-    barrier()
-    eng.enable_step_timing(True)
-    launches0 = _lib.calls.dgs_launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local_rank) as clocks:
-        e0.record(stream)
-        for i in range(args.warmup, args.warmup + args.steps):
-            one_step(i)
-        e1.record(stream)
-        barrier()
-    launches = _lib.calls.dgs_launch_count() - launches0
-    ms_total = e0.elapsed_time(e1)
-    step_kernel_ms = eng.step_timings_ms()
-    eng.enable_step_timing(False)
-    if dist is not None:
-        t = torch.tensor([ms_total], device=device)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_total = float(t)
-        lt = torch.tensor([launches], device=device, dtype=torch.int64)
-        dist.all_reduce(lt)
-        launches = int(lt)
-    value = args.steps * PER_SLOT_BATCH * world / (ms_total * 1e-3)
-
-    # ---- exposed grad-sync tail: from the end of backward's last kernel to the end of the step kernel ----
-    tail_us = None
-    try:
-        ev = []
-        orig = ctx.step_optimizer
-
-        def timed_step_optimizer(*a: Any, **k: Any) -> None:
-            if not ctx._should_communicate_and_update():
-                return orig(*a, **k)  # not an optimizer step: nothing to time
-            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a0.record(stream)
-            orig(*a, **k)
-            a1.record(stream)
-            ev.append((a0, a1))
-
-        ctx.step_optimizer = timed_step_optimizer  # type: ignore
-        for i in range(2 * AGG + 8 - (8 % AGG if AGG > 1 else 0)):
-            one_step(args.warmup + args.steps + i)
-        torch.cuda.synchronize()
-        ctx.step_optimizer = orig  # type: ignore
-        tails = sorted(a.elapsed_time(b) for a, b in ev)
-        tail_us = tails[len(tails) // 2] * 1e3
-    except Exception:
-        tail_us = None
-
-    # ---- end to end through the public API: host batches in, metrics out, every step ----------------------
-    e2e_steps = args.steps
-
-    class HostLoader:
-        def __iter__(self) -> Any:
-            i = 0
-            while True:
-                yield host_batches[i % len(host_batches)]
-                i += 1
-
-    trial.loader = HostLoader()
-    reports: List[Any] = []
-    base = (args.warmup + args.steps + 4 * AGG + 16) // AGG * AGG  # resume on an aggregation boundary
-    warm = pytorch._PyTorchTrialController(trial, ctx, max_length=base + AGG, reporting_period=1, steps_completed=base)
-    warm.run()
-    ctl = pytorch._PyTorchTrialController(trial, ctx, max_length=base + AGG + e2e_steps, reporting_period=1, steps_completed=base + AGG,
-                                          on_report=lambda n, r: reports.append(r))
-    barrier()
-    t0 = time.perf_counter()
-    ctl.run()
-    barrier()
-    e2e_s = time.perf_counter() - t0
-    if dist is not None:
-        t = torch.tensor([e2e_s], device=device, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t)
-    h2d = sum(t.numel() * t.element_size() for t in host_batches[0])
-    d2h = 1 * 1 * 8 + 8 + 1 + 8  # per-batch mean (1x1 f64) + period mean (f64) + validity byte + int64 count
-    e2e = {"value": e2e_steps * PER_SLOT_BATCH * world / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-           "ms_per_step": e2e_s / e2e_steps * 1e3, "api": "_PyTorchTrialController.run(), reporting_period=1, pinned host batches"}
-
-    # ---- roofline of the dominant kernel of the path (fused SGD step) --------------------------------
-    peak, peak_src = measured_peaks()
-    k_ms = sorted(step_kernel_ms)[len(step_kernel_ms) // 2] if step_kernel_ms else None
-    bytes_per_elem = CifarResNetTrial.STEP_BYTES_PER_ELEM  # DESIGN.md, kernel table
-    roofline = None
-    if k_ms:
-        achieved = bytes_per_elem * p_total / (k_ms * 1e-3) / 1e9
-        roofline = {"bound": "hbm", "kernel": CifarResNetTrial.STEP_KERNEL, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                    "frac": achieved / peak, "traffic": NCU_TRAFFIC_BYTES if args.workload == "cifar_resnet18" else None, "peak_source": peak_src, "elements": p_total,
-                    "algorithmic_bytes_per_element": bytes_per_elem, "us_per_launch": k_ms * 1e3,
-                    "note": "median over the timed region of CUDA events recorded inside libdgs around each launch (dgs_timer_read); for "
-                            "models smaller than L2 the wire bucket just written by the flatten kernel is partly still cached"}
-
-    micro = None
-    if not args.no_microbench:
-        # one bucket = the whole buffer: the microbench has no backward pass for smaller buckets to overlap with
-        micro = gradsync_microbench(ctx, args.micro_mb, 12, peak, bucket_mb=args.micro_mb)
-        if world > 1:  # the opt-in reduce-scatter / sharded-step / all-gather variant of the same step
-            torch.cuda.empty_cache()
-            micro["sharded_variant"] = gradsync_microbench(ctx, args.micro_mb, 12, peak, sharded=True, bucket_mb=args.micro_mb)
-
-    cpu = None
-    if world == 1 and not args.no_cpu_baseline:
-        r = run_cpu_port(steps=20, warmup=1, budget_s=20.0, workload=args.workload)
-        cpu = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
-
-    if rank == 0:
-        line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": CifarResNetTrial.DTYPE,
-            "data": "synthetic",
-            "config": {"workload": CifarResNetTrial.NAME, "per_slot_batch": PER_SLOT_BATCH, "global_batch": PER_SLOT_BATCH * world,
-                       "optimizer": CifarResNetTrial.OPTIMIZER, "aggregation_frequency": AGG, "parallelism": f"dp{world}",
-                       "l2": "8 distinct input batches cycled; forward/backward activations between optimizer steps exceed L2",
-                       "param_elements": p_total},
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks.summary(),
-            "grad_sync_us_per_step": tail_us, "gradsync_microbench": micro,
-        }
-        print(json.dumps(line), flush=True)
-    ctx.close()
-    dctx.close()
-    if dist is not None:
-        dist.barrier()
-        dist.destroy_process_group()
+    return rc
 
 
 def run_torch_gpu(args: argparse.Namespace) -> None:
@@ -463,11 +695,10 @@ def run_torch_gpu(args: argparse.Namespace) -> None:
     the reference context.  Not part of the driver contract; prints a line with impl 'torch' for comparison."""
     import torch
 
-    from oracle import torch_port
-    from workloads.trials import WORKLOADS
+    from workloads.parity import DdpRefContext
 
-    CifarResNetTrial = WORKLOADS[args.workload]
-    PER_SLOT_BATCH = CifarResNetTrial.PER_SLOT_BATCH
+    W = _workload(args)
+    batch = W.PER_SLOT_BATCH
     rank, world, local_rank = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
     torch.cuda.set_device(local_rank)
     device = torch.device("cuda", local_rank)
@@ -477,19 +708,10 @@ def run_torch_gpu(args: argparse.Namespace) -> None:
 
         dist.init_process_group("nccl", device_id=device)
     torch.manual_seed(17)
-
-    class Ctx(torch_port.RefContext):
-        def wrap_model(self, model: Any) -> Any:
-            model = model.to(self.device)
-            if world > 1:
-                model = torch.nn.parallel.DistributedDataParallel(model)  # reference _pytorch_context.py:295-296
-            self.models.append(model)
-            return model
-
-    ctx = Ctx(aggregation_frequency=CifarResNetTrial.AGG, device=str(device))
-    trial = CifarResNetTrial(ctx)
+    ctx = DdpRefContext(world, aggregation_frequency=W.AGG, device=str(device))
+    trial = W(ctx)
     gen = torch.Generator().manual_seed(1234 + rank)
-    batches = [tuple(t.to(device) for t in CifarResNetTrial.synthetic_batch(PER_SLOT_BATCH, gen)) for _ in range(8)]
+    batches = [tuple(t.to(device) for t in W.synthetic_batch(batch, gen)) for _ in range(8)]
 
     def step(i: int) -> None:
         ctx._current_batch_idx = i
@@ -507,15 +729,11 @@ def run_torch_gpu(args: argparse.Namespace) -> None:
         step(i)
     e1.record()
     torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1)
-    if dist is not None:
-        t = torch.tensor([ms], device=device)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t)
+    ms = _max_over_ranks(dist, device, [e0.elapsed_time(e1)])[0]
     if rank == 0:
-        print(json.dumps({"impl": "torch", "metric": METRIC, "value": args.steps * PER_SLOT_BATCH * world / (ms * 1e-3), "unit": UNIT,
+        print(json.dumps({"impl": "torch", "metric": METRIC, "value": args.steps * batch * world / (ms * 1e-3), "unit": UNIT,
                           "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-                          "config": {"workload": CifarResNetTrial.NAME, "parallelism": f"torch DDP dp{world}"}}), flush=True)
+                          "config": {"workload": W.NAME, "parallelism": f"torch DDP dp{world}"}}), flush=True)
     if dist is not None:
         dist.destroy_process_group()
 
@@ -531,7 +749,7 @@ def main() -> None:
     elif args.impl == "torch":
         run_torch_gpu(args)
     else:
-        run_ours(args)
+        sys.exit(run_ours(args))
 
 
 if __name__ == "__main__":

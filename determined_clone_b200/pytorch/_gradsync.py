@@ -36,7 +36,6 @@ import torch
 from determined_clone_b200 import _lib, errors
 from determined_clone_b200.pytorch._comm import Comm
 
-_SKIP_ALLREDUCE = "allreduce" in __import__("os").environ.get("DGS_DEBUG_SKIP", "")  # measurement aid only
 ALIGN_ELEMS = 64  # 128 bytes of bf16, 256 bytes of fp32: every tensor starts vector-aligned
 FIRST_BUCKET_BYTES = 1 << 20
 # Bucket cap: NCCL's allreduce over NVSwitch needs large messages (measured at 8 x B200, gpurun_out/
@@ -450,7 +449,15 @@ class GradSyncEngine:
         n = sum(len(fs.tensors) for fs in self.sets)
         self._learn_tries += 1
         complete = len(self._order) == n and len(set(self._order)) == n
+        # The ranks must take the same branch below (one of them issues a broadcast): `complete` is rank-local --
+        # with a data-dependent graph one rank can miss a parameter that the others saw -- so agree on it first.
+        # Every rank gets here in the same backward pass (hooks are installed by the first begin_pass everywhere).
+        flag = torch.tensor([1 if complete else 0], dtype=torch.int64, device=self.device)
+        self.comm.allreduce(flag)  # type: ignore
+        self.comm.wait()  # type: ignore
+        complete = int(flag.item()) == self.world
         if not complete and self._learn_tries < 3:
+            self._order = []
             return
         for h in self._hooks:
             h.remove()
@@ -465,13 +472,14 @@ class GradSyncEngine:
         # layer's 1-D parameters completes last wherever it sits in the buffer); rank 0's order is adopted
         # by everyone so that the NCCL sequences cannot differ
         order = sorted(last, key=lambda k: last[k])
-        if len(order) == len(self._launch_order):
-            flat = torch.tensor([x for sb in order for x in sb], dtype=torch.int64, device=self.device)
-            self.comm.broadcast(flat, 0)  # type: ignore
-            self.comm.wait()  # type: ignore
-            got = flat.tolist()
-            # adopted at the next window boundary: this window may already be part-way through the old order
-            self._pending_order = [(got[i], got[i + 1]) for i in range(0, len(got), 2)]
+        # complete on every rank => every bucket appears in `order` on every rank: the broadcast below is collective
+        assert len(order) == len(self._launch_order)
+        flat = torch.tensor([x for sb in order for x in sb], dtype=torch.int64, device=self.device)
+        self.comm.broadcast(flat, 0)  # type: ignore
+        self.comm.wait()  # type: ignore
+        got = flat.tolist()
+        # adopted at the next window boundary: this window may already be part-way through the old order
+        self._pending_order = [(got[i], got[i + 1]) for i in range(0, len(got), 2)]
         for (si, bi), pos in last.items():
             _, ti = self._order[pos]
             param = self.sets[si].tensors[ti].param
@@ -576,7 +584,7 @@ class GradSyncEngine:
                 return
             itemsize = fs.wire.element_size()
             base, span = fs.wire.data_ptr() + b.begin * itemsize, b.end - b.begin
-            if self.comm is not None and not b.reduced and not _SKIP_ALLREDUCE:
+            if self.comm is not None and not b.reduced:
                 if self.sharded:
                     self.comm.reduce_scatter_raw(base, span // self.world, fs.wire_code)
                 else:
@@ -784,6 +792,18 @@ class GradSyncEngine:
         return runs
 
     # -- measurement: CUDA events around the optimizer kernel, on the stream it is launched on ----------
+    def route_name(self) -> str:
+        """Which exchange this engine performs per optimizer step (reported by bench.py)."""
+        if self.comm is None:
+            return "single-gpu (no exchange)"
+        if self.sharded:
+            return "nccl reduce-scatter + sharded step + all-gather"
+        return "nccl allreduce"
+
+    def step_elements(self) -> int:
+        """Elements one optimizer step of this rank covers (all flat sets; 1/N of them with the sharded step)."""
+        return sum(fs.total for fs in self.sets) // (self.world if self.sharded else 1)
+
     def enable_step_timing(self, on: bool = True) -> None:
         """CUDA events recorded inside libdgs immediately around every optimizer-kernel launch."""
         _lib.calls.dgs_timer_enable(1 if on else 0)

@@ -27,9 +27,6 @@ from determined_clone_b200.pytorch._comm import Comm
 from determined_clone_b200.pytorch._reducer import _PyTorchReducerContext
 
 logger = logging.getLogger("determined.pytorch")
-# measurement aid only (tools/, never set in tests or bench): DGS_DEBUG_SKIP=buffers,allreduce switches a
-# collective off to see what it costs
-_DEBUG_SKIP = set(filter(None, __import__("os").environ.get("DGS_DEBUG_SKIP", "").split(",")))
 
 
 class PyTorchExperimentalContext:
@@ -104,7 +101,7 @@ class _BufferSync:
         self.comm.wait()
 
     def _pre_forward(self, module: nn.Module, args: Any) -> None:
-        if module.training and torch.is_grad_enabled() and "buffers" not in _DEBUG_SKIP:
+        if module.training and torch.is_grad_enabled():
             self.sync()
 
 

@@ -21,6 +21,7 @@ import os
 import pathlib
 import pickle
 import random
+import sys
 import tempfile
 import time
 import uuid
@@ -175,7 +176,8 @@ class _PyTorchTrialController:
         self.validation_reports: List[Dict[str, Any]] = []
         self.checkpoints: List[str] = []  # uuids written in this run, oldest first
         self._best_validation: Optional[float] = None
-        self.callbacks: Dict[str, Any] = (trial_inst.build_callbacks() if trial_inst is not None else None) or {}
+        # duck-typed trials (anything with train_batch / build_training_data_loader) get PyTorchTrial's defaults
+        self.callbacks: Dict[str, Any] = getattr(trial_inst, "build_callbacks", dict)() or {}
         for name, cb in self.callbacks.items():
             if not isinstance(cb, PyTorchCallback):
                 raise TypeError(f"build_callbacks() must map names to PyTorchCallback objects; '{name}' is a {type(cb).__name__}")
@@ -200,19 +202,31 @@ class _PyTorchTrialController:
         torch.random.manual_seed(seed)
 
     def _set_data_loaders(self) -> None:
+        """Reference _pytorch_trial.py:446-506: a det DataLoader is adapted (repeat / shard / skip) here, anything
+        else is taken as is once the trial has opted out of the reproducibility checks; the epoch length is the
+        chief's len() of the loader it will iterate (per rank already), sys.maxsize when it has none."""
+        from determined_clone_b200.pytorch._data import _dataset_repro_warning
+
         d = self.context.distributed
+        checked = not self.context.experimental._data_repro_checks_disabled
         train = self.trial.build_training_data_loader()
-        self.context._epoch_len = (len(train) - d.rank + d.size - 1) // d.size if hasattr(train, "__len__") else None
         if isinstance(train, DataLoader):
             self.training_loader = train.get_data_loader(repeat=True, skip=self.batches_trained, num_replicas=d.size, rank=d.rank)
         else:
+            if checked:
+                raise RuntimeError(_dataset_repro_warning("build_training_data_loader", train))
             self.training_loader = train
-        if self.context._epoch_len is not None and d.size > 1:
-            self.context._epoch_len = d.broadcast(self.context._epoch_len)  # ranks must agree on epoch boundaries
+        try:
+            epoch_len = len(self.training_loader)
+        except TypeError:
+            epoch_len = sys.maxsize
+        self.context._epoch_len = d.broadcast(epoch_len) if d.size > 1 else epoch_len  # ranks must agree on epoch boundaries
         val = self.trial.build_validation_data_loader()
         if isinstance(val, DataLoader):
             self.validation_loader = val.get_data_loader(repeat=False, skip=0, num_replicas=d.size, rank=d.rank)
         else:
+            if val is not None and checked:
+                raise RuntimeError(_dataset_repro_warning("build_validation_data_loader", val))
             self.validation_loader = val
 
     # ---- training loop ------------------------------------------------------------------------------
