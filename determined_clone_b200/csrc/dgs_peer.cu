@@ -1,0 +1,299 @@
+// Peer-memory exchange over NVLink 5 / NVSwitch: the bucket "allreduce" of the data-parallel path done by this
+// library's own kernels on peer-mapped buffers instead of ncclAllReduce.
+//
+// Takes over DDP's bucket allreduce on the boundary backward pass (reference
+// harness/determined/pytorch/_pytorch_context.py:295-296 wraps the model in DistributedDataParallel, :813-816 is the
+// backward pass whose hooks all-reduce the buckets) for up to DGS_PEER_MAX ranks on one NVSwitch domain:
+//
+//   backward, per bucket   dgs_flatten_push      grads (+ fp32 accumulator) * 1/(N*A) -> cast -> written straight into
+//                                                the OWNER rank's wire buffer (row = source rank): flatten, scale, cast
+//                                                and the reduce-scatter transfer are one kernel, posted stores over NVLink
+//   step_optimizer         dgs_peer_barrier      every rank's pushes have landed
+//                          dgs_peer_reduce       owner sums its N rows in rank order (deterministic; fp32 accumulate,
+//                                                one rounding) and emits the per-CTA sums of squares of the L2 norm
+//                          dgs_peer_norm_exchange  8-byte all-to-all of the ranks' sums of squares + barrier -> norm
+//                          dgs_step_*_push       (dgs_step.cu) clip + optimizer step on the owner's 1/N slice, new
+//                                                parameters stored to every rank's parameter buffer (the all-gather)
+//                          dgs_peer_barrier      every rank's parameter stores have landed
+//
+// Every rank maps the others' buffers with CUDA IPC (cudaIpcGetMemHandle / cudaIpcOpenMemHandle); the 64-byte handles
+// travel through the caller's control plane.  Cross-GPU ordering uses flags in a small peer-mapped sync block per rank:
+// st.release.sys / ld.acquire.sys with a monotonically increasing epoch per slot, so nothing is ever reset.  A wait
+// that exceeds its timeout does not trap (that would be a GPU fault): it records an error code in a host-mapped word,
+// stops waiting, and every later wait returns at once, so the stream drains and the host can raise.
+#include "dgs_common.cuh"
+
+#include <cuda.h>
+
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+
+namespace dgs {
+namespace {
+
+constexpr int kThreads = 256;
+
+// ---- IPC bookkeeping ----------------------------------------------------------------------------------------------
+std::mutex g_ipc_mutex;
+std::map<std::string, void*> g_opened;  // handle bytes -> mapped base pointer (one open per allocation per process)
+int* g_err_host = nullptr;              // host-mapped error word, shared by every peer group of the process
+int* g_err_dev = nullptr;
+
+int ensure_error_word() {
+  if (g_err_host != nullptr) return DGS_OK;
+  DGS_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&g_err_host), sizeof(int), cudaHostAllocMapped | cudaHostAllocPortable));
+  *g_err_host = 0;
+  DGS_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void**>(&g_err_dev), g_err_host, 0));
+  return DGS_OK;
+}
+
+// ---- device-side flag protocol ----------------------------------------------------------------------------------
+__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+struct SyncPtrs {
+  unsigned int* flags[DGS_PEER_MAX];  // flags[r] = rank r's sync block (peer-mapped; [me] is local)
+};
+
+// sync block layout (uint32 words): flag[slot][src] at slot * DGS_PEER_MAX + src, then doubles for the norm exchange
+constexpr int kFlagWords = DGS_PEER_SLOTS * DGS_PEER_MAX;
+__device__ __forceinline__ double* sumsq_slots(unsigned int* block, unsigned int epoch) {
+  // double-buffered by epoch parity: a fast rank may write epoch e+1 while a slow one still reads epoch e
+  return reinterpret_cast<double*>(block + kFlagWords) + (epoch & 1u) * DGS_PEER_MAX;
+}
+
+// thread `t` < nranks: tell rank t that this rank reached `epoch` on `slot`, then wait for rank t's flag here.
+// Epoch comparison is wrap-safe (signed difference).
+__device__ __forceinline__ void signal_and_wait(const SyncPtrs& S, int slot, unsigned int epoch, int nranks, int rank,
+                                                unsigned long long timeout_ns, int* err) {
+  const int t = threadIdx.x;
+  if (t < nranks) {
+    __threadfence_system();  // everything this rank wrote before (earlier kernels included) is visible system-wide first
+    st_release_sys(S.flags[t] + slot * DGS_PEER_MAX + rank, epoch);
+    const unsigned int* mine = S.flags[rank] + slot * DGS_PEER_MAX + t;
+    if (*reinterpret_cast<volatile int*>(err) == 0) {
+      const unsigned long long t0 = globaltimer_ns();
+      while ((int)(ld_acquire_sys(mine) - epoch) < 0) {
+        if (globaltimer_ns() - t0 > timeout_ns) {
+          *reinterpret_cast<volatile int*>(err) = 1000 + slot * 16 + t;  // which slot, which peer never arrived
+          __threadfence_system();
+          break;
+        }
+        __nanosleep(64);
+      }
+    }
+  }
+  __syncthreads();
+}
+
+__global__ void barrier_kernel(const __grid_constant__ SyncPtrs S, int slot, unsigned int epoch, int nranks, int rank,
+                               unsigned long long timeout_ns, int* err) {
+  signal_and_wait(S, slot, epoch, nranks, rank, timeout_ns, err);
+}
+
+// One CTA: sum this rank's per-CTA partial sums of squares in double, hand the result to every rank, wait for
+// everyone's, add them in rank order (the same order on every rank: identical norms bit for bit), take the root.
+__global__ void __launch_bounds__(kThreads)
+norm_exchange_kernel(const __grid_constant__ SyncPtrs S, const float* __restrict__ partials, int n_partials, int slot,
+                     unsigned int epoch, int nranks, int rank, unsigned long long timeout_ns, int* err,
+                     float* __restrict__ out_norm) {
+  __shared__ double red[32];
+  double s = 0.0;
+  for (int i = threadIdx.x; i < n_partials; i += kThreads) s += (double)partials[i];
+  s = block_sum(s, red);
+  __shared__ double mine;
+  if (threadIdx.x == 0) mine = s;
+  __syncthreads();
+  if (threadIdx.x < nranks) sumsq_slots(S.flags[threadIdx.x], epoch)[rank] = mine;  // plain store, released by the flag below
+  signal_and_wait(S, slot, epoch, nranks, rank, timeout_ns, err);
+  if (threadIdx.x == 0) {
+    const double* slots = sumsq_slots(S.flags[rank], epoch);
+    double tot = 0.0;
+    for (int r = 0; r < nranks; ++r) tot += reinterpret_cast<const volatile double*>(slots)[r];
+    out_norm[0] = (float)sqrt(tot);
+  }
+}
+
+// Owner-side reduction: rows r = 0..N-1 of this bucket in MY wire hold rank r's contribution to my slice.
+// wire[begin + rank*span + k] = sum_r wire[begin + r*span + k] (fp32 accumulate in rank order), plus the sum of
+// squares of the result for the global norm.  Reads N*span elements once, writes span: local HBM only.
+template <typename W>
+__global__ void __launch_bounds__(kThreads)
+peer_reduce_kernel(W* __restrict__ bucket, long long span, int nranks, int rank, float* __restrict__ partials) {
+  constexpr int VEC = is16<W>::value ? 8 : 4;
+  __shared__ float red[32];
+  const long long nvec = span / VEC;  // span is a multiple of 8 elements
+  const long long stride = (long long)gridDim.x * kThreads;
+  float ss = 0.f;
+  for (long long i = (long long)blockIdx.x * kThreads + threadIdx.x; i < nvec; i += stride) {
+    float acc[VEC], v[DGS_PEER_MAX][VEC];
+#pragma unroll
+    for (int r = 0; r < DGS_PEER_MAX; ++r)
+      if (r < nranks) load_vec<W, VEC, Cache::Stream>(bucket + r * span + i * VEC, v[r]);
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) acc[k] = v[0][k];
+#pragma unroll
+    for (int r = 1; r < DGS_PEER_MAX; ++r)
+      if (r < nranks) {
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) acc[k] += v[r][k];
+      }
+    store_vec<W, VEC>(bucket + (long long)rank * span + i * VEC, acc);
+    // the norm is that of the values as stored (rounded to the wire dtype), as clip_grad_norm_ would see them
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) {
+      const float q = to_f32(from_f32<W>(acc[k]));
+      ss = fmaf(q, q, ss);
+    }
+  }
+  const float tot = block_sum(ss, red);
+  if (threadIdx.x == 0) partials[blockIdx.x] = tot;
+}
+
+int check_group(const char* who, int nranks, int rank) {
+  DGS_CHECK_ARG(nranks >= 2 && nranks <= DGS_PEER_MAX && rank >= 0 && rank < nranks, "%s: rank %d of %d (at most %d ranks)",
+                who, rank, nranks, DGS_PEER_MAX);
+  return DGS_OK;
+}
+
+int fill_sync(const char* who, void* const* sync_blocks, int nranks, SyncPtrs* S) {
+  DGS_CHECK_ARG(sync_blocks != nullptr, "%s: sync_blocks is NULL", who);
+  for (int r = 0; r < DGS_PEER_MAX; ++r) S->flags[r] = nullptr;
+  for (int r = 0; r < nranks; ++r) {
+    DGS_CHECK_ARG(sync_blocks[r] != nullptr && (reinterpret_cast<uintptr_t>(sync_blocks[r]) & 15u) == 0,
+                  "%s: sync block of rank %d is NULL or misaligned", who, r);
+    S->flags[r] = static_cast<unsigned int*>(sync_blocks[r]);
+  }
+  return DGS_OK;
+}
+
+unsigned long long timeout_ns(double seconds) {
+  if (!(seconds > 0)) seconds = 120.0;
+  return (unsigned long long)(seconds * 1e9);
+}
+
+}  // namespace
+}  // namespace dgs
+
+extern "C" int dgs_peer_export(const void* ptr, void* handle64_out, int64_t* offset_out) {
+  using namespace dgs;
+  static_assert(sizeof(cudaIpcMemHandle_t) == DGS_PEER_HANDLE_BYTES, "cudaIpcMemHandle_t is 64 bytes");
+  DGS_CHECK_ARG(ptr && handle64_out && offset_out, "dgs_peer_export: NULL argument");
+  cudaIpcMemHandle_t h;
+  DGS_CUDA(cudaIpcGetMemHandle(&h, const_cast<void*>(ptr)));
+  // the handle names the whole allocation: find where in it `ptr` lies (driver API through the runtime's loader, so
+  // that the library needs no link-time libcuda and still loads on machines without a driver)
+  typedef CUresult (*GetRange)(CUdeviceptr*, size_t*, CUdeviceptr);
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  DGS_CUDA(cudaGetDriverEntryPoint("cuMemGetAddressRange", &fn, cudaEnableDefault, &q));
+  DGS_CHECK_ARG(fn != nullptr && q == cudaDriverEntryPointSuccess, "dgs_peer_export: cuMemGetAddressRange is unavailable");
+  CUdeviceptr base = 0;
+  size_t size = 0;
+  const CUresult rc = reinterpret_cast<GetRange>(fn)(&base, &size, reinterpret_cast<CUdeviceptr>(ptr));
+  if (rc != CUDA_SUCCESS) return fail(DGS_ECUDA, "dgs_peer_export: cuMemGetAddressRange failed (%d)", (int)rc);
+  memcpy(handle64_out, &h, sizeof(h));
+  *offset_out = (int64_t)(reinterpret_cast<CUdeviceptr>(ptr) - base);
+  return DGS_OK;
+}
+
+extern "C" int dgs_peer_open(const void* handle64, int64_t offset, void** out_ptr) {
+  using namespace dgs;
+  DGS_CHECK_ARG(handle64 && out_ptr && offset >= 0, "dgs_peer_open: bad argument");
+  std::lock_guard<std::mutex> lock(g_ipc_mutex);
+  const std::string key(static_cast<const char*>(handle64), DGS_PEER_HANDLE_BYTES);
+  auto it = g_opened.find(key);
+  void* base = nullptr;
+  if (it != g_opened.end()) {
+    base = it->second;
+  } else {
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, sizeof(h));
+    DGS_CUDA(cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
+    g_opened.emplace(key, base);
+  }
+  *out_ptr = static_cast<char*>(base) + offset;
+  return DGS_OK;
+}
+
+extern "C" int dgs_peer_close_all(void) {
+  using namespace dgs;
+  std::lock_guard<std::mutex> lock(g_ipc_mutex);
+  for (auto& kv : g_opened) (void)cudaIpcCloseMemHandle(kv.second);
+  g_opened.clear();
+  (void)cudaGetLastError();
+  return DGS_OK;
+}
+
+extern "C" int dgs_peer_error(int* code_out) {
+  using namespace dgs;
+  DGS_CHECK_ARG(code_out != nullptr, "dgs_peer_error: NULL argument");
+  *code_out = (g_err_host != nullptr) ? *reinterpret_cast<volatile int*>(g_err_host) : 0;
+  return DGS_OK;
+}
+
+extern "C" int dgs_peer_error_clear(void) {
+  if (dgs::g_err_host != nullptr) *reinterpret_cast<volatile int*>(dgs::g_err_host) = 0;
+  return DGS_OK;
+}
+
+extern "C" int dgs_peer_barrier(void* const* sync_blocks, int nranks, int rank, int slot, uint32_t epoch,
+                                double timeout_s, dgs_stream_t stream) {
+  using namespace dgs;
+  if (int rc = check_group("dgs_peer_barrier", nranks, rank)) return rc;
+  DGS_CHECK_ARG(slot >= 0 && slot < DGS_PEER_SLOTS, "dgs_peer_barrier: slot %d outside [0, %d)", slot, DGS_PEER_SLOTS);
+  SyncPtrs S;
+  if (int rc = fill_sync("dgs_peer_barrier", sync_blocks, nranks, &S)) return rc;
+  if (int rc = ensure_error_word()) return rc;
+  barrier_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(S, slot, epoch, nranks, rank, timeout_ns(timeout_s), g_err_dev);
+  DGS_LAUNCHED();
+  return DGS_OK;
+}
+
+extern "C" int dgs_peer_norm_exchange(void* const* sync_blocks, int nranks, int rank, int slot, uint32_t epoch,
+                                      const float* partials, int n_partials, float* out_norm, double timeout_s,
+                                      dgs_stream_t stream) {
+  using namespace dgs;
+  if (int rc = check_group("dgs_peer_norm_exchange", nranks, rank)) return rc;
+  DGS_CHECK_ARG(slot >= 0 && slot < DGS_PEER_SLOTS, "dgs_peer_norm_exchange: slot %d outside [0, %d)", slot, DGS_PEER_SLOTS);
+  DGS_CHECK_ARG(partials != nullptr && out_norm != nullptr && n_partials >= 0, "dgs_peer_norm_exchange: bad buffers");
+  SyncPtrs S;
+  if (int rc = fill_sync("dgs_peer_norm_exchange", sync_blocks, nranks, &S)) return rc;
+  if (int rc = ensure_error_word()) return rc;
+  norm_exchange_kernel<<<1, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(S, partials, n_partials, slot, epoch, nranks, rank,
+                                                                                timeout_ns(timeout_s), g_err_dev, out_norm);
+  DGS_LAUNCHED();
+  return DGS_OK;
+}
+
+extern "C" int dgs_peer_reduce(void* bucket, int dtype, int64_t span, int nranks, int rank, float* partials,
+                               dgs_stream_t stream) {
+  using namespace dgs;
+  if (int rc = check_group("dgs_peer_reduce", nranks, rank)) return rc;
+  DGS_CHECK_ARG(span >= 0 && (span & 7) == 0, "dgs_peer_reduce: span %lld is not a multiple of 8 elements", (long long)span);
+  DGS_CHECK_ARG(partials != nullptr, "dgs_peer_reduce: partials is NULL");
+  DGS_CHECK_ARG(span == 0 || (bucket != nullptr && aligned16(bucket)), "dgs_peer_reduce: bucket is NULL or misaligned");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int grid = dgs_l2norm_grid(span);
+  switch (dtype) {
+    case DGS_F32: peer_reduce_kernel<float><<<grid, kThreads, 0, st>>>((float*)bucket, span, nranks, rank, partials); break;
+    case DGS_BF16: peer_reduce_kernel<__nv_bfloat16><<<grid, kThreads, 0, st>>>((__nv_bfloat16*)bucket, span, nranks, rank, partials); break;
+    case DGS_F16: peer_reduce_kernel<__half><<<grid, kThreads, 0, st>>>((__half*)bucket, span, nranks, rank, partials); break;
+    default: return fail(DGS_EINVAL, "dgs_peer_reduce: bad dtype %d", dtype);
+  }
+  DGS_LAUNCHED();
+  return DGS_OK;
+}
