@@ -20,6 +20,7 @@ ALIGN_BYTES = 128
 NORM_MAX_PARTIALS = 9472
 NOALLOC_MAX_PARTIALS = 4096
 NOALLOC_MAX_ELEMS = 4096 * 16384
+PEER_MAX, PEER_SLOTS, PEER_HANDLE_BYTES, PEER_SYNC_BYTES = 8, 4, 64, 512
 
 
 class Seg(ctypes.Structure):
@@ -97,6 +98,17 @@ SIGNATURES = {
     "dgs_comm_l2norm_partial_async": [_vp, _vp, _i, _i64, _vp],
     "dgs_comm_wait": [_vp, _vp],
     "dgs_nccl_version": [ctypes.POINTER(_i)],
+    "dgs_peer_export": [_vp, _vp, ctypes.POINTER(_i64)],
+    "dgs_peer_open": [_vp, _i64, ctypes.POINTER(_vp)],
+    "dgs_peer_close_all": [],
+    "dgs_peer_error": [ctypes.POINTER(_i)],
+    "dgs_peer_error_clear": [],
+    "dgs_peer_barrier": [ctypes.POINTER(_vp), _i, _i, _i, ctypes.c_uint32, ctypes.c_double, _vp],
+    "dgs_flatten_push": [ctypes.POINTER(Seg), _i, _i, _vp, ctypes.POINTER(_vp), _i, _i, _f, _i64, _i64, _i, _i, _vp],
+    "dgs_peer_reduce": [_vp, _i, _i64, _i, _i, _vp, _vp],
+    "dgs_peer_norm_exchange": [ctypes.POINTER(_vp), _i, _i, _i, ctypes.c_uint32, _vp, _i, _vp, ctypes.c_double, _vp],
+    "dgs_step_adam_push": [_vp, _vp, _vp, _i, _vp, _i, _i64, ctypes.POINTER(AdamRange), _i, _vp, _f, ctypes.POINTER(_vp), _i, _i, _vp],
+    "dgs_step_sgd_push": [_vp, _vp, _i, _vp, _i, _i64, ctypes.POINTER(SgdRange), _i, _vp, _f, ctypes.POINTER(_vp), _i, _i, _vp],
 }
 _RESTYPES = {"dgs_last_error": ctypes.c_char_p, "dgs_launch_count": ctypes.c_int64}
 # functions whose int return is a value, not a status

@@ -42,6 +42,33 @@ struct Table {
   int n;
 };
 
+// Destinations of the updated parameters.  Plain step: the local buffer only.  Push step (dgs_step_*_push, the
+// all-gather half of the peer exchange, dgs_peer.cu): the same element offset in every rank's parameter buffer,
+// peer-mapped over NVLink; dst[own rank] is the local buffer the kernel also reads.
+struct ParamDst {
+  void* dst[DGS_PEER_MAX];
+  int n;
+};
+
+template <bool PUSH, typename P, int VEC>
+__device__ __forceinline__ void store_param(P* __restrict__ local, const ParamDst& D, long long i, const float (&v)[VEC]) {
+  if constexpr (PUSH) {
+#pragma unroll
+    for (int r = 0; r < DGS_PEER_MAX; ++r)
+      if (r < D.n) store_vec<P, VEC>(static_cast<P*>(D.dst[r]) + i, v);
+  } else {
+    store_vec<P, VEC>(local + i, v);
+  }
+}
+template <bool PUSH, typename P>
+__device__ __forceinline__ void store_param1(P* __restrict__ local, const ParamDst& D, long long e, float v) {
+  if constexpr (PUSH) {
+    for (int r = 0; r < D.n; ++r) static_cast<P*>(D.dst[r])[e] = from_f32<P>(v);
+  } else {
+    local[e] = from_f32<P>(v);
+  }
+}
+
 __device__ __forceinline__ float fast_sqrt(float x) {
   float r;
   asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
@@ -97,11 +124,12 @@ inline int step_unroll() {
   return v;
 }
 
-template <typename P, typename G, int kUnroll>
+template <typename P, typename G, int kUnroll, bool PUSH>
 __global__ void __launch_bounds__(kThreads)
 adam_kernel(P* __restrict__ param, P* __restrict__ ea, P* __restrict__ eas, const G* __restrict__ grad,
             long long n, const __grid_constant__ Table<AdamHp> T,
-            const float* __restrict__ total_norm, float max_norm, const float* __restrict__ inv_scale) {
+            const float* __restrict__ total_norm, float max_norm, const float* __restrict__ inv_scale,
+            const __grid_constant__ ParamDst D) {
   constexpr int VEC = StepCfg<P, G, kUnroll>::VEC;
   constexpr int TILE = StepCfg<P, G, kUnroll>::TILE;
   const float clip = grad_coef(total_norm, max_norm, inv_scale);
@@ -128,7 +156,7 @@ adam_kernel(P* __restrict__ param, P* __restrict__ ea, P* __restrict__ eas, cons
         const long long i = e0 + (long long)(u * kThreads + threadIdx.x) * VEC;
 #pragma unroll
         for (int k = 0; k < VEC; ++k) adam_update(p[u][k], m[u][k], v[u][k], g[u][k], h, clip);
-        store_vec<P, VEC>(param + i, p[u]);
+        store_param<PUSH, P, VEC>(param, D, i, p[u]);
         store_vec<P, VEC>(ea + i, m[u]);
         store_vec<P, VEC>(eas + i, v[u]);
       }
@@ -140,7 +168,7 @@ adam_kernel(P* __restrict__ param, P* __restrict__ ea, P* __restrict__ eas, cons
         if (q < 0) continue;
         float p = to_f32(param[e]), m = to_f32(ea[e]), v = to_f32(eas[e]);
         adam_update(p, m, v, to_f32(grad[e]), T.r[q], clip);
-        param[e] = from_f32<P>(p);
+        store_param1<PUSH, P>(param, D, e, p);
         ea[e] = from_f32<P>(m);
         eas[e] = from_f32<P>(v);
       }
@@ -148,11 +176,11 @@ adam_kernel(P* __restrict__ param, P* __restrict__ ea, P* __restrict__ eas, cons
   }
 }
 
-template <typename P, typename G, bool HAS_BUF, int kUnroll>
+template <typename P, typename G, bool HAS_BUF, int kUnroll, bool PUSH>
 __global__ void __launch_bounds__(kThreads)
 sgd_kernel(P* __restrict__ param, P* __restrict__ buf, const G* __restrict__ grad, long long n,
            const __grid_constant__ Table<SgdHp> T, const float* __restrict__ total_norm,
-           float max_norm, const float* __restrict__ inv_scale) {
+           float max_norm, const float* __restrict__ inv_scale, const __grid_constant__ ParamDst D) {
   constexpr int VEC = StepCfg<P, G, kUnroll>::VEC;
   constexpr int TILE = StepCfg<P, G, kUnroll>::TILE;
   const float clip = grad_coef(total_norm, max_norm, inv_scale);
@@ -183,7 +211,7 @@ sgd_kernel(P* __restrict__ param, P* __restrict__ buf, const G* __restrict__ gra
         const long long i = e0 + (long long)(u * kThreads + threadIdx.x) * VEC;
 #pragma unroll
         for (int k = 0; k < VEC; ++k) sgd_update(p[u][k], b[u][k], g[u][k], h, clip, HAS_BUF);
-        store_vec<P, VEC>(param + i, p[u]);
+        store_param<PUSH, P, VEC>(param, D, i, p[u]);
         if constexpr (HAS_BUF) store_vec<P, VEC>(buf + i, b[u]);
       }
     } else {
@@ -195,7 +223,7 @@ sgd_kernel(P* __restrict__ param, P* __restrict__ buf, const G* __restrict__ gra
         float b = 0.0f;
         if (HAS_BUF && !(T.r[q].flags & DGS_SGD_FIRST_STEP)) b = to_f32(buf[e]);
         sgd_update(p, b, to_f32(grad[e]), T.r[q], clip, HAS_BUF);
-        param[e] = from_f32<P>(p);
+        store_param1<PUSH, P>(param, D, e, p);
         if constexpr (HAS_BUF) buf[e] = from_f32<P>(b);
       }
     }
@@ -225,13 +253,19 @@ int check_ranges(const char* who, const Range* ranges, int n_ranges, int64_t n) 
   return DGS_OK;
 }
 
+const ParamDst kLocalOnly = {{nullptr}, 0};
+
 template <typename P, typename G, int U>
 int launch_adam_u(void* param, void* ea, void* eas, const void* grad, int64_t n, const Table<AdamHp>& T,
-                  const float* tn, float max_norm, const float* inv, cudaStream_t st) {
+                  const float* tn, float max_norm, const float* inv, const ParamDst* push, cudaStream_t st) {
   const long long tiles = (n + StepCfg<P, G, U>::TILE - 1) / StepCfg<P, G, U>::TILE;
   const int grid = tile_grid(tiles);
   timer_begin(st);
-  adam_kernel<P, G, U><<<grid, kThreads, 0, st>>>((P*)param, (P*)ea, (P*)eas, (const G*)grad, n, T, tn, max_norm, inv);
+  if (push != nullptr) {
+    adam_kernel<P, G, U, true><<<grid, kThreads, 0, st>>>((P*)param, (P*)ea, (P*)eas, (const G*)grad, n, T, tn, max_norm, inv, *push);
+  } else {
+    adam_kernel<P, G, U, false><<<grid, kThreads, 0, st>>>((P*)param, (P*)ea, (P*)eas, (const G*)grad, n, T, tn, max_norm, inv, kLocalOnly);
+  }
   timer_end(st);
   DGS_LAUNCHED();
   return DGS_OK;
@@ -239,23 +273,29 @@ int launch_adam_u(void* param, void* ea, void* eas, const void* grad, int64_t n,
 
 template <typename P, typename G>
 int launch_adam(void* param, void* ea, void* eas, const void* grad, int64_t n, const Table<AdamHp>& T,
-                const float* tn, float max_norm, const float* inv, cudaStream_t st) {
+                const float* tn, float max_norm, const float* inv, const ParamDst* push, cudaStream_t st) {
   // one vector per array per thread (4 loads in flight) measured best; DGS_STEP_UNROLL=2|4 re-runs the sweep
-  if (step_unroll() == 2) return launch_adam_u<P, G, 2>(param, ea, eas, grad, n, T, tn, max_norm, inv, st);
-  if (step_unroll() == 4) return launch_adam_u<P, G, 4>(param, ea, eas, grad, n, T, tn, max_norm, inv, st);
-  return launch_adam_u<P, G, 1>(param, ea, eas, grad, n, T, tn, max_norm, inv, st);
+  if (push == nullptr && step_unroll() == 2) return launch_adam_u<P, G, 2>(param, ea, eas, grad, n, T, tn, max_norm, inv, push, st);
+  if (push == nullptr && step_unroll() == 4) return launch_adam_u<P, G, 4>(param, ea, eas, grad, n, T, tn, max_norm, inv, push, st);
+  return launch_adam_u<P, G, 1>(param, ea, eas, grad, n, T, tn, max_norm, inv, push, st);
 }
 
 template <typename P, typename G, int U>
 int launch_sgd_u(void* param, void* buf, const void* grad, int64_t n, const Table<SgdHp>& T,
-                 const float* tn, float max_norm, const float* inv, cudaStream_t st) {
+                 const float* tn, float max_norm, const float* inv, const ParamDst* push, cudaStream_t st) {
   const long long tiles = (n + StepCfg<P, G, U>::TILE - 1) / StepCfg<P, G, U>::TILE;
   const int grid = tile_grid(tiles);
   timer_begin(st);
-  if (buf != nullptr) {
-    sgd_kernel<P, G, true, U><<<grid, kThreads, 0, st>>>((P*)param, (P*)buf, (const G*)grad, n, T, tn, max_norm, inv);
+  if (push != nullptr) {
+    if (buf != nullptr) {
+      sgd_kernel<P, G, true, U, true><<<grid, kThreads, 0, st>>>((P*)param, (P*)buf, (const G*)grad, n, T, tn, max_norm, inv, *push);
+    } else {
+      sgd_kernel<P, G, false, U, true><<<grid, kThreads, 0, st>>>((P*)param, nullptr, (const G*)grad, n, T, tn, max_norm, inv, *push);
+    }
+  } else if (buf != nullptr) {
+    sgd_kernel<P, G, true, U, false><<<grid, kThreads, 0, st>>>((P*)param, (P*)buf, (const G*)grad, n, T, tn, max_norm, inv, kLocalOnly);
   } else {
-    sgd_kernel<P, G, false, U><<<grid, kThreads, 0, st>>>((P*)param, nullptr, (const G*)grad, n, T, tn, max_norm, inv);
+    sgd_kernel<P, G, false, U, false><<<grid, kThreads, 0, st>>>((P*)param, nullptr, (const G*)grad, n, T, tn, max_norm, inv, kLocalOnly);
   }
   timer_end(st);
   DGS_LAUNCHED();
@@ -264,28 +304,30 @@ int launch_sgd_u(void* param, void* buf, const void* grad, int64_t n, const Tabl
 
 template <typename P, typename G>
 int launch_sgd(void* param, void* buf, const void* grad, int64_t n, const Table<SgdHp>& T,
-               const float* tn, float max_norm, const float* inv, cudaStream_t st) {
-  if (step_unroll() == 2) return launch_sgd_u<P, G, 2>(param, buf, grad, n, T, tn, max_norm, inv, st);
-  if (step_unroll() == 4) return launch_sgd_u<P, G, 4>(param, buf, grad, n, T, tn, max_norm, inv, st);
-  return launch_sgd_u<P, G, 1>(param, buf, grad, n, T, tn, max_norm, inv, st);
+               const float* tn, float max_norm, const float* inv, const ParamDst* push, cudaStream_t st) {
+  if (push == nullptr && step_unroll() == 2) return launch_sgd_u<P, G, 2>(param, buf, grad, n, T, tn, max_norm, inv, push, st);
+  if (push == nullptr && step_unroll() == 4) return launch_sgd_u<P, G, 4>(param, buf, grad, n, T, tn, max_norm, inv, push, st);
+  return launch_sgd_u<P, G, 1>(param, buf, grad, n, T, tn, max_norm, inv, push, st);
 }
 
-}  // namespace
-}  // namespace dgs
-
-extern "C" int dgs_step_adam(void* param, void* exp_avg, void* exp_avg_sq, int state_dtype,
-                             const void* grad, int grad_dtype, int64_t n,
-                             const dgs_adam_range* ranges, int n_ranges, const float* total_norm,
-                             float max_norm, dgs_stream_t stream) {
-  return dgs_step_adam_scaled(param, exp_avg, exp_avg_sq, state_dtype, grad, grad_dtype, n, ranges, n_ranges,
-                              total_norm, max_norm, nullptr, stream);
+// the push variants' destination table: every rank's parameter pointer for the same element range, [rank] local
+int fill_dst(const char* who, void* param, void* const* param_peers, int nranks, int rank, ParamDst* D) {
+  DGS_CHECK_ARG(nranks >= 2 && nranks <= DGS_PEER_MAX && rank >= 0 && rank < nranks, "%s: rank %d of %d (at most %d ranks)", who,
+                rank, nranks, DGS_PEER_MAX);
+  DGS_CHECK_ARG(param_peers != nullptr, "%s: param_peers is NULL", who);
+  for (int r = 0; r < DGS_PEER_MAX; ++r) D->dst[r] = nullptr;
+  for (int r = 0; r < nranks; ++r) {
+    DGS_CHECK_ARG(param_peers[r] != nullptr && aligned16(param_peers[r]), "%s: parameter pointer of rank %d is NULL or misaligned", who, r);
+    D->dst[r] = param_peers[r];
+  }
+  DGS_CHECK_ARG(param_peers[rank] == param, "%s: param_peers[rank] must be the local parameter pointer", who);
+  D->n = nranks;
+  return DGS_OK;
 }
 
-extern "C" int dgs_step_adam_scaled(void* param, void* exp_avg, void* exp_avg_sq, int state_dtype,
-                                    const void* grad, int grad_dtype, int64_t n,
-                                    const dgs_adam_range* ranges, int n_ranges, const float* total_norm,
-                                    float max_norm, const float* inv_scale, dgs_stream_t stream) {
-  using namespace dgs;
+int step_adam_impl(void* param, void* exp_avg, void* exp_avg_sq, int state_dtype, const void* grad, int grad_dtype,
+                   int64_t n, const dgs_adam_range* ranges, int n_ranges, const float* total_norm, float max_norm,
+                   const float* inv_scale, const ParamDst* push, cudaStream_t st) {
   DGS_CHECK_ARG(n >= 0, "dgs_step_adam: n < 0");
   if (int rc = check_ranges("dgs_step_adam", ranges, n_ranges, n)) return rc;
   if (n == 0 || n_ranges == 0) return DGS_OK;
@@ -309,10 +351,9 @@ extern "C" int dgs_step_adam_scaled(void* param, void* exp_avg, void* exp_avg_sq
     h.neg_step = (float)(-r.step_size);
     h.inv_bc2_sqrt = (float)(1.0 / r.bias_correction2_sqrt);
   }
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
 #define DGS_ADAM_CASE(PD, PT, GD, GT) \
   if (state_dtype == PD && grad_dtype == GD) \
-    return launch_adam<PT, GT>(param, exp_avg, exp_avg_sq, grad, n, T, total_norm, max_norm, inv_scale, st);
+    return launch_adam<PT, GT>(param, exp_avg, exp_avg_sq, grad, n, T, total_norm, max_norm, inv_scale, push, st);
   DGS_ADAM_CASE(DGS_F32, float, DGS_F32, float)
   DGS_ADAM_CASE(DGS_F32, float, DGS_BF16, __nv_bfloat16)
   DGS_ADAM_CASE(DGS_F32, float, DGS_F16, __half)
@@ -324,18 +365,9 @@ extern "C" int dgs_step_adam_scaled(void* param, void* exp_avg, void* exp_avg_sq
   return fail(DGS_EUNSUPPORTED, "dgs_step_adam: state dtype %d with grad dtype %d", state_dtype, grad_dtype);
 }
 
-extern "C" int dgs_step_sgd(void* param, void* momentum_buf, int state_dtype, const void* grad,
-                            int grad_dtype, int64_t n, const dgs_sgd_range* ranges, int n_ranges,
-                            const float* total_norm, float max_norm, dgs_stream_t stream) {
-  return dgs_step_sgd_scaled(param, momentum_buf, state_dtype, grad, grad_dtype, n, ranges, n_ranges, total_norm,
-                             max_norm, nullptr, stream);
-}
-
-extern "C" int dgs_step_sgd_scaled(void* param, void* momentum_buf, int state_dtype, const void* grad,
-                                   int grad_dtype, int64_t n, const dgs_sgd_range* ranges, int n_ranges,
-                                   const float* total_norm, float max_norm, const float* inv_scale,
-                                   dgs_stream_t stream) {
-  using namespace dgs;
+int step_sgd_impl(void* param, void* momentum_buf, int state_dtype, const void* grad, int grad_dtype, int64_t n,
+                  const dgs_sgd_range* ranges, int n_ranges, const float* total_norm, float max_norm,
+                  const float* inv_scale, const ParamDst* push, cudaStream_t st) {
   DGS_CHECK_ARG(n >= 0, "dgs_step_sgd: n < 0");
   if (int rc = check_ranges("dgs_step_sgd", ranges, n_ranges, n)) return rc;
   if (n == 0 || n_ranges == 0) return DGS_OK;
@@ -365,10 +397,9 @@ extern "C" int dgs_step_sgd_scaled(void* param, void* momentum_buf, int state_dt
   }
   DGS_CHECK_ARG(!any_mom || all_mom, "dgs_step_sgd: ranges with and without momentum must go in separate calls");
   void* buf = any_mom ? momentum_buf : nullptr;
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
 #define DGS_SGD_CASE(PD, PT, GD, GT) \
   if (state_dtype == PD && grad_dtype == GD) \
-    return launch_sgd<PT, GT>(param, buf, grad, n, T, total_norm, max_norm, inv_scale, st);
+    return launch_sgd<PT, GT>(param, buf, grad, n, T, total_norm, max_norm, inv_scale, push, st);
   DGS_SGD_CASE(DGS_F32, float, DGS_F32, float)
   DGS_SGD_CASE(DGS_F32, float, DGS_BF16, __nv_bfloat16)
   DGS_SGD_CASE(DGS_F32, float, DGS_F16, __half)
@@ -378,4 +409,57 @@ extern "C" int dgs_step_sgd_scaled(void* param, void* momentum_buf, int state_dt
   DGS_SGD_CASE(DGS_F16, __half, DGS_F16, __half)
 #undef DGS_SGD_CASE
   return fail(DGS_EUNSUPPORTED, "dgs_step_sgd: state dtype %d with grad dtype %d", state_dtype, grad_dtype);
+}
+
+}  // namespace
+}  // namespace dgs
+
+extern "C" int dgs_step_adam(void* param, void* exp_avg, void* exp_avg_sq, int state_dtype,
+                             const void* grad, int grad_dtype, int64_t n,
+                             const dgs_adam_range* ranges, int n_ranges, const float* total_norm,
+                             float max_norm, dgs_stream_t stream) {
+  return dgs::step_adam_impl(param, exp_avg, exp_avg_sq, state_dtype, grad, grad_dtype, n, ranges, n_ranges, total_norm,
+                             max_norm, nullptr, nullptr, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int dgs_step_adam_scaled(void* param, void* exp_avg, void* exp_avg_sq, int state_dtype,
+                                    const void* grad, int grad_dtype, int64_t n,
+                                    const dgs_adam_range* ranges, int n_ranges, const float* total_norm,
+                                    float max_norm, const float* inv_scale, dgs_stream_t stream) {
+  return dgs::step_adam_impl(param, exp_avg, exp_avg_sq, state_dtype, grad, grad_dtype, n, ranges, n_ranges, total_norm,
+                             max_norm, inv_scale, nullptr, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int dgs_step_adam_push(void* param, void* exp_avg, void* exp_avg_sq, int state_dtype, const void* grad,
+                                  int grad_dtype, int64_t n, const dgs_adam_range* ranges, int n_ranges,
+                                  const float* total_norm, float max_norm, void* const* param_peers, int nranks,
+                                  int rank, dgs_stream_t stream) {
+  dgs::ParamDst D;
+  if (int rc = dgs::fill_dst("dgs_step_adam_push", param, param_peers, nranks, rank, &D)) return rc;
+  return dgs::step_adam_impl(param, exp_avg, exp_avg_sq, state_dtype, grad, grad_dtype, n, ranges, n_ranges, total_norm,
+                             max_norm, nullptr, &D, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int dgs_step_sgd(void* param, void* momentum_buf, int state_dtype, const void* grad,
+                            int grad_dtype, int64_t n, const dgs_sgd_range* ranges, int n_ranges,
+                            const float* total_norm, float max_norm, dgs_stream_t stream) {
+  return dgs::step_sgd_impl(param, momentum_buf, state_dtype, grad, grad_dtype, n, ranges, n_ranges, total_norm,
+                            max_norm, nullptr, nullptr, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int dgs_step_sgd_scaled(void* param, void* momentum_buf, int state_dtype, const void* grad,
+                                   int grad_dtype, int64_t n, const dgs_sgd_range* ranges, int n_ranges,
+                                   const float* total_norm, float max_norm, const float* inv_scale,
+                                   dgs_stream_t stream) {
+  return dgs::step_sgd_impl(param, momentum_buf, state_dtype, grad, grad_dtype, n, ranges, n_ranges, total_norm,
+                            max_norm, inv_scale, nullptr, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int dgs_step_sgd_push(void* param, void* momentum_buf, int state_dtype, const void* grad, int grad_dtype,
+                                 int64_t n, const dgs_sgd_range* ranges, int n_ranges, const float* total_norm,
+                                 float max_norm, void* const* param_peers, int nranks, int rank, dgs_stream_t stream) {
+  dgs::ParamDst D;
+  if (int rc = dgs::fill_dst("dgs_step_sgd_push", param, param_peers, nranks, rank, &D)) return rc;
+  return dgs::step_sgd_impl(param, momentum_buf, state_dtype, grad, grad_dtype, n, ranges, n_ranges, total_norm,
+                            max_norm, nullptr, &D, static_cast<cudaStream_t>(stream));
 }

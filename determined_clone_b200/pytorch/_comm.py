@@ -18,8 +18,11 @@ def _stream() -> ctypes.c_void_p:
 
 
 class Comm:
-    def __init__(self, rank: int, size: int, device: torch.device, bcast: Callable[[Any], Any]) -> None:
+    def __init__(self, rank: int, size: int, device: torch.device, bcast: Callable[[Any], Any],
+                 allgather: Optional[Callable[[Any], Any]] = None) -> None:
         self.rank, self.size, self.device = rank, size, device
+        # control-plane allgather of small Python objects (CUDA IPC handles of the peer-memory exchange, _peer.py)
+        self.allgather_obj = allgather
         ident = ctypes.create_string_buffer(128)
         if rank == 0:
             _lib.calls.dgs_comm_unique_id(ident)
@@ -33,7 +36,7 @@ class Comm:
 
     @classmethod
     def from_distributed(cls, distributed: Any, device: torch.device) -> "Comm":
-        return cls(distributed.rank, distributed.size, device, distributed.broadcast)
+        return cls(distributed.rank, distributed.size, device, distributed.broadcast, distributed.allgather)
 
     def _handle(self) -> ctypes.c_void_p:
         if self._h is None:

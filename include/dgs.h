@@ -297,6 +297,71 @@ int dgs_comm_l2norm_partial_async(dgs_comm* comm, const void* x, int dtype, int6
 int dgs_comm_wait(dgs_comm* comm, dgs_stream_t compute);
 int dgs_nccl_version(int* version);
 
+/* ------------------------------------------------------------------------------------------------
+ * 6. peer-memory exchange: the bucket allreduce as this library's own kernels over NVLink / NVSwitch
+ *
+ * Replaces: DistributedDataParallel's bucket allreduce on the boundary backward pass
+ * (H/pytorch/_pytorch_context.py:295-296 wraps the model, :813-816 runs the backward whose hooks
+ * reduce the buckets) -- the same call sites as dgs_comm_allreduce_async, for up to DGS_PEER_MAX
+ * ranks whose GPUs can map each other's memory (one NVSwitch domain).  Instead of NCCL:
+ *   dgs_flatten_push        flatten + scale + cast + reduce-scatter transfer in one kernel: each value
+ *                           is stored straight into the wire buffer of the rank that owns its slice
+ *   dgs_peer_barrier        all ranks' stores have landed (flags in peer-mapped sync blocks)
+ *   dgs_peer_reduce         owner sums its N rows in rank order, emits sum-of-squares partials
+ *   dgs_peer_norm_exchange  8-byte all-to-all of the ranks' sums of squares -> global L2 norm
+ *   dgs_step_*_push         clip + step on the owner's slice; new parameters stored to every rank
+ * Bucket layout: a bucket is nranks * span contiguous elements of the flat buffer, rank j owns
+ * elements [begin + j*span, begin + (j+1)*span).  In rank j's OWN wire buffer, row r of the bucket
+ * (elements [begin + r*span, ...)) receives rank r's contribution to slice j; after dgs_peer_reduce
+ * row j holds the sum, i.e. the reduced gradient sits where the flat layout expects it.
+ * All remote accesses are ordinary global stores (and flag loads) on peer-mapped pointers.
+ *
+ * Memory is shared with CUDA IPC: dgs_peer_export gives the 64-byte handle of the allocation that
+ * contains `ptr` and ptr's offset in it; the handles travel through the caller's control plane;
+ * dgs_peer_open maps a peer's allocation (once per process, cached) and returns the peer's pointer.
+ * The library still allocates no tensor memory.  Sync block: DGS_PEER_SYNC_BYTES of zero-initialised
+ * device memory per rank, exported and opened like the buffers.  Flags carry an epoch that the
+ * caller increases by one per use of a slot on every rank in lockstep.  A wait that exceeds
+ * timeout_s (<= 0: 120 s) records a code readable with dgs_peer_error, stops waiting, and makes every
+ * later wait return at once: the stream drains and the host can raise instead of hanging.
+ * ---------------------------------------------------------------------------------------------- */
+#define DGS_PEER_MAX 8
+#define DGS_PEER_SLOTS 4
+#define DGS_PEER_HANDLE_BYTES 64
+#define DGS_PEER_SYNC_BYTES 512 /* DGS_PEER_SLOTS*DGS_PEER_MAX uint32 flags + 2*DGS_PEER_MAX doubles */
+
+int dgs_peer_export(const void* ptr, void* handle64_out, int64_t* offset_out);
+int dgs_peer_open(const void* handle64, int64_t offset, void** out_ptr);
+int dgs_peer_close_all(void);
+int dgs_peer_error(int* code_out);
+int dgs_peer_error_clear(void);
+/* sync_blocks[r] = rank r's sync block as mapped in this process ([rank] is the local one) */
+int dgs_peer_barrier(void* const* sync_blocks, int nranks, int rank, int slot, uint32_t epoch,
+                     double timeout_s, dgs_stream_t stream);
+/* Same modes and arguments as dgs_flatten_accumulate with DGS_WRITE_WIRE set, except that the wire
+ * value of flat element f is stored to wire_peers[owner(f)] + f + (rank - owner(f)) * span.  All
+ * segments must lie inside [bucket_begin, bucket_begin + nranks*span). */
+int dgs_flatten_push(const dgs_seg* segs, int n_segs, int grad_dtype, float* acc, void* const* wire_peers,
+                     int wire_dtype, int mode, float scale, int64_t bucket_begin, int64_t span,
+                     int nranks, int rank, dgs_stream_t stream);
+/* bucket = this rank's wire + bucket_begin.  partials receives dgs_l2norm_grid(span) floats. */
+int dgs_peer_reduce(void* bucket, int dtype, int64_t span, int nranks, int rank, float* partials,
+                    dgs_stream_t stream);
+/* out_norm[0] = sqrt(sum over ranks (in rank order) of sum(partials)); implies a barrier */
+int dgs_peer_norm_exchange(void* const* sync_blocks, int nranks, int rank, int slot, uint32_t epoch,
+                           const float* partials, int n_partials, float* out_norm, double timeout_s,
+                           dgs_stream_t stream);
+/* dgs_step_adam / dgs_step_sgd on this rank's slice (param, state, grad point at the slice) with the
+ * updated parameters stored to param_peers[0..nranks) (every rank's pointer to the same slice;
+ * param_peers[rank] == param). */
+int dgs_step_adam_push(void* param, void* exp_avg, void* exp_avg_sq, int state_dtype, const void* grad,
+                       int grad_dtype, int64_t n, const dgs_adam_range* ranges, int n_ranges,
+                       const float* total_norm, float max_norm, void* const* param_peers, int nranks,
+                       int rank, dgs_stream_t stream);
+int dgs_step_sgd_push(void* param, void* momentum_buf, int state_dtype, const void* grad, int grad_dtype,
+                      int64_t n, const dgs_sgd_range* ranges, int n_ranges, const float* total_norm,
+                      float max_norm, void* const* param_peers, int nranks, int rank, dgs_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
