@@ -34,6 +34,7 @@ from typing import Any, Callable, Dict, List, Optional, Sequence, Tuple
 import torch
 
 from determined_clone_b200 import _lib, errors
+from determined_clone_b200.pytorch import _peer
 from determined_clone_b200.pytorch._comm import Comm
 
 ALIGN_ELEMS = 64  # 128 bytes of bf16, 256 bytes of fp32: every tensor starts vector-aligned
@@ -178,6 +179,7 @@ class _FlatSet:
         self.dtype_code = self.wire_code = 0
         self.acc_ptr: Any = None
         self.wire_ptr: Any = None
+        self.peer_wire: Any = None  # (void*)[world]: every rank's pointer to its wire buffer of this set (peer route)
         self.segs_all: Any = None  # prebuilt dgs_seg[len(tensors)] for whole-set launches (single GPU)
         self.params: List[Any] = []  # every parameter of the set, in table order
         self.group_runs: Optional[List[Tuple[int, int, int, List[_Tensor]]]] = None
@@ -198,6 +200,7 @@ class GradSyncEngine:
         bucket_bytes: int = BUCKET_BYTES,
         first_bucket_bytes: int = FIRST_BUCKET_BYTES,
         sharded_step: Optional[bool] = None,
+        route: Optional[str] = None,
     ) -> None:
         _lib.load()  # fail now, loudly, if libdgs.so is missing
         _check_device(device)
@@ -232,15 +235,32 @@ class GradSyncEngine:
         self._steps_host: Optional[torch.Tensor] = None  # Adam's per-parameter `step`, one host tensor
         self._step_views: List[torch.Tensor] = []
         self._fused_kind = self._classify(optimizer)
-        # Sharded step (opt-in: sharded_step=True or DGS_SHARDED_STEP=1; several GPUs, fused optimizers only):
-        # buckets are reduce-SCATTERED, every rank clips and steps only its 1/N slice of each bucket, and the
-        # updated parameters are all-gathered.  Same NVLink bytes as the allreduce, 1/N of the optimizer's HBM
-        # traffic, and the step no longer waits behind the second half of the allreduce.  Optimizer state of
-        # other ranks' slices is fetched when optimizer.state_dict() is called.
-        if sharded_step is None:
-            sharded_step = _os.environ.get("DGS_SHARDED_STEP", "") not in ("", "0")
-        self.sharded = bool(sharded_step and comm is not None and self._fused_kind is not None and not fp16_compression
-                            and ALIGN_ELEMS % (8 * self.world) == 0)
+        # Exchange route of the optimizer step on several GPUs:
+        #   allreduce  NCCL allreduce of each bucket, every rank steps every element
+        #   sharded    NCCL reduce-scatter, every rank clips and steps only its 1/N slice of each bucket, NCCL
+        #              all-gather of the updated parameters (round 1's opt-in sharded step)
+        #   peer       the same slicing, but the exchange is this library's own kernels on peer-mapped buffers over
+        #              NVLink: the flatten kernel stores each value into the owner's wire buffer, the owner reduces,
+        #              the step kernel stores the new parameters to every rank (csrc/dgs_peer.cu, _peer.py)
+        #   auto       (default) start on allreduce; once two optimizer steps in a row used the path in the way the
+        #              sliced routes can honour (no GradScaler, clip_grads absent or provably nothing but
+        #              clip_grad_norm_, auto_zero_grads) move to peer for good -- if peer set-up succeeded on every
+        #              rank.  A later step that does not fit moves back to allreduce (demote()).
+        # With sliced routes the optimizer state of other ranks' slices is fetched when optimizer.state_dict() is called.
+        if route is None:
+            route = "sharded" if sharded_step else _os.environ.get("DGS_ROUTE") or ("sharded" if _os.environ.get("DGS_SHARDED_STEP", "") not in ("", "0") else "auto")
+        if route not in ("auto", "allreduce", "sharded", "peer"):
+            raise errors.InvalidExperimentException(f"optimizations.grad_sync_route must be auto, allreduce, sharded or peer; got {route!r}")
+        sliceable = bool(comm is not None and self._fused_kind is not None and not fp16_compression and ALIGN_ELEMS % (8 * self.world) == 0)
+        if route in ("sharded", "peer") and comm is not None and not sliceable:
+            route = "allreduce"  # non-fused optimizer, fp16 wire compression or a world size the 128-byte alignment does not divide
+        self.route = route if comm is not None else "allreduce"
+        self.sliceable = sliceable
+        self.sharded = self.route in ("sharded", "peer")  # this rank holds (and steps) only its slice of every bucket
+        self.peer = self.route == "peer"                   # ... exchanged by the peer kernels instead of NCCL
+        self.peers: Optional[_peer.PeerGroup] = None
+        self.peer_unavailable: Optional[str] = None  # why peer set-up failed, if it did
+        self._conforming_steps = 0
         self.last_total_norm: Optional[torch.Tensor] = None
         self._inv_scale: Optional[torch.Tensor] = None
         # Several GPUs: norm pass 1 is run per bucket right behind the bucket's allreduce (aux stream, bucket still
@@ -318,13 +338,14 @@ class GradSyncEngine:
             fs.params = [t.param for t in fs.tensors]
             for k, t in enumerate(fs.tensors):
                 fs.segs_all[k].dst_off, fs.segs_all[k].numel = t.off, t.numel
-        # norm scratch: [whole-buffer partials of every set | per-bucket partials of every set]
+        # norm scratch: [whole-buffer partials of every set | per-bucket partials of every set].  A bucket's slots are
+        # sized for the whole bucket, so that they also hold the (fewer) partials of one slice after a route change;
+        # unused slots stay zero (_set_route clears the scratch), the final pass sums them all.
         n_partials = sum(_lib.calls.dgs_l2norm_grid(fs.total) for fs in self.sets)
         self._bucket_partials_base = n_partials
         for fs in self.sets:
             for b in fs.buckets:
-                span = (b.end - b.begin) // (self.world if self.sharded else 1)
-                b.norm_off, b.norm_n = n_partials, _lib.calls.dgs_l2norm_grid(span)
+                b.norm_off, b.norm_n = n_partials, _lib.calls.dgs_l2norm_grid(b.end - b.begin)
                 n_partials += b.norm_n
         self._partials = torch.zeros(max(n_partials, 1), dtype=torch.float32, device=self.device)
         self._launch_order = [(si, bi) for si, fs in enumerate(self.sets) for bi in range(len(fs.buckets))]
@@ -333,8 +354,60 @@ class GradSyncEngine:
             for fs in self.sets:
                 self.comm.broadcast(fs.param, 0)
             self.comm.wait()
-        if self.sharded:
             self._state_hook = self.optimizer.register_state_dict_pre_hook(lambda opt: self.gather_state())
+        if self.comm is not None and self.sliceable and self.route in ("auto", "peer"):
+            self._setup_peers(required=self.route == "peer")
+
+    def _setup_peers(self, required: bool) -> None:
+        """Map every rank's wire and parameter buffers (all-or-none across ranks)."""
+        comm = self.comm
+        assert comm is not None
+        try:
+            if comm.allgather_obj is None:
+                raise _lib.DgsError("the communicator has no control-plane allgather to carry the IPC handles")
+            buffers = {}
+            for si, fs in enumerate(self.sets):
+                buffers[f"wire{si}"], buffers[f"param{si}"] = fs.wire, fs.param
+            timeout = float(_os.environ.get("DGS_PEER_TIMEOUT_S", "0") or 0)
+            self.peers = _peer.PeerGroup(comm.rank, comm.size, self.device, comm.allgather_obj, buffers, timeout_s=timeout)
+            for si, fs in enumerate(self.sets):
+                fs.peer_wire = self.peers.table(f"wire{si}")
+        except _lib.DgsError as e:
+            self.peers = None
+            if required:
+                raise
+            self.peer_unavailable = str(e)
+
+    def _set_route(self, sliced: bool, peer: bool) -> None:
+        """Switch between the full-gradient route and the sliced ones; only between windows."""
+        self.sharded, self.peer = sliced, peer
+        self._partials.zero_()
+        self._eager_norm = False
+        self.last_total_norm = None
+
+    def note_step(self, conforming: bool) -> None:
+        """Called by the context after every optimizer step with whether that step used the path in a way the sliced
+        routes can honour.  route == auto: two such steps in a row move the engine to the peer route."""
+        if self.route != "auto" or self.peers is None:
+            return
+        self._conforming_steps = self._conforming_steps + 1 if conforming else 0
+        if not self.sharded and self._conforming_steps >= 2:
+            self._set_route(True, True)
+
+    def demote(self, present: Optional[List[List[bool]]] = None) -> None:
+        """A step the sliced routes cannot honour arrived (route == auto only): bring every rank's optimizer state and,
+        if a window is waiting (finish_window already ran), the reduced gradient slices back to all ranks, and
+        continue on the allreduce route for good."""
+        assert self.comm is not None and self.sharded
+        self.gather_state()
+        if present is not None:
+            for fs in self.sets:
+                isz = fs.wire.element_size()
+                for b in sorted(fs.buckets, key=lambda x: x.begin):
+                    self.comm.allgather_inplace_raw(fs.wire.data_ptr() + b.begin * isz, (b.end - b.begin) // self.world * isz)
+            self.comm.wait()
+        self.route = "allreduce"
+        self._set_route(False, False)
 
     def _cut_buckets(self, fs: _FlatSet) -> None:
         itemsize = torch.empty(0, dtype=fs.wire_dtype).element_size()
@@ -546,9 +619,7 @@ class GradSyncEngine:
                 for k, ti in enumerate(b.tensors):
                     segs[k].src = grads[ti].data_ptr()
             mode = (_lib.READ_ACC if first_state else 0) | (_lib.WRITE_WIRE if to_wire else 0)
-            _lib.calls.dgs_flatten_accumulate(
-                segs, len(b.tensors), fs.dtype_code, fs.acc_ptr, fs.wire_ptr, fs.wire_code, mode, self.scale * self.unscale, stream,
-            )
+            self._flatten(fs, b, segs, len(b.tensors), fs.dtype_code, fs.acc_ptr, mode, stream)
         else:
             for read_acc in (False, True):
                 idxs = [ti for ti in grads if in_window[ti] == read_acc]
@@ -560,9 +631,7 @@ class GradSyncEngine:
                     seg = segs[k]
                     seg.src, seg.dst_off, seg.numel = grads[ti].data_ptr(), t.off, t.numel
                 mode = (_lib.READ_ACC if read_acc else 0) | (_lib.WRITE_WIRE if to_wire else 0)
-                _lib.calls.dgs_flatten_accumulate(
-                    segs, len(idxs), fs.dtype_code, fs.acc_ptr, fs.wire_ptr, fs.wire_code, mode, self.scale * self.unscale, stream,
-                )
+                self._flatten(fs, b, segs, len(idxs), fs.dtype_code, fs.acc_ptr, mode, stream)
         flags = fs.in_wire if to_wire else fs.in_window
         for ti in grads:
             flags[ti] = True
@@ -570,6 +639,15 @@ class GradSyncEngine:
         if to_wire:
             b.flushed = True
             self._reduce_ready(fs)
+
+    def _flatten(self, fs: _FlatSet, b: _Bucket, segs: Any, n: int, grad_code: int, acc_ptr: Any, mode: int, stream: Any) -> None:
+        """One flatten launch over tensors of bucket b.  Peer route, wire-writing modes: the values go straight to the
+        rank that owns their slice (dgs_flatten_push) -- the reduce-scatter transfer is this kernel's stores."""
+        if self.peer and mode & _lib.WRITE_WIRE:
+            _lib.calls.dgs_flatten_push(segs, n, grad_code, acc_ptr, fs.peer_wire, fs.wire_code, mode, self.scale * self.unscale,
+                                        b.begin, (b.end - b.begin) // self.world, self.world, self.comm.rank, stream)  # type: ignore
+        else:
+            _lib.calls.dgs_flatten_accumulate(segs, n, grad_code, acc_ptr, fs.wire_ptr, fs.wire_code, mode, self.scale * self.unscale, stream)
 
     def _reduce_ready(self, fs: Optional[_FlatSet] = None) -> None:
         """Issue allreduces strictly in `_launch_order`, so that every rank issues the same NCCL sequence.
@@ -584,12 +662,14 @@ class GradSyncEngine:
                 return
             itemsize = fs.wire.element_size()
             base, span = fs.wire.data_ptr() + b.begin * itemsize, b.end - b.begin
-            if self.comm is not None and not b.reduced:
+            if self.peer:
+                pass  # nothing to issue: the flatten kernel's stores were the transfer; the owner reduces at step time
+            elif self.comm is not None and not b.reduced:
                 if self.sharded:
                     self.comm.reduce_scatter_raw(base, span // self.world, fs.wire_code)
                 else:
                     self.comm.allreduce_raw(base, span, fs.wire_code)
-            if self._eager_norm and self.comm is not None and not b.norm_done:
+            if self._eager_norm and self.comm is not None and not b.norm_done and not self.peer:
                 # behind this bucket's collective, on the communicator's aux stream, while the data is in L2
                 if self.sharded:
                     span //= self.world
@@ -645,10 +725,7 @@ class GradSyncEngine:
                     for k, ti in enumerate(late):
                         t = fs.tensors[ti]
                         segs[k].src, segs[k].dst_off, segs[k].numel = fs.acc.data_ptr() + 4 * t.off, t.off, t.numel
-                    _lib.calls.dgs_flatten_accumulate(
-                        segs, len(late), _lib.F32, None, _ptr(fs.wire), _lib.dtype_code(fs.wire_dtype),
-                        _lib.WRITE_WIRE, self.scale * self.unscale, _stream(),
-                    )
+                    self._flatten(fs, b, segs, len(late), _lib.F32, None, _lib.WRITE_WIRE, _stream())
                     for ti in late:
                         fs.in_wire[ti] = True
                 missing = [ti for ti in b.tensors if not have[ti]]
@@ -667,7 +744,20 @@ class GradSyncEngine:
                 b.flushed = True
             self._reduce_ready(fs)
             present.append(have)
-        if self.comm is not None:
+        if self.peer:
+            # every rank's pushes have landed -> each owner sums its rows (rank order) and leaves the per-CTA sums of
+            # squares of its reduced slice in the bucket's norm slots
+            assert self.peers is not None
+            self.peers.check()
+            stream = _stream()
+            self.peers.barrier(_peer.S_PUSHED, stream)
+            for fs in self.sets:
+                isz = fs.wire.element_size()
+                for b in fs.buckets:
+                    _lib.calls.dgs_peer_reduce(_ptr(fs.wire, b.begin * isz), fs.wire_code, (b.end - b.begin) // self.world, self.world,
+                                               self.comm.rank, _ptr(self._partials, 4 * b.norm_off), stream)  # type: ignore
+                    b.norm_done = True
+        elif self.comm is not None:
             self.comm.wait()
         # in-place edits of the gradient views by user code (clip_grad_value_, manual scaling, ...) bump the
         # wire tensors' autograd version; the kernels never do.  total_norm() uses it to notice stale partials.
@@ -685,7 +775,10 @@ class GradSyncEngine:
                     and all(b.norm_done for fs in self.sets for b in fs.buckets))
         n_bucket_slots = self._partials.numel() - self._bucket_partials_base
         bucket_slots = _ptr(self._partials, 4 * self._bucket_partials_base)
-        if self.sharded:
+        if self.peer:
+            # the owner reduction already wrote the partials of my slices: exchange the ranks' sums (8 bytes each way)
+            self.peers.norm_exchange(bucket_slots, n_bucket_slots, _ptr(self._norm), stream)  # type: ignore
+        elif self.sharded:
             if not eager_ok:  # pass 1 over this rank's slice of every bucket
                 for fs in self.sets:
                     isz = fs.wire.element_size()
@@ -708,7 +801,7 @@ class GradSyncEngine:
                 _lib.calls.dgs_l2norm_partial(_ptr(fs.wire), fs.wire_code, fs.total, _ptr(self._partials, 4 * off), stream)
                 off += n
             _lib.calls.dgs_l2norm_final(_ptr(self._partials), off, _ptr(self._norm), stream)
-        self._eager_norm, self._eager_unused, self._norm_requested = True, 0, True
+        self._eager_norm, self._eager_unused, self._norm_requested = not self.peer, 0, True
         self.last_total_norm = self._norm[0]
         return self.last_total_norm
 
@@ -796,9 +889,11 @@ class GradSyncEngine:
         """Which exchange this engine performs per optimizer step (reported by bench.py)."""
         if self.comm is None:
             return "single-gpu (no exchange)"
+        if self.peer:
+            return "peer kernels over NVLink: push-flatten (reduce-scatter) + owner reduce + sliced step pushing parameters (all-gather)"
         if self.sharded:
             return "nccl reduce-scatter + sharded step + all-gather"
-        return "nccl allreduce"
+        return "nccl allreduce" + (" (auto: peer route after two conforming steps)" if self.route == "auto" and self.peers is not None else "")
 
     def step_elements(self) -> int:
         """Elements one optimizer step of this rank covers (all flat sets; 1/N of them with the sharded step)."""
@@ -827,15 +922,24 @@ class GradSyncEngine:
         finally:
             self._inv_scale = None
 
-    def _step_call(self, plain: Any, scaled: Any, *args: Any) -> None:
-        """args = everything up to and including max_norm; the stream goes last."""
-        if self._inv_scale is None:
+    def _step_call(self, plain: Any, scaled: Any, *args: Any, push: Any = None) -> None:
+        """args = everything up to and including max_norm; the stream goes last.  push = (entry point, destination
+        table) on the peer route: the updated parameters are stored to every rank."""
+        if push is not None:
+            fn, table = push
+            self._launch_step(fn, *args, table, self.world, self.comm.rank, _stream())  # type: ignore
+        elif self._inv_scale is None:
             self._launch_step(plain, *args, _stream())
         else:
             self._launch_step(scaled, *args, _ptr(self._inv_scale), _stream())
 
     def _launch_step(self, fn: Any, *args: Any) -> None:
         fn(*args)
+
+    def _push_table(self, fs: _FlatSet, entry: str, lo_bytes: int) -> Any:
+        if not self.peer:
+            return None
+        return getattr(_lib.calls, entry), self.peers.table(f"param{self.sets.index(fs)}", lo_bytes)  # type: ignore
 
     def _fused_step(self, present: List[List[bool]], clip: Optional[ClipRequest]) -> None:
         norm_ptr, max_norm = None, 0.0
@@ -875,6 +979,10 @@ class GradSyncEngine:
     def _after_sharded_step(self) -> None:
         """All-gather the updated parameters, bucket by bucket, in place; the next forward waits for it."""
         assert self.comm is not None
+        if self.peer:
+            # the step kernels stored the new parameters to every rank: wait until everyone's stores have landed here
+            self.peers.barrier(_peer.S_PARAMS, _stream())  # type: ignore
+            return
         for fs in self.sets:
             isz = fs.param.element_size()
             for b in sorted(fs.buckets, key=lambda x: x.begin):
@@ -938,6 +1046,7 @@ class GradSyncEngine:
                         _lib.calls.dgs_step_sgd, _lib.calls.dgs_step_sgd_scaled,
                         _ptr(fs.param, lo * psz), _ptr(buf, lo * psz) if with_momentum else None,
                         fs.dtype_code, _ptr(fs.wire, lo * wsz), fs.wire_code, hi - lo, arr, len(chunk), norm_ptr, max_norm,
+                        push=self._push_table(fs, "dgs_step_sgd_push", lo * psz),
                     )
             if buf is not None:
                 views = fs.state_views["momentum_buffer"]
@@ -1007,5 +1116,6 @@ class GradSyncEngine:
                     _lib.calls.dgs_step_adam, _lib.calls.dgs_step_adam_scaled,
                     _ptr(fs.param, lo * psz), _ptr(m, lo * psz), _ptr(v, lo * psz), fs.dtype_code,
                     _ptr(fs.wire, lo * wsz), fs.wire_code, hi - lo, arr, len(chunk), norm_ptr, max_norm,
+                    push=self._push_table(fs, "dgs_step_adam_push", lo * psz),
                 )
             base += n_t

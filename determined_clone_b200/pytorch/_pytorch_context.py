@@ -463,6 +463,7 @@ class PyTorchTrialContext(_PyTorchReducerContext):
             backward_passes_per_step=backward_passes_per_step,
             fp16_compression=bool(fp16_compression) and self.distributed.size > 1,
             sharded_step=((self._exp_conf or {}).get("optimizations", {}) or {}).get("sharded_step"),
+            route=((self._exp_conf or {}).get("optimizations", {}) or {}).get("grad_sync_route"),
         )
         self.optimizers.append(optimizer)
         return optimizer
@@ -689,24 +690,36 @@ class PyTorchTrialContext(_PyTorchReducerContext):
         parameters = [p for group in optimizer.param_groups for p in group.get("params", [])]
         if scaler is None and self.experimental._auto_amp:
             scaler = self._scaler
-        if eng.sharded:
-            return self._sharded_step(eng, optimizer, parameters, present, clip_grads, scaler)
-        aliased = all(fs.wire_dtype == fs.dtype for fs in eng.sets)
         if scaler is not None and not scaler.is_enabled():
             scaler = None  # a disabled GradScaler is a pass-through in torch too
+        # what the sliced routes (every rank holds and steps 1/N of each bucket) can honour; see GradSyncEngine.route
+        sliceable_call = scaler is None and auto_zero_grads and eng.can_fuse()
+        if eng.sharded:
+            if eng.route == "auto" and not sliceable_call:
+                eng.demote(present)  # back to full gradients on every rank, for good; this step continues below
+            else:
+                return self._sharded_step(eng, optimizer, parameters, present, clip_grads, scaler)
+        aliased = all(fs.wire_dtype == fs.dtype for fs in eng.sets)
         if scaler is not None and eng.can_fuse() and (aliased or clip_grads is None):
+            eng.note_step(False)
             return self._amp_fused_step(eng, optimizer, parameters, present, clip_grads, scaler, auto_zero_grads)
         fused = eng.can_fuse() and scaler is None and (aliased or clip_grads is None)
 
         clip_req: Optional[_gradsync.ClipRequest] = None
         materialized = False
+        pure_clip = clip_grads is None
         if clip_grads is not None or not fused or not auto_zero_grads:
             eng.materialize_grads(present)
             materialized = True
         if clip_grads is not None:
             if self._scaler and self.experimental._auto_amp:
                 self._scaler.unscale_(optimizer)
+            versions = [fs.wire._version for fs in eng.sets]
             clip_req = _run_clip(eng, clip_grads, parameters, defer=fused and aliased)
+            # exactly clip_grad_norm_ over the optimizer's parameters, nothing edited in place, nothing replaced
+            pure_clip = (clip_req.max_norm is not None and versions == [fs.wire._version for fs in eng.sets]
+                         and all(t.param.grad is v for fs, have in zip(eng.sets, present)
+                                 for t, v, ok in zip(fs.tensors, fs.grad_views, have) if ok))
             if aliased:
                 _fold_back_replaced_grads(eng, present)
 
@@ -722,13 +735,17 @@ class PyTorchTrialContext(_PyTorchReducerContext):
                 eng.clear_grads()
         eng.reset_window()
         eng.stepped_in_batch = self._current_batch_idx
+        # the sliced routes cannot show a clip function the whole gradient: only a function that provably never looks
+        # (none at all, or nothing but clip_grad_norm_) lets route "auto" move there
+        eng.note_step(sliceable_call and fused and pure_clip and (clip_grads is None or _is_plain_norm_clip(clip_grads)))
 
     def _sharded_step(self, eng: Any, optimizer: Any, parameters: List[Any], present: Any, clip_grads: Any, scaler: Any) -> None:
         """step_optimizer when the engine reduce-scatters (opt-in sharded step): each rank holds only its slice
         of the averaged gradients, so the only clip function that can be honoured is the one the kernels
         implement -- torch.nn.utils.clip_grad_norm_ over all of the optimizer's parameters."""
         if scaler:
-            raise errors.InvalidExperimentException("sharded_step cannot be combined with a GradScaler")
+            raise errors.InvalidExperimentException(
+                "sharded_step cannot be combined with a GradScaler (set optimizations.grad_sync_route: allreduce)")
         clip_req = None
         if clip_grads is not None:
             eng.materialize_grads(present)
@@ -737,9 +754,11 @@ class PyTorchTrialContext(_PyTorchReducerContext):
             eng.clear_grads()
             if versions != [fs.wire._version for fs in eng.sets]:  # the function edited gradients in place
                 raise errors.InvalidExperimentException(
-                    "with optimizations.sharded_step the clip_grads function may only call "
+                    "with optimizations.sharded_step (or the peer route that grad_sync_route: auto moves to after two "
+                    "optimizer steps whose clip_grads only called clip_grad_norm_) the clip_grads function may only call "
                     "torch.nn.utils.clip_grad_norm_(params, max_norm) on the parameters it is given: every rank "
-                    "holds just its own slice of the averaged gradients"
+                    "holds just its own slice of the averaged gradients. Set optimizations.grad_sync_route: allreduce "
+                    "for a clip function that edits gradients in place on some steps only."
                 )
         eng.fused_step(present, clip_req)
         eng.reset_window()
@@ -779,6 +798,43 @@ def _info_field(name: str) -> int:
     info = _info.get_cluster_info()
     trial = getattr(info, "trial", None) if info is not None else None
     return int(getattr(trial, name, 0) or 0)
+
+
+_PLAIN_CLIP_NAMES = {"torch", "nn", "utils", "clip_grad", "clip_grad_norm_"}
+
+
+def _is_plain_norm_clip(fn: Any) -> bool:
+    """True only if `fn` provably does nothing but call torch.nn.utils.clip_grad_norm_ on its argument -- the one
+    clip function the sliced routes (each rank holds 1/N of the averaged gradients) can serve, because it never gets
+    to READ a gradient.  Decided statically and conservatively: a functools.partial of clip_grad_norm_, or a plain
+    function / lambda / method whose code names nothing outside {torch, nn, utils, clip_grad, clip_grad_norm_}, has no
+    nested code and closes over numbers only (the reference's own example is such a lambda, reference
+    harness/determined/pytorch/_pytorch_context.py:851-853).  Anything else -- a callable object, a function that
+    logs gradient statistics -- answers False and keeps full gradients on every rank."""
+    import functools
+    import types
+
+    real = torch.nn.utils.clip_grad_norm_
+    if isinstance(fn, functools.partial):
+        return fn.func is real and not fn.args and all(isinstance(v, (int, float, bool, type(None))) for v in fn.keywords.values())
+    fn = getattr(fn, "__func__", fn)  # bound method -> function
+    code = getattr(fn, "__code__", None)
+    if not isinstance(fn, types.FunctionType) or code is None:
+        return False
+    if any(isinstance(c, types.CodeType) for c in code.co_consts) or not set(code.co_names) <= _PLAIN_CLIP_NAMES:
+        return False
+    if "clip_grad_norm_" not in code.co_names:
+        return False
+    for cell in fn.__closure__ or ():
+        try:
+            if not isinstance(cell.cell_contents, (int, float)):
+                return False
+        except ValueError:
+            return False
+    g = fn.__globals__
+    expected = {"torch": torch, "nn": torch.nn, "utils": torch.nn.utils, "clip_grad": torch.nn.utils.clip_grad, "clip_grad_norm_": real}
+    root = code.co_names[0]  # the first name loaded is a global (or builtin) lookup; the rest are attribute walks from it
+    return g.get(root) is expected[root]
 
 
 def _fold_back_replaced_grads(eng: _gradsync.GradSyncEngine, present: List[List[bool]]) -> None:

@@ -227,6 +227,119 @@ class FakeCalls:
         v[0] = float(v[0]) ** 0.5 if float(v[0]) >= 0 else float("nan")
 
 
+    # ---- peer exchange (include/dgs.h section 6) --------------------------------------------------------------------
+    # Remote memory is another PROCESS's host memory here, so a "peer pointer" is a token: (owner rank + 1) << 56 plus
+    # the address in the owner's process.  Stores to tokens are queued and delivered when the ranks meet at the next
+    # barrier (all_gather_object over gloo) -- which is also when the real kernels' stores are guaranteed visible.
+    _TAG = 56
+
+    def _peer_state(self) -> Any:
+        if not hasattr(self, "_mail"):
+            self._mail = []  # (dest rank, dest address, dtype code, tensor)
+        return self._mail
+
+    def dgs_peer_export(self, ptr: Any, handle_out: Any, offset_out: Any) -> None:
+        import torch.distributed as dist
+
+        handle_out.raw = bytes([dist.get_rank() + 1]) + bytes(_lib.PEER_HANDLE_BYTES - 1)
+        offset_out._obj.value = _addr(ptr)
+
+    def dgs_peer_open(self, handle: Any, offset: int, out: Any) -> None:
+        out._obj.value = (handle.raw[0] << self._TAG) + offset
+
+    def dgs_peer_close_all(self) -> None:
+        pass
+
+    def dgs_peer_error(self, out: Any) -> None:
+        out._obj.value = 0
+
+    def dgs_peer_error_clear(self) -> None:
+        pass
+
+    def _store(self, token: int, dt: int, data: torch.Tensor) -> None:
+        owner = (token >> self._TAG) - 1
+        if owner < 0:  # a local address
+            _view(token, dt, data.numel()).copy_(data)
+        else:
+            self._peer_state().append((owner, token & ((1 << self._TAG) - 1), dt, data.clone()))
+
+    def _deliver(self) -> None:
+        import torch.distributed as dist
+
+        boxes = [None] * dist.get_world_size()
+        dist.all_gather_object(boxes, self._peer_state())
+        me = dist.get_rank()
+        for box in boxes:
+            for dest, addr, dt, data in box:
+                if dest == me:
+                    _view(addr, dt, data.numel()).copy_(data)
+        self._mail = []
+
+    def dgs_peer_barrier(self, sync: Any, nranks: int, rank: int, slot: int, epoch: int, timeout: float, stream: Any) -> None:
+        self.launches += 1
+        self.log.append(("peer_barrier", slot, epoch))
+        self._deliver()
+
+    def dgs_flatten_push(self, segs: Any, n: int, gdt: int, acc: Any, wire_peers: Any, wdt: int, mode: int, scale: float,
+                         begin: int, span: int, nranks: int, rank: int, stream: Any) -> None:
+        self.launches += 1
+        self.log.append(("flatten_push", n, mode, float(scale)))
+        assert mode & _lib.WRITE_WIRE
+        isz = torch.empty(0, dtype=_TORCH[wdt]).element_size()
+        for k in range(n):
+            s = segs[k]
+            total = _view(s.src, gdt, s.numel).float()
+            if mode & _lib.READ_ACC:
+                total = _view(_addr(acc) + 4 * s.dst_off, _lib.F32, s.numel) + total
+            vals = (total * torch.tensor(scale, dtype=torch.float32)).to(_TORCH[wdt])
+            f0 = s.dst_off
+            while f0 < s.dst_off + s.numel:  # split the tensor at slice boundaries
+                j = (f0 - begin) // span
+                f1 = min(s.dst_off + s.numel, begin + (j + 1) * span)
+                self._store(_addr(wire_peers[j]) + isz * (f0 + (rank - j) * span), wdt, vals[f0 - s.dst_off:f1 - s.dst_off])
+                f0 = f1
+
+    def dgs_peer_reduce(self, bucket: Any, dt: int, span: int, nranks: int, rank: int, partials: Any, stream: Any) -> None:
+        self.launches += 1
+        self.log.append(("peer_reduce", span))
+        rows = _view(bucket, dt, nranks * span).view(nranks, span)
+        acc = rows[0].float().clone()
+        for r in range(1, nranks):
+            acc += rows[r].float()
+        rows[rank].copy_(acc.to(rows.dtype))
+        if span > 0:
+            _view(partials, _lib.F32, 1)[0] = float(rows[rank].double().pow(2).sum())
+
+    def dgs_peer_norm_exchange(self, sync: Any, nranks: int, rank: int, slot: int, epoch: int, partials: Any, n_partials: int,
+                               out: Any, timeout: float, stream: Any) -> None:
+        import torch.distributed as dist
+
+        self.launches += 1
+        self.log.append(("peer_norm_exchange", epoch))
+        mine = torch.tensor([float(_view(partials, _lib.F32, n_partials).double().sum()) if n_partials else 0.0], dtype=torch.float64)
+        parts = [torch.zeros_like(mine) for _ in range(nranks)]
+        dist.all_gather(parts, mine)
+        self._deliver()
+        total = sum(float(p) for p in parts)
+        _view(out, _lib.F32, 1)[0] = total ** 0.5 if total == total and total >= 0 else float("nan")
+
+    def _push_params(self, p: Any, sdt: int, n: int, peers: Any, nranks: int, rank: int) -> None:
+        mine = _view(p, sdt, n)
+        for r in range(nranks):
+            if r != rank:
+                self._store(_addr(peers[r]), sdt, mine)
+
+    def dgs_step_adam_push(self, p, m, v, sdt, g, gdt, n, ranges, n_ranges, total_norm, max_norm, peers, nranks, rank, stream) -> None:
+        assert _addr(peers[rank]) == _addr(p)
+        self.dgs_step_adam(p, m, v, sdt, g, gdt, n, ranges, n_ranges, total_norm, max_norm, stream)
+        self._push_params(p, sdt, n, peers, nranks, rank)
+
+    def dgs_step_sgd_push(self, p, buf, sdt, g, gdt, n, ranges, n_ranges, total_norm, max_norm, peers, nranks, rank, stream) -> None:
+        assert _addr(peers[rank]) == _addr(p)
+        self.dgs_step_sgd(p, buf, sdt, g, gdt, n, ranges, n_ranges, total_norm, max_norm, stream)
+        self._push_params(p, sdt, n, peers, nranks, rank)
+
+
 class _NoStream:
     cuda_stream = 0
 

@@ -26,7 +26,9 @@ def _np(t):
     return t.detach().float().cpu().numpy().copy()
 
 
-def _worker(rank: int, size: int, port: int, zmq_ports, name: str, sharded: bool, small_buckets: bool, out_dir: str) -> None:
+def _worker(rank: int, size: int, port: int, zmq_ports, name: str, sharded, small_buckets: bool, out_dir: str) -> None:
+    route = {False: "allreduce", True: "sharded"}.get(sharded, sharded)  # False / True (round 1's spelling) or a route name
+    sharded = route != "allreduce"
     for p in (str(ROOT), str(ROOT / "tests"), str(ROOT / "tests" / "golden")):
         if p not in sys.path:
             sys.path.insert(0, p)
@@ -94,12 +96,12 @@ def _worker(rank: int, size: int, port: int, zmq_ports, name: str, sharded: bool
                 return {"loss": loss}
 
         pytorch._PyTorchTrialController.pre_execute_hook(17)
-        conf = {"optimizations": {"sharded_step": True}} if sharded else None
+        conf = {"optimizations": {"sharded_step": True}} if route == "sharded" else {"optimizations": {"grad_sync_route": route}}
         ctx = pytorch.PyTorchTrialContext(distributed=dctx, hparams=g.hp, slots_per_trial=size, aggregation_frequency=g.agg,
                                           trial_seed=17, exp_conf=conf)
         trial = Trial(ctx)
         eng = ctx._engines[trial.opt]
-        assert eng.sharded == sharded and eng.comm is not None
+        assert eng.sharded == sharded and eng.comm is not None and eng.peer == (route == "peer")
         ctl = pytorch._PyTorchTrialController(trial, ctx, max_length=g.steps * g.agg, reporting_period=g.agg,
                                               on_report=lambda n, r: reports.append((n, r)))
         ctl.run()
@@ -117,7 +119,11 @@ def _worker(rank: int, size: int, port: int, zmq_ports, name: str, sharded: bool
         for j, i in enumerate(OPT_ORDER_TO_MODEL):
             assert_close(_np(state[j][key]), g.state(g.steps - 1, i, key), "float32", f"{name}: {key} of param {i}")
         kinds = [e[0] for e in fake.log]
-        assert ("reduce_scatter" in kinds) == sharded
+        assert ("reduce_scatter" in kinds) == (route == "sharded")
+        # peer route: the flatten kernel's stores are the transfer, the owner reduces, barriers frame the step
+        assert ("flatten_push" in kinds) == ("peer_reduce" in kinds) == ("peer_barrier" in kinds) == (route == "peer")
+        if route == "peer":
+            assert ("peer_norm_exchange" in kinds) == (g.clip is not None)
         assert any(e[0] == "allreduce" and e[1] > 1 for e in fake.log) != sharded  # sharded: only the norm's one float is all-reduced
         assert "broadcast" in kinds  # rank 0's parameters at wrap_optimizer; the learned bucket order
         if rank == 0:
@@ -129,7 +135,7 @@ def _worker(rank: int, size: int, port: int, zmq_ports, name: str, sharded: bool
         # one allreduce (or reduce-scatter) per bucket per optimizer step, issued in the same order on both ranks
         n_buckets = sum(len(fs.buckets) for fs in eng.sets)
         assert (n_buckets >= 3) == small_buckets
-        per_step = [e for e in fake.log if e[0] in ("allreduce", "reduce_scatter") and e[1] > 1]
+        per_step = [e for e in fake.log if e[0] in ("allreduce", "reduce_scatter", "peer_reduce") and e[1] > 1]
         assert len(per_step) == n_buckets * g.steps
         everyone = dctx.allgather([e[1] for e in per_step])
         assert everyone[0] == everyone[1]
@@ -142,6 +148,7 @@ def _worker(rank: int, size: int, port: int, zmq_ports, name: str, sharded: bool
 
 @pytest.mark.parametrize("name,sharded,small_buckets", [
     ("sgd_n2_a2", False, True), ("adamw_n2_a4_clip", False, False), ("sgd_n2_a2", True, False), ("adamw_n2_a4_clip", True, True),
+    ("sgd_n2_a2", "peer", True), ("adamw_n2_a4_clip", "peer", False), ("adamw_n2_a4_clip", "peer", True),
 ])
 def test_two_rank_scenarios_with_emulated_kernels_and_gloo(tmp_path, name, sharded, small_buckets):
     import torch.multiprocessing as mp
