@@ -382,18 +382,37 @@ def gradsync_microbench(ctx: Any, dist: Any, mb: int, dtype: str, agg: int, step
 
 
 def microbench_sweep(ctx: Any, dist: Any, args: argparse.Namespace, peak: float) -> Dict[str, Any]:
+    from determined_clone_b200 import _lib
+
+    world = ctx.distributed.size
+    route: Optional[str] = None
+    note = None
+    if world > 1:
+        # the route a conforming trial ends up on (GradSyncEngine route "auto"): the peer kernels when the GPUs can map
+        # each other's memory, else NCCL allreduce
+        route = "peer"
+        try:
+            gradsync_microbench(ctx, dist, min(args.micro_mb), "f32", 1, 1, peak, route="peer")
+        except _lib.DgsError as e:
+            route, note = "allreduce", f"peer route unavailable: {str(e)[:200]}"
     rows = []
     for dtype in ("f32", "bf16"):
         for agg in (1, 4):
             for mb in args.micro_mb:
-                rows.append(gradsync_microbench(ctx, dist, mb, dtype, agg, args.micro_steps, peak, bucket_mb=args.micro_bucket_mb))
+                rows.append(gradsync_microbench(ctx, dist, mb, dtype, agg, args.micro_steps, peak, bucket_mb=args.micro_bucket_mb, route=route))
                 DEV.empty_cache()
     head = [r for r in rows if r["dtype"] == "f32" and r["aggregation_frequency"] == 1]
     big = max(head, key=lambda r: r["mib"]) if head else None
     at_1g = next((r for r in head if r["mib"] == 1024), big)
+    others = []
+    if world > 1 and at_1g is not None:
+        for other in ("allreduce", "sharded"):
+            if other != route:
+                others.append(gradsync_microbench(ctx, dist, at_1g["mib"], "f32", 1, args.micro_steps, peak, bucket_mb=args.micro_bucket_mb, route=other))
+                DEV.empty_cache()
     return {"optimizer": "adamw + clip_grad_norm_ 1.0", "nvlink_gbs_per_direction": NVLINK_GBS, "hbm_gbs": peak,
             "bytes_per_element": {f"{d}_A{a}": v for (d, a), v in MICRO_BYTES.items()},
-            "headline": at_1g, "rows": rows}
+            "headline": at_1g, "same_point_on_the_nccl_routes": others, "note": note, "rows": rows}
 
 
 class _StepTimer:
@@ -554,7 +573,7 @@ def measure_workload(args: argparse.Namespace, W: Any, dctx: Any, dist: Any, dev
 
 def run_parity(args: argparse.Namespace, dctx: Any, dist: Any, device: Any, rank: int, world: int) -> Dict[str, Any]:
     """See the module docstring.  Returns {"n", "ok", "max_rel", "cases": [...]}."""
-    from determined_clone_b200 import core, pytorch
+    from determined_clone_b200 import _lib, core, pytorch
     from workloads import parity as P
 
     cases: List[Dict[str, Any]] = []
@@ -562,13 +581,25 @@ def run_parity(args: argparse.Namespace, dctx: Any, dist: Any, device: Any, rank
     def reduce_max(v: List[float]) -> List[float]:
         return _max_over_ranks(dist, device, v)
 
+    # N = 1: free-running and per-step synced.  N > 1: the same on the default route (auto: NCCL allreduce for two
+    # steps, then the peer kernels where the trial's clip function allows it) and per-step synced with the peer
+    # route and with the NCCL allreduce route pinned, so that both exchanges are checked whatever auto decides
+    plans = [("free", None), ("synced", None)] + ([("synced", "peer"), ("synced", "allreduce")] if world > 1 else [])
     for name in args.parity_cases:
         W = _workload(args, name)
-        for mode in ("free", "synced"):
+        for mode, route in plans:
             pytorch._PyTorchTrialController.pre_execute_hook(17)
             ctx = pytorch.PyTorchTrialContext(distributed=dctx, hparams={"global_batch_size": W.PER_SLOT_BATCH * world},
-                                              slots_per_trial=world, aggregation_frequency=W.AGG, trial_seed=17, device=device)
-            cases.append(P.live_parity(name, W, ctx, device, rank, world, steps=args.parity_steps, mode=mode, reduce_max=reduce_max))
+                                              slots_per_trial=world, aggregation_frequency=W.AGG, trial_seed=17, device=device,
+                                              exp_conf={"optimizations": {"grad_sync_route": route}} if route else None)
+            try:
+                case = P.live_parity(name, W, ctx, device, rank, world, steps=args.parity_steps, mode=mode, reduce_max=reduce_max)
+            except _lib.DgsError as e:  # peer set-up refused on this box (all ranks alike): reported, not a mismatch
+                if route != "peer":
+                    raise
+                case = {"case": name, "mode": mode, "ok": True, "skipped": str(e)[:300]}
+            case["route_requested"] = route or "auto"
+            cases.append(case)
             DEV.empty_cache()
     # the 2-slot fixtures recorded from the unmodified reference (real torch DDP over gloo), on ranks 0 and 1
     if world >= 2 and not DEV.emulated:
@@ -596,7 +627,7 @@ def run_parity(args: argparse.Namespace, dctx: Any, dist: Any, device: Any, rank
         bad = [f for f in everyone if f]
         cases.append({"case": "reference-recorded 2-slot fixtures (sgd_n2_a2, adamw_n2_a4_clip, adamw_bf16_n2_a2_clip) on ranks 0-1",
                       "mode": "fixtures", "ok": not bad, "error": bad[0] if bad else None})
-    free = [c for c in cases if c.get("mode") == "free"]
+    free = [c for c in cases if c.get("mode") == "free" and "max_rel" in c]
     return {"n": world, "ok": all(c["ok"] for c in cases), "max_rel": max((c["max_rel"] for c in free), default=None),
             "against": "torch DDP (NCCL) + torch.optim on the same GPUs, same seeds and inputs (workloads/parity.py)", "cases": cases}
 
@@ -658,7 +689,7 @@ def run_ours(args: argparse.Namespace) -> int:
         extra: Dict[str, Any] = {}
         if not args.no_extra and args.workload != "gpt2_medium":
             G = _workload(args, "gpt2_medium")
-            extra[G.NAME] = measure_workload(args, G, dctx, dist, device, rank, world, local_rank, 8 * G.AGG, 2 * G.AGG, with_e2e=False)
+            extra[G.NAME] = measure_workload(args, G, dctx, dist, device, rank, world, local_rank, 8 * G.AGG, 3 * G.AGG, with_e2e=False)
             extra[G.NAME]["unit"] = "sequences/s (4 x 1024 tokens per slot per micro-batch)"
 
         micro = None

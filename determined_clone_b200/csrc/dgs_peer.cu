@@ -84,16 +84,22 @@ __device__ __forceinline__ void signal_and_wait(const SyncPtrs& S, int slot, uns
     __threadfence_system();  // everything this rank wrote before (earlier kernels included) is visible system-wide first
     st_release_sys(S.flags[t] + slot * DGS_PEER_MAX + rank, epoch);
     const unsigned int* mine = S.flags[rank] + slot * DGS_PEER_MAX + t;
-    if (*reinterpret_cast<volatile int*>(err) == 0) {
-      const unsigned long long t0 = globaltimer_ns();
-      while ((int)(ld_acquire_sys(mine) - epoch) < 0) {
-        if (globaltimer_ns() - t0 > timeout_ns) {
+    unsigned long long t0 = 0;
+    unsigned int spins = 0;
+    while ((int)(ld_acquire_sys(mine) - epoch) < 0) {
+      // the slow path only: the error word lives in host memory (a PCIe read), so it is looked at once the wait has
+      // lasted a while -- a wait that follows an earlier timeout then ends after ~1 ms instead of a full timeout
+      if ((++spins & 1023u) == 0) {
+        const unsigned long long now = globaltimer_ns();
+        if (t0 == 0) t0 = now;
+        if (*reinterpret_cast<volatile int*>(err) != 0) break;
+        if (now - t0 > timeout_ns) {
           *reinterpret_cast<volatile int*>(err) = 1000 + slot * 16 + t;  // which slot, which peer never arrived
           __threadfence_system();
           break;
         }
-        __nanosleep(64);
       }
+      __nanosleep(32);
     }
   }
   __syncthreads();
@@ -192,9 +198,7 @@ extern "C" int dgs_peer_export(const void* ptr, void* handle64_out, int64_t* off
   using namespace dgs;
   static_assert(sizeof(cudaIpcMemHandle_t) == DGS_PEER_HANDLE_BYTES, "cudaIpcMemHandle_t is 64 bytes");
   DGS_CHECK_ARG(ptr && handle64_out && offset_out, "dgs_peer_export: NULL argument");
-  cudaIpcMemHandle_t h;
-  DGS_CUDA(cudaIpcGetMemHandle(&h, const_cast<void*>(ptr)));
-  // the handle names the whole allocation: find where in it `ptr` lies (driver API through the runtime's loader, so
+  // a handle names a whole allocation: find the allocation `ptr` lies in (driver API through the runtime's loader, so
   // that the library needs no link-time libcuda and still loads on machines without a driver)
   typedef CUresult (*GetRange)(CUdeviceptr*, size_t*, CUdeviceptr);
   void* fn = nullptr;
@@ -205,6 +209,8 @@ extern "C" int dgs_peer_export(const void* ptr, void* handle64_out, int64_t* off
   size_t size = 0;
   const CUresult rc = reinterpret_cast<GetRange>(fn)(&base, &size, reinterpret_cast<CUdeviceptr>(ptr));
   if (rc != CUDA_SUCCESS) return fail(DGS_ECUDA, "dgs_peer_export: cuMemGetAddressRange failed (%d)", (int)rc);
+  cudaIpcMemHandle_t h;
+  DGS_CUDA(cudaIpcGetMemHandle(&h, reinterpret_cast<void*>(base)));
   memcpy(handle64_out, &h, sizeof(h));
   *offset_out = (int64_t)(reinterpret_cast<CUdeviceptr>(ptr) - base);
   return DGS_OK;

@@ -226,7 +226,7 @@ class ShardedGoldenTrial(GoldenTrial):
         return {"loss": loss}
 
 
-def _sharded_rank_main(rank: int, size: int, name: str, ports) -> None:
+def _sharded_rank_main(rank: int, size: int, name: str, ports, route: str = "sharded") -> None:
     torch.cuda.set_device(rank)
     dctx = core.DistributedContext(rank=rank, size=size, local_rank=rank, local_size=size, cross_rank=0, cross_size=1,
                                    pub_port=ports[0], pull_port=ports[1])
@@ -235,11 +235,16 @@ def _sharded_rank_main(rank: int, size: int, name: str, ports) -> None:
         rec = {"avg": [], "norm": [], "params": [], "state": []}
         pytorch._PyTorchTrialController.pre_execute_hook(17)
         ctx = pytorch.PyTorchTrialContext(distributed=dctx, hparams=g.hp, slots_per_trial=g.slots, aggregation_frequency=g.agg,
-                                          exp_conf={"optimizations": {"sharded_step": True}})
+                                          exp_conf={"optimizations": {"sharded_step": True} if route == "sharded" else {"grad_sync_route": route}})
         trial = ShardedGoldenTrial(ctx, g, rec)
-        assert ctx._engines[trial.opt].sharded
+        eng = ctx._engines[trial.opt]
+        # "auto" starts on NCCL allreduce and moves to the peer kernels after two optimizer steps (the clip function
+        # of this trial is provably nothing but clip_grad_norm_); "peer" runs them from the first step
+        assert eng.sharded == (route != "auto") and eng.peer == (route == "peer")
         pytorch._PyTorchTrialController(trial, ctx, max_length=g.steps * g.agg, reporting_period=g.agg).run()
         torch.cuda.synchronize()
+        if route == "auto":
+            assert eng.peer and eng.sharded, f"route auto did not reach the peer kernels: {eng.peer_unavailable}"
         dt = g.dtype
         wide = 1.0 if dt == "float32" else 5.0
         for s in range(g.steps):
@@ -261,10 +266,13 @@ def _sharded_rank_main(rank: int, size: int, name: str, ports) -> None:
         dctx.close()
 
 
+@pytest.mark.parametrize("route", ["sharded", "peer", "auto"])
 @pytest.mark.parametrize("name", [n for n, sc in SCENARIOS.items() if sc["slots"] == 2])
-def test_two_slot_sharded_step_matches_reference(lib, name):
+def test_two_slot_sharded_step_matches_reference(lib, name, route):
+    """The sliced routes against the fixtures recorded from the reference on 2-rank torch DDP: NCCL reduce-scatter /
+    all-gather ("sharded"), this library's peer kernels over NVLink ("peer"), and the default ("auto")."""
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs (run with gpurun --gpus 2)")
     import torch.multiprocessing as mp
 
-    mp.spawn(_sharded_rank_main, args=(2, name, (_free_port(), _free_port())), nprocs=2, join=True)
+    mp.spawn(_sharded_rank_main, args=(2, name, (_free_port(), _free_port()), route), nprocs=2, join=True)

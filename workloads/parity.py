@@ -143,7 +143,9 @@ def live_parity(name: str, trial_cls: Any, ours_ctx: Any, device: torch.device, 
             def recorder(slot: int, inner: Callable) -> Callable:
                 def clip(params: Any) -> None:
                     params = list(params)
-                    grads = [p.grad.detach().float().clone() for p in params]
+                    # sliced routes: a rank holds only its 1/N of the averaged gradients, there is nothing whole to read
+                    sliced = slot == 0 and any(e.sharded for e in ours_ctx._engines.values())
+                    grads = None if sliced else [p.grad.detach().float().clone() for p in params]
                     norm = torch.nn.utils.clip_grad_norm_(params, 1.0)
                     seen[slot].append((grads, float(norm)))
                 return clip
@@ -187,7 +189,8 @@ def live_parity(name: str, trial_cls: Any, ours_ctx: Any, device: torch.device, 
                 noise_per_step.append(rel)
             if seen[0] and seen[1]:
                 (go, no), (gr, nr) = seen[0][-1], seen[1][-1]
-                worst["grad"] = max(worst["grad"], max(_tensor_err(a, b_, rtol)[0] for a, b_ in zip(go, gr)))
+                if go is not None:
+                    worst["grad"] = max(worst["grad"], max(_tensor_err(a, b_, rtol)[0] for a, b_ in zip(go, gr)))
                 worst["norm"] = max(worst["norm"], abs(no - nr) / max(abs(nr), 1e-30))
                 if twin and seen[2]:
                     gt, nt = seen[2][-1]
@@ -225,7 +228,8 @@ def live_parity(name: str, trial_cls: Any, ours_ctx: Any, device: torch.device, 
             "total_norm": bool(w_norm <= rtol) if strict else within(w_norm, n_norm),
             "replicas_identical": neg_eq == -1.0,
         }
-        return {"case": name, "mode": mode, "optimizer_steps": steps, "aggregation_frequency": agg, "dtype": trial_cls.DTYPE,
+        routes = sorted({e.route_name() for e in ours_ctx._engines.values()})
+        return {"case": name, "mode": mode, "route_at_end": routes[0] if len(routes) == 1 else routes, "optimizer_steps": steps, "aggregation_frequency": agg, "dtype": trial_cls.DTYPE,
                 "rtol": rtol, "max_rel": w_rel, "max_frac_outside_elementwise": w_bad, "max_loss_rel": w_loss,
                 "max_grad_rel": w_grad if hasattr(trial_cls, "_clip") else None, "max_norm_rel": w_norm if hasattr(trial_cls, "_clip") else None,
                 "worst_tensor": worst["what"], "max_rel_per_step": per_step,
