@@ -518,7 +518,12 @@ def measure_workload(args: argparse.Namespace, W: Any, dctx: Any, dist: Any, dev
 
     # ---- roofline of the dominant kernel of the path (fused optimizer step) --------------------------------
     peak, peak_src = measured_peaks()
-    k_ms = sorted(step_kernel_ms)[len(step_kernel_ms) // 2] if step_kernel_ms else None
+    # one optimizer step = one launch (several only when a flat set has more than 24 hyper-parameter ranges): the
+    # launches of each step are added up, the median over the steps is reported
+    n_opt = steps // agg
+    per = len(step_kernel_ms) // n_opt if n_opt and step_kernel_ms and len(step_kernel_ms) % n_opt == 0 else 0
+    per_step = sorted(sum(step_kernel_ms[i * per:(i + 1) * per]) for i in range(n_opt)) if per else []
+    k_ms = per_step[len(per_step) // 2] if per_step else None
     roofline = None
     if k_ms:
         bpe = W.STEP_BYTES_PER_ELEM
@@ -528,7 +533,7 @@ def measure_workload(args: argparse.Namespace, W: Any, dctx: Any, dist: Any, dev
         roofline = {"bound": "hbm", "kernel": W.STEP_KERNEL, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                     "traffic": cap.get("dram_bytes_per_launch"), "traffic_source": cap.get("source"), "peak_source": peak_src,
                     "elements": n_elem, "algorithmic_bytes_per_element": bpe, "algorithmic_bytes_per_launch": bpe * n_elem,
-                    "us_per_launch": k_ms * 1e3, "launches_timed": len(step_kernel_ms),
+                    "us_per_launch": k_ms * 1e3, "launches_timed": len(step_kernel_ms), "launches_per_step": per,
                     "note": "median over the timed region of CUDA events recorded inside libdgs around each launch (dgs_timer_read)"}
 
     out: Dict[str, Any] = {
@@ -772,8 +777,8 @@ def run_torch_gpu(args: argparse.Namespace) -> None:
 def main() -> None:
     # stdout carries exactly one JSON line: keep NCCL's "NCCL version ..." banner (printed to stdout when the image
     # sets NCCL_DEBUG=VERSION) out of it; an explicit NCCL_DEBUG=INFO from the caller is respected
-    if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-        os.environ["NCCL_DEBUG"] = "WARN"
+    if os.environ.get("NCCL_DEBUG", "VERSION").upper() in ("VERSION", "WARN"):
+        os.environ.pop("NCCL_DEBUG", None)  # both levels print the banner
     args = parse()
     if args.impl == "reference":
         run_reference(args)

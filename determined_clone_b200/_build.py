@@ -13,7 +13,7 @@ from typing import List
 
 CSRC = pathlib.Path(__file__).resolve().parent / "csrc"
 LIB = CSRC / "libdgs.so"
-SOURCES = ["dgs_api.cu", "dgs_flatten.cu", "dgs_norm.cu", "dgs_noalloc.cu", "dgs_step.cu", "dgs_metric.cu", "dgs_comm.cu", "dgs_peer.cu"]
+SOURCES = ["dgs_api.cu", "dgs_flatten.cu", "dgs_norm.cu", "dgs_noalloc.cu", "dgs_step.cu", "dgs_metric.cu", "dgs_comm.cu", "dgs_peer.cu", "dgs_direct.cu"]
 NVCC_FLAGS = [
     "-O3",
     "-std=c++17",

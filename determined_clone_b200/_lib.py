@@ -20,7 +20,8 @@ ALIGN_BYTES = 128
 NORM_MAX_PARTIALS = 9472
 NOALLOC_MAX_PARTIALS = 4096
 NOALLOC_MAX_ELEMS = 4096 * 16384
-PEER_MAX, PEER_SLOTS, PEER_HANDLE_BYTES, PEER_SYNC_BYTES = 8, 4, 64, 512
+DIRECT_MAX_SEGS = 512
+PEER_MAX, PEER_SLOTS, PEER_HANDLE_BYTES, PEER_SYNC_BYTES, PEER_MAX_BUCKETS = 8, 4, 64, 512, 128
 
 
 class Seg(ctypes.Structure):
@@ -81,6 +82,10 @@ SIGNATURES = {
     "dgs_step_sgd": [_vp, _vp, _i, _vp, _i, _i64, ctypes.POINTER(SgdRange), _i, _vp, _f, _vp],
     "dgs_step_adam_scaled": [_vp, _vp, _vp, _i, _vp, _i, _i64, ctypes.POINTER(AdamRange), _i, _vp, _f, _vp, _vp],
     "dgs_step_sgd_scaled": [_vp, _vp, _i, _vp, _i, _i64, ctypes.POINTER(SgdRange), _i, _vp, _f, _vp, _vp],
+    "dgs_direct_step_adam": [ctypes.POINTER(Seg), ctypes.POINTER(ctypes.c_int32), _i, _i, _vp, _f, _vp, _vp, _vp, _i,
+                             ctypes.POINTER(AdamRange), _i, _i, _f, _vp, _i, _vp, _vp],
+    "dgs_direct_step_sgd": [ctypes.POINTER(Seg), ctypes.POINTER(ctypes.c_int32), _i, _i, _vp, _f, _vp, _vp, _i,
+                            ctypes.POINTER(SgdRange), _i, _i, _f, _vp, _i, _vp, _vp],
     "dgs_timer_enable": [_i],
     "dgs_timer_read": [_vp, _i, ctypes.POINTER(_i)],
     "dgs_metric_pack": [ctypes.POINTER(ScalarRef), _i, _vp, _vp, _vp],
@@ -106,6 +111,7 @@ SIGNATURES = {
     "dgs_peer_barrier": [ctypes.POINTER(_vp), _i, _i, _i, ctypes.c_uint32, ctypes.c_double, _vp],
     "dgs_flatten_push": [ctypes.POINTER(Seg), _i, _i, _vp, ctypes.POINTER(_vp), _i, _i, _f, _i64, _i64, _i, _i, _vp],
     "dgs_peer_reduce": [_vp, _i, _i64, _i, _i, _vp, _vp],
+    "dgs_peer_reduce_multi": [_vp, _i, ctypes.POINTER(_i64), ctypes.POINTER(_i64), _i, _i, _i, _vp, _i, _vp],
     "dgs_peer_norm_exchange": [ctypes.POINTER(_vp), _i, _i, _i, ctypes.c_uint32, _vp, _i, _vp, ctypes.c_double, _vp],
     "dgs_step_adam_push": [_vp, _vp, _vp, _i, _vp, _i, _i64, ctypes.POINTER(AdamRange), _i, _vp, _f, ctypes.POINTER(_vp), _i, _i, _vp],
     "dgs_step_sgd_push": [_vp, _vp, _i, _vp, _i, _i64, ctypes.POINTER(SgdRange), _i, _vp, _f, ctypes.POINTER(_vp), _i, _i, _vp],

@@ -169,6 +169,66 @@ peer_reduce_kernel(W* __restrict__ bucket, long long span, int nranks, int rank,
   if (threadIdx.x == 0) partials[blockIdx.x] = tot;
 }
 
+// The same reduction over every bucket of a flat buffer in one launch: tiles of all buckets' slices are dealt to a
+// persistent grid, each CTA leaves ONE partial (so the norm needs gridDim.x slots however many buckets there are).
+struct ReduceTable {
+  long long begin[DGS_PEER_MAX_BUCKETS];       // element offset of the bucket in the wire buffer
+  long long span[DGS_PEER_MAX_BUCKETS];        // elements per rank
+  long long tile_start[DGS_PEER_MAX_BUCKETS];  // first tile of the bucket's slice
+  int n;
+  long long tiles;
+};
+
+template <typename W>
+__global__ void __launch_bounds__(kThreads)
+peer_reduce_multi_kernel(W* __restrict__ wire, const __grid_constant__ ReduceTable T, int nranks, int rank,
+                         float* __restrict__ partials, int capacity) {
+  constexpr int VEC = is16<W>::value ? 8 : 4;
+  constexpr int kU = 2;
+  constexpr long long TILE = (long long)kThreads * VEC * kU;
+  __shared__ float red[32];
+  float ss = 0.f;
+  for (long long t = blockIdx.x; t < T.tiles; t += gridDim.x) {
+    int lo = 0, hi = T.n - 1;
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (T.tile_start[mid] <= t) lo = mid; else hi = mid - 1;
+    }
+    W* __restrict__ bucket = wire + T.begin[lo];
+    const long long span = T.span[lo];
+    const long long base = (t - T.tile_start[lo]) * TILE;
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const long long i = base + (long long)(u * kThreads + threadIdx.x) * VEC;
+      if (i < span) {  // span is a multiple of 8: a vector is inside or outside as a whole
+        float acc[VEC], v[DGS_PEER_MAX][VEC];
+#pragma unroll
+        for (int r = 0; r < DGS_PEER_MAX; ++r)
+          if (r < nranks) load_vec<W, VEC, Cache::Stream>(bucket + r * span + i, v[r]);
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) acc[k] = v[0][k];
+#pragma unroll
+        for (int r = 1; r < DGS_PEER_MAX; ++r)
+          if (r < nranks) {
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) acc[k] += v[r][k];
+          }
+        store_vec<W, VEC>(bucket + (long long)rank * span + i, acc);
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) {
+          const float q = to_f32(from_f32<W>(acc[k]));
+          ss = fmaf(q, q, ss);
+        }
+      }
+    }
+  }
+  const float tot = block_sum(ss, red);
+  if (threadIdx.x == 0) partials[blockIdx.x] = tot;
+  // slots this launch does not use must read as zero in the final sum
+  if (blockIdx.x == 0)
+    for (int i = gridDim.x + threadIdx.x; i < capacity; i += kThreads) partials[i] = 0.f;
+}
+
 int check_group(const char* who, int nranks, int rank) {
   DGS_CHECK_ARG(nranks >= 2 && nranks <= DGS_PEER_MAX && rank >= 0 && rank < nranks, "%s: rank %d of %d (at most %d ranks)",
                 who, rank, nranks, DGS_PEER_MAX);
@@ -299,6 +359,46 @@ extern "C" int dgs_peer_reduce(void* bucket, int dtype, int64_t span, int nranks
     case DGS_BF16: peer_reduce_kernel<__nv_bfloat16><<<grid, kThreads, 0, st>>>((__nv_bfloat16*)bucket, span, nranks, rank, partials); break;
     case DGS_F16: peer_reduce_kernel<__half><<<grid, kThreads, 0, st>>>((__half*)bucket, span, nranks, rank, partials); break;
     default: return fail(DGS_EINVAL, "dgs_peer_reduce: bad dtype %d", dtype);
+  }
+  DGS_LAUNCHED();
+  return DGS_OK;
+}
+
+extern "C" int dgs_peer_reduce_multi(void* wire, int dtype, const int64_t* bucket_begin, const int64_t* bucket_span,
+                                     int n_buckets, int nranks, int rank, float* partials, int partials_capacity,
+                                     dgs_stream_t stream) {
+  using namespace dgs;
+  if (int rc = check_group("dgs_peer_reduce_multi", nranks, rank)) return rc;
+  DGS_CHECK_ARG(n_buckets >= 0 && n_buckets <= DGS_PEER_MAX_BUCKETS, "dgs_peer_reduce_multi: n_buckets %d outside [0, %d]", n_buckets,
+                DGS_PEER_MAX_BUCKETS);
+  DGS_CHECK_ARG(partials != nullptr && partials_capacity >= 1, "dgs_peer_reduce_multi: partials scratch is missing");
+  DGS_CHECK_ARG(n_buckets == 0 || (wire && aligned16(wire) && bucket_begin && bucket_span), "dgs_peer_reduce_multi: NULL or misaligned buffer");
+  const int vec = (dtype == DGS_F32) ? 4 : 8;
+  const long long tile = (long long)kThreads * vec * 2;
+  ReduceTable T;
+  T.n = 0;
+  T.tiles = 0;
+  for (int b = 0; b < n_buckets; ++b) {
+    DGS_CHECK_ARG(bucket_begin[b] >= 0 && (bucket_begin[b] & 7) == 0 && bucket_span[b] >= 0 && (bucket_span[b] & 7) == 0,
+                  "dgs_peer_reduce_multi: bucket %d: begin %lld / span %lld must be multiples of 8 elements", b,
+                  (long long)bucket_begin[b], (long long)bucket_span[b]);
+    if (bucket_span[b] == 0) continue;
+    T.begin[T.n] = bucket_begin[b];
+    T.span[T.n] = bucket_span[b];
+    T.tile_start[T.n] = T.tiles;
+    T.tiles += (bucket_span[b] + tile - 1) / tile;
+    ++T.n;
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  long long grid = (long long)sm_count() * 8;
+  if (grid > T.tiles) grid = T.tiles;
+  if (grid > partials_capacity) grid = partials_capacity;
+  if (grid < 1) grid = 1;
+  switch (dtype) {
+    case DGS_F32: peer_reduce_multi_kernel<float><<<(int)grid, kThreads, 0, st>>>((float*)wire, T, nranks, rank, partials, partials_capacity); break;
+    case DGS_BF16: peer_reduce_multi_kernel<__nv_bfloat16><<<(int)grid, kThreads, 0, st>>>((__nv_bfloat16*)wire, T, nranks, rank, partials, partials_capacity); break;
+    case DGS_F16: peer_reduce_multi_kernel<__half><<<(int)grid, kThreads, 0, st>>>((__half*)wire, T, nranks, rank, partials, partials_capacity); break;
+    default: return fail(DGS_EINVAL, "dgs_peer_reduce_multi: bad dtype %d", dtype);
   }
   DGS_LAUNCHED();
   return DGS_OK;

@@ -179,6 +179,7 @@ class _FlatSet:
         self.dtype_code = self.wire_code = 0
         self.acc_ptr: Any = None
         self.wire_ptr: Any = None
+        self.reduce_table: Any = None  # peer route: (begins, spans, first norm slot, slots) of dgs_peer_reduce_multi
         self.peer_wire: Any = None  # (void*)[world]: every rank's pointer to its wire buffer of this set (peer route)
         self.segs_all: Any = None  # prebuilt dgs_seg[len(tensors)] for whole-set launches (single GPU)
         self.params: List[Any] = []  # every parameter of the set, in table order
@@ -752,10 +753,21 @@ class GradSyncEngine:
             stream = _stream()
             self.peers.barrier(_peer.S_PUSHED, stream)
             for fs in self.sets:
-                isz = fs.wire.element_size()
+                if len(fs.buckets) <= _lib.PEER_MAX_BUCKETS:
+                    if fs.reduce_table is None:
+                        bs = sorted(fs.buckets, key=lambda x: x.begin)
+                        fs.reduce_table = ((ctypes.c_int64 * len(bs))(*[b.begin for b in bs]),
+                                           (ctypes.c_int64 * len(bs))(*[(b.end - b.begin) // self.world for b in bs]),
+                                           min(b.norm_off for b in bs), sum(b.norm_n for b in bs))
+                    begins, spans, slot0, n_slots = fs.reduce_table
+                    _lib.calls.dgs_peer_reduce_multi(fs.wire_ptr, fs.wire_code, begins, spans, len(fs.buckets), self.world, self.comm.rank,  # type: ignore
+                                                     _ptr(self._partials, 4 * slot0), n_slots, stream)
+                else:
+                    isz = fs.wire.element_size()
+                    for b in fs.buckets:
+                        _lib.calls.dgs_peer_reduce(_ptr(fs.wire, b.begin * isz), fs.wire_code, (b.end - b.begin) // self.world, self.world,
+                                                   self.comm.rank, _ptr(self._partials, 4 * b.norm_off), stream)  # type: ignore
                 for b in fs.buckets:
-                    _lib.calls.dgs_peer_reduce(_ptr(fs.wire, b.begin * isz), fs.wire_code, (b.end - b.begin) // self.world, self.world,
-                                               self.comm.rank, _ptr(self._partials, 4 * b.norm_off), stream)  # type: ignore
                     b.norm_done = True
         elif self.comm is not None:
             self.comm.wait()
@@ -966,14 +978,17 @@ class GradSyncEngine:
             for i in range(0, len(items), _lib.MAX_RANGES):
                 plan.append((0, fs.total, items[i:i + _lib.MAX_RANGES]))
             return plan
+        # one launch over all of this rank's slices (a model has a handful of buckets; a launch per bucket is what
+        # bounded small models): the kernel skips tiles outside every range
         rank, world = self.comm.rank, self.world  # type: ignore
+        mine: List[Tuple[int, int, Any]] = []
         for b in sorted(fs.buckets, key=lambda x: x.begin):
             span = (b.end - b.begin) // world
             lo, hi = b.begin + rank * span, b.begin + (rank + 1) * span
-            mine = [(max(x, lo), min(y, hi), k) for x, y, k in items if x < hi and y > lo]
-            for i in range(0, len(mine), _lib.MAX_RANGES):
-                chunk = mine[i:i + _lib.MAX_RANGES]
-                plan.append((chunk[0][0], chunk[-1][1], chunk))
+            mine += [(max(x, lo), min(y, hi), k) for x, y, k in items if x < hi and y > lo]
+        for i in range(0, len(mine), _lib.MAX_RANGES):
+            chunk = mine[i:i + _lib.MAX_RANGES]
+            plan.append((chunk[0][0], chunk[-1][1], chunk))
         return plan
 
     def _after_sharded_step(self) -> None:

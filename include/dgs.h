@@ -200,6 +200,36 @@ int dgs_step_sgd_scaled(void* param, void* momentum_buf, int state_dtype, const 
                         int64_t n, const dgs_sgd_range* ranges, int n_ranges, const float* total_norm,
                         float max_norm, const float* inv_scale, dgs_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * 3b. single-launch step for one GPU: flatten + scale + (global L2 norm) + clip + optimizer step
+ *
+ * Replaces, on one slot, the same reference lines as sections 1-3 together
+ * (H/pytorch/_pytorch_context.py:818-825 _average_gradients, :902 clip_grads == clip_grad_norm_,
+ * :914-924 optimizer.step() + zero_grad()) in ONE cooperative kernel that reads the gradient tensors
+ * through the segment table instead of a wire buffer: the averaged gradient
+ * cast((acc + g) * scale) is formed on the fly (acc == NULL: g * scale), so it is never written and
+ * re-read (fp32 AdamW + clip: 32 B/element instead of 40; no clip: 28 instead of 36), and a small
+ * model pays one launch instead of four.  seg_range[i] names the row of `ranges` that holds tensor
+ * i's hyper-parameters (ranges[].begin/end are ignored here); every tensor of the optimizer must be
+ * listed (elements that no segment covers are left untouched).  clip != 0: the global norm of the
+ * averaged gradients is computed first (one grid-wide barrier), written to out_norm[0], and every
+ * gradient is multiplied by min(max_norm / (norm + 1e-6), 1); `partials` is scratch for
+ * partials_capacity floats (>= 1; more allows a larger grid, 148 x 8 is never exceeded).
+ * At most DGS_DIRECT_MAX_SEGS tensors per call; gradient dtype must equal the state dtype.
+ * ---------------------------------------------------------------------------------------------- */
+#define DGS_DIRECT_MAX_SEGS 512
+
+int dgs_direct_step_adam(const dgs_seg* segs, const int32_t* seg_range, int n_segs, int grad_dtype,
+                         const float* acc, float scale, void* param, void* exp_avg, void* exp_avg_sq,
+                         int state_dtype, const dgs_adam_range* ranges, int n_ranges, int clip,
+                         float max_norm, float* partials, int partials_capacity, float* out_norm,
+                         dgs_stream_t stream);
+/* momentum_buf may be NULL when every range has momentum == 0 */
+int dgs_direct_step_sgd(const dgs_seg* segs, const int32_t* seg_range, int n_segs, int grad_dtype,
+                        const float* acc, float scale, void* param, void* momentum_buf, int state_dtype,
+                        const dgs_sgd_range* ranges, int n_ranges, int clip, float max_norm,
+                        float* partials, int partials_capacity, float* out_norm, dgs_stream_t stream);
+
 /* Device-side timing of the optimizer kernels (grad-sync us/step without host noise): while enabled, every
  * dgs_step_adam / dgs_step_sgd launch is bracketed by CUDA events recorded inside the call, on the stream it
  * is launched on.  dgs_timer_read synchronises with the last recorded launch, writes the elapsed microseconds
@@ -347,6 +377,13 @@ int dgs_flatten_push(const dgs_seg* segs, int n_segs, int grad_dtype, float* acc
 /* bucket = this rank's wire + bucket_begin.  partials receives dgs_l2norm_grid(span) floats. */
 int dgs_peer_reduce(void* bucket, int dtype, int64_t span, int nranks, int rank, float* partials,
                     dgs_stream_t stream);
+/* dgs_peer_reduce over every bucket of one flat buffer in ONE launch (a model has a handful of buckets; per-bucket
+ * launches are what bounds small models): bucket b is wire[bucket_begin[b] .. + nranks*bucket_span[b]).  Writes one
+ * partial per CTA to partials[0..grid) and zero to the rest of partials[0..partials_capacity). */
+#define DGS_PEER_MAX_BUCKETS 128
+int dgs_peer_reduce_multi(void* wire, int dtype, const int64_t* bucket_begin, const int64_t* bucket_span,
+                          int n_buckets, int nranks, int rank, float* partials, int partials_capacity,
+                          dgs_stream_t stream);
 /* out_norm[0] = sqrt(sum over ranks (in rank order) of sum(partials)); implies a barrier */
 int dgs_peer_norm_exchange(void* const* sync_blocks, int nranks, int rank, int slot, uint32_t epoch,
                            const float* partials, int n_partials, float* out_norm, double timeout_s,

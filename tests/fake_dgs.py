@@ -310,6 +310,17 @@ class FakeCalls:
         if span > 0:
             _view(partials, _lib.F32, 1)[0] = float(rows[rank].double().pow(2).sum())
 
+    def dgs_peer_reduce_multi(self, wire: Any, dt: int, begins: Any, spans: Any, n_buckets: int, nranks: int, rank: int,
+                              partials: Any, capacity: int, stream: Any) -> None:
+        isz = torch.empty(0, dtype=_TORCH[dt]).element_size()
+        _view(partials, _lib.F32, capacity).zero_()
+        total = 0.0
+        for b in range(n_buckets):
+            one = torch.zeros(1, dtype=torch.float32)
+            self.dgs_peer_reduce(_addr(wire) + isz * begins[b], dt, spans[b], nranks, rank, one.data_ptr(), stream)
+            total += float(one[0])
+        _view(partials, _lib.F32, 1)[0] = total
+
     def dgs_peer_norm_exchange(self, sync: Any, nranks: int, rank: int, slot: int, epoch: int, partials: Any, n_partials: int,
                                out: Any, timeout: float, stream: Any) -> None:
         import torch.distributed as dist
@@ -323,21 +334,26 @@ class FakeCalls:
         total = sum(float(p) for p in parts)
         _view(out, _lib.F32, 1)[0] = total ** 0.5 if total == total and total >= 0 else float("nan")
 
-    def _push_params(self, p: Any, sdt: int, n: int, peers: Any, nranks: int, rank: int) -> None:
-        mine = _view(p, sdt, n)
-        for r in range(nranks):
-            if r != rank:
-                self._store(_addr(peers[r]), sdt, mine)
+    def _push_params(self, p: Any, sdt: int, ranges: Any, n_ranges: int, peers: Any, nranks: int, rank: int) -> None:
+        """Only elements inside a range were stepped, and only those are stored to the peers (the gaps between this
+        rank's slices belong to other ranks, whose fresh values must not be overwritten)."""
+        isz = torch.empty(0, dtype=_TORCH[sdt]).element_size()
+        for i in range(n_ranges):
+            b, e = ranges[i].begin, ranges[i].end
+            mine = _view(_addr(p) + isz * b, sdt, e - b)
+            for r in range(nranks):
+                if r != rank:
+                    self._store(_addr(peers[r]) + isz * b, sdt, mine)
 
     def dgs_step_adam_push(self, p, m, v, sdt, g, gdt, n, ranges, n_ranges, total_norm, max_norm, peers, nranks, rank, stream) -> None:
         assert _addr(peers[rank]) == _addr(p)
         self.dgs_step_adam(p, m, v, sdt, g, gdt, n, ranges, n_ranges, total_norm, max_norm, stream)
-        self._push_params(p, sdt, n, peers, nranks, rank)
+        self._push_params(p, sdt, ranges, n_ranges, peers, nranks, rank)
 
     def dgs_step_sgd_push(self, p, buf, sdt, g, gdt, n, ranges, n_ranges, total_norm, max_norm, peers, nranks, rank, stream) -> None:
         assert _addr(peers[rank]) == _addr(p)
         self.dgs_step_sgd(p, buf, sdt, g, gdt, n, ranges, n_ranges, total_norm, max_norm, stream)
-        self._push_params(p, sdt, n, peers, nranks, rank)
+        self._push_params(p, sdt, ranges, n_ranges, peers, nranks, rank)
 
 
 class _NoStream:

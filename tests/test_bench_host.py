@@ -60,7 +60,8 @@ def _check_line(line):
     assert line["gpu_launches"] > 0
     assert line["config"]["workload"] == "cifar10_resnet18_pytorchtrial" and line["config"]["global_batch"] == 8 * line["n_gpus"]
     assert line["parity"]["ok"] and line["parity"]["n"] == line["n_gpus"]
-    assert [c["mode"] for c in line["parity"]["cases"]] == ["free", "synced"]
+    want = [("free", "auto"), ("synced", "auto")] + ([("synced", "peer"), ("synced", "allreduce")] if line["n_gpus"] > 1 else [])
+    assert [(c["mode"], c["route_requested"]) for c in line["parity"]["cases"]] == want
     rows = line["gradsync_microbench"]["rows"]
     assert {(r["dtype"], r["aggregation_frequency"]) for r in rows} == {("f32", 1), ("f32", 4), ("bf16", 1), ("bf16", 4)}
 
