@@ -315,8 +315,12 @@ def _max_over_ranks(dist: Any, device: Any, vals: List[float]) -> List[float]:
     return [float(x) for x in t.tolist()]
 
 
-MICRO_BYTES = {  # algorithmic HBM bytes per element per optimizer step, DESIGN.md section 3 (AdamW + clip)
+# algorithmic HBM bytes per element per optimizer step, DESIGN.md section 3 (AdamW + clip_grad_norm_)
+MICRO_BYTES = {  # several GPUs: the averaged gradient has to exist in memory (the wire buffer) to be exchanged
     ("f32", 1): 8 + 4 + 28, ("f32", 4): 8 + 12 + 12 + 12 + 4 + 28, ("bf16", 1): 4 + 2 + 14, ("bf16", 4): 6 + 10 + 10 + 8 + 2 + 14,
+}
+MICRO_BYTES_1GPU = {  # one GPU: gradients read once for the norm and once by the step (dgs_direct_step_*), no wire buffer
+    ("f32", 1): 4 + 28, ("f32", 4): 8 + 12 + 12 + 8 + 8 + 24, ("bf16", 1): 2 + 14, ("bf16", 4): 6 + 10 + 10 + 6 + 6 + 12,
 }
 
 
@@ -347,15 +351,36 @@ def gradsync_microbench(ctx: Any, dist: Any, mb: int, dtype: str, agg: int, step
     clip.max_norm = 1.0
     st = DEV.stream()
 
-    def step(i: int) -> None:
+    marks: List[List[Any]] = []
+
+    def step(i: int, timed: bool = False) -> None:
+        ev = [DEV.event() for _ in range(5)] if timed else None
+        if ev:
+            ev[0].record(st)
         for m in range(agg):
             eng.begin_pass(final=(m == agg - 1))
             for p, g in zip(params, grads[(i + m) % 2]):
                 p.grad = g  # what autograd leaves behind when backward produces this gradient
             eng.end_pass()
-        present = eng.finish_window()
-        eng.total_norm()
-        eng.fused_step(present, clip)
+        if ev:
+            ev[1].record(st)
+        if eng.direct and eng.can_direct(True):
+            present = eng.finish_window(allow_direct=True)
+            eng.direct_step(present, 1.0)  # one GPU: flatten + norm + clip + step in one launch
+            if ev:
+                ev[2].record(st)
+                ev[3].record(st)
+        else:
+            present = eng.finish_window()
+            if ev:
+                ev[2].record(st)
+            eng.total_norm()
+            if ev:
+                ev[3].record(st)
+            eng.fused_step(present, clip)
+        if ev:
+            ev[4].record(st)
+            marks.append(ev)
         eng.reset_window()
 
     for i in range(3):
@@ -370,12 +395,18 @@ def gradsync_microbench(ctx: Any, dist: Any, mb: int, dtype: str, agg: int, step
     e1.record(st)
     DEV.sync()
     ms = _max_over_ranks(dist, dev, [e0.elapsed_time(e1) / steps])[0]
-    hbm_bytes = MICRO_BYTES[(dtype, agg)] * n
+    # where the time goes (two more steps with events between the phases; not part of the timed region above)
+    for i in range(2):
+        step(i, timed=True)
+    DEV.sync()
+    names = ["flatten_all_passes", "finish_window(exchange)", "norm", "step(+param exchange)"]
+    phases = {nm: round(min(ev[k].elapsed_time(ev[k + 1]) for ev in marks) * 1e3, 1) for k, nm in enumerate(names)}
+    hbm_bytes = (MICRO_BYTES if world > 1 else MICRO_BYTES_1GPU)[(dtype, agg)] * n
     t_hbm = hbm_bytes / (peak_gbs * 1e9)
     t_nvl = (2 * (world - 1) / world * isz * n) / (NVLINK_GBS * 1e9) if world > 1 else 0.0
     out = {"mib": mb, "dtype": dtype, "aggregation_frequency": agg, "route": eng.route_name(), "us_per_step": ms * 1e3,
            "roofline_us": max(t_hbm, t_nvl) * 1e6, "frac": max(t_hbm, t_nvl) / (ms * 1e-3) if ms > 0 else None,
-           "bound": "nvlink" if t_nvl > t_hbm else "hbm"}
+           "bound": "nvlink" if t_nvl > t_hbm else "hbm", "phases_us": phases}
     eng.close()
     del eng, opt, params, grads
     return out
@@ -411,7 +442,7 @@ def microbench_sweep(ctx: Any, dist: Any, args: argparse.Namespace, peak: float)
                 others.append(gradsync_microbench(ctx, dist, at_1g["mib"], "f32", 1, args.micro_steps, peak, bucket_mb=args.micro_bucket_mb, route=other))
                 DEV.empty_cache()
     return {"optimizer": "adamw + clip_grad_norm_ 1.0", "nvlink_gbs_per_direction": NVLINK_GBS, "hbm_gbs": peak,
-            "bytes_per_element": {f"{d}_A{a}": v for (d, a), v in MICRO_BYTES.items()},
+            "bytes_per_element": {f"{d}_A{a}": v for (d, a), v in (MICRO_BYTES if world > 1 else MICRO_BYTES_1GPU).items()},
             "headline": at_1g, "same_point_on_the_nccl_routes": others, "note": note, "rows": rows}
 
 

@@ -179,6 +179,10 @@ class _FlatSet:
         self.dtype_code = self.wire_code = 0
         self.acc_ptr: Any = None
         self.wire_ptr: Any = None
+        # single GPU: the final pass's gradients, kept (not yet flattened) until step_optimizer shows whether the
+        # single-launch step can take them (dgs_direct_step_*): (gradient tensors, accumulator already holds earlier passes)
+        self.deferred: Optional[Tuple[List[torch.Tensor], bool]] = None
+        self.seg_range: Any = None  # (int32)[len(tensors)]: hyper-parameter row of every tensor, for the direct step
         self.reduce_table: Any = None  # peer route: (begins, spans, first norm slot, slots) of dgs_peer_reduce_multi
         self.peer_wire: Any = None  # (void*)[world]: every rank's pointer to its wire buffer of this set (peer route)
         self.segs_all: Any = None  # prebuilt dgs_seg[len(tensors)] for whole-set launches (single GPU)
@@ -259,6 +263,11 @@ class GradSyncEngine:
         self.sliceable = sliceable
         self.sharded = self.route in ("sharded", "peer")  # this rank holds (and steps) only its slice of every bucket
         self.peer = self.route == "peer"                   # ... exchanged by the peer kernels instead of NCCL
+        # One GPU: flatten + norm + clip + step as ONE kernel reading the gradient tensors in place (csrc/dgs_direct.cu)
+        # whenever the optimizer step is ours and nothing needs the averaged gradients in memory; DGS_DIRECT=0 keeps
+        # the three-kernel path (flatten -> wire, norm, step).
+        self.direct = comm is None and self._fused_kind is not None and _os.environ.get("DGS_DIRECT", "1") != "0"
+        self._direct_clip: Optional[Tuple[bool, float]] = None  # set for the duration of direct_step()
         self.peers: Optional[_peer.PeerGroup] = None
         self.peer_unavailable: Optional[str] = None  # why peer set-up failed, if it did
         self._conforming_steps = 0
@@ -502,9 +511,14 @@ class GradSyncEngine:
         if not to_wire and fs.acc is None:
             fs.acc = torch.zeros(fs.total, dtype=torch.float32, device=self.device)
             fs.acc_ptr = _ptr(fs.acc)
-        mode = (_lib.READ_ACC if state else 0) | (_lib.WRITE_WIRE if to_wire else 0)
-        _lib.calls.dgs_flatten_accumulate(segs, len(tensors), fs.dtype_code, fs.acc_ptr, fs.wire_ptr, fs.wire_code, mode,
-                                          self.scale * self.unscale, _stream())
+        if to_wire and self.direct and len(tensors) <= _lib.DIRECT_MAX_SEGS and fs.wire_dtype == fs.dtype:
+            # leave the gradients where they are (the segment table points at them): step_optimizer decides between the
+            # single-launch step and this flatten (flush_deferred)
+            fs.deferred = (grads, bool(state))
+        else:
+            mode = (_lib.READ_ACC if state else 0) | (_lib.WRITE_WIRE if to_wire else 0)
+            _lib.calls.dgs_flatten_accumulate(segs, len(tensors), fs.dtype_code, fs.acc_ptr, fs.wire_ptr, fs.wire_code, mode,
+                                              self.scale * self.unscale, _stream())
         flags = fs.in_wire if to_wire else fs.in_window
         for i in range(len(tensors)):
             flags[i] = True
@@ -681,8 +695,26 @@ class GradSyncEngine:
             self._next_launch += 1
 
     # ---- step ---------------------------------------------------------------------------------------
-    def finish_window(self) -> List[List[bool]]:
-        """Make every wire slice final (stragglers that never came through a final-pass hook), issue the
+    def has_deferred(self) -> bool:
+        return any(fs.deferred is not None for fs in self.sets)
+
+    def flush_deferred(self) -> None:
+        """Run the flatten that _flush_whole_set left pending: the averaged gradients are needed in the wire buffer
+        after all (a clip function that looks at them, a GradScaler, an optimizer whose step stays in torch)."""
+        for fs in self.sets:
+            if fs.deferred is None:
+                continue
+            _, read_acc = fs.deferred
+            mode = (_lib.READ_ACC if read_acc else 0) | _lib.WRITE_WIRE
+            _lib.calls.dgs_flatten_accumulate(fs.segs_all, len(fs.tensors), fs.dtype_code, fs.acc_ptr, fs.wire_ptr, fs.wire_code, mode,
+                                              self.scale * self.unscale, _stream())
+            fs.deferred = None
+
+    def finish_window(self, allow_direct: bool = False) -> List[List[bool]]:
+        """allow_direct: the caller will either call direct_step() or flush_deferred() itself; otherwise pending
+        gradients are flattened here, so that everything below finds the wire buffer complete.
+
+        Make every wire slice final (stragglers that never came through a final-pass hook), issue the
         remaining allreduces and make the compute stream wait for them.  Returns, per set, which tensors
         received any gradient in this window."""
         for p in self._frozen_at_wrap:
@@ -710,6 +742,8 @@ class GradSyncEngine:
                     )
         present: List[List[bool]] = []
         self.last_total_norm = None
+        if not allow_direct or any(t.param.grad is not None for fs in self.sets if fs.deferred is not None for t in fs.tensors):
+            self.flush_deferred()  # (also when gradients appeared outside context.backward(): they go through the accumulator)
         for si, fs in enumerate(self.sets):
             for bi, b in enumerate(fs.buckets):
                 grads = self._collect(fs, b)  # gradients produced outside context.backward()
@@ -841,6 +875,8 @@ class GradSyncEngine:
                 self._eager_norm = False  # nobody clips by norm any more
         self._norm_slots_valid, self._norm_requested = True, False
         self._next_launch = 0
+        for fs in self.sets:
+            fs.deferred = None
         if self._pending_order is not None:
             self._launch_order, self._pending_order = self._pending_order, None
         for fs in self.sets:
@@ -933,6 +969,49 @@ class GradSyncEngine:
             self._fused_step(present, clip)
         finally:
             self._inv_scale = None
+
+    def can_direct(self, clip: bool) -> bool:
+        """Whether the pending gradients can go through the single-launch step: every flat set deferred, and -- with
+        clipping -- one set only (the norm is global; the kernel sees one set)."""
+        return bool(self.sets) and all(fs.deferred is not None for fs in self.sets) and (not clip or len(self.sets) == 1)
+
+    def direct_step(self, present: List[List[bool]], max_norm: Optional[float]) -> None:
+        """flatten + (norm + clip) + optimizer step of the pending gradients in one kernel per flat set."""
+        assert self._fused_kind is not None and self.can_direct(max_norm is not None)
+        self._direct_clip = (max_norm is not None, float(max_norm or 0.0))
+        try:
+            self._fused_step(present, None)
+        finally:
+            self._direct_clip = None
+            for fs in self.sets:
+                fs.deferred = None
+        if max_norm is not None:
+            self.last_total_norm = None
+
+    def _leave_direct(self, norm_ptr: Any, max_norm: float) -> Tuple[Any, float]:
+        """The single-launch step does not fit after all (groups with and without momentum, more hyper-parameter rows
+        than a launch takes): flatten now and continue on the three-kernel path with the same clipping."""
+        self.flush_deferred()
+        if self._direct_clip is not None and self._direct_clip[0]:
+            self.total_norm()
+            return _ptr(self._norm), self._direct_clip[1]
+        return norm_ptr, max_norm
+
+    def _direct_launch(self, fs: _FlatSet, entry: str, runs: List[Any], arr: Any, state_ptrs: List[Any]) -> None:
+        """runs[k] = (begin, end, key, tensors) is row k of `arr`."""
+        if fs.seg_range is None:
+            fs.seg_range = (ctypes.c_int32 * len(fs.tensors))()
+        for k, run in enumerate(runs):
+            for t in run[3]:
+                fs.seg_range[t.index] = k
+        _, read_acc = fs.deferred  # type: ignore
+        clip, max_norm = self._direct_clip  # type: ignore
+        n0 = self._partials.numel()
+        getattr(_lib.calls, entry)(
+            fs.segs_all, fs.seg_range, len(fs.tensors), fs.dtype_code, fs.acc_ptr if read_acc else None, self.scale * self.unscale,
+            _ptr(fs.param), *state_ptrs, fs.dtype_code, arr, len(runs), 1 if clip else 0, max_norm,
+            _ptr(self._partials), n0, _ptr(self._norm), _stream(),
+        )
 
     def _step_call(self, plain: Any, scaled: Any, *args: Any, push: Any = None) -> None:
         """args = everything up to and including max_norm; the stream goes last.  push = (entry point, destination
@@ -1043,20 +1122,25 @@ class GradSyncEngine:
 
                 runs = self._ranges(fs, have, key)
             psz, wsz = fs.param.element_size(), fs.wire.element_size()
+            if fs.deferred is not None:
+                kinds = {groups[r[2][0]]["momentum"] != 0 for r in runs}
+                if self._direct_clip is not None and everyone and len(kinds) == 1 and len(runs) <= _lib.MAX_RANGES:
+                    arr = (_lib.SgdRange * len(runs))()
+                    for k, (b, e, (gi, first), _) in enumerate(runs):
+                        self._fill_sgd_range(arr[k], b, e, groups[gi], first)
+                    self._direct_launch(fs, "dgs_direct_step_sgd", runs, arr, [_ptr(buf) if True in kinds else None])
+                    runs_to_launch: List[Any] = []
+                else:
+                    norm_ptr, max_norm = self._leave_direct(norm_ptr, max_norm)
+                    runs_to_launch = runs
+            else:
+                runs_to_launch = runs
             for with_momentum in (True, False):
-                sel = [(r[0], r[1], r[2]) for r in runs if (groups[r[2][0]]["momentum"] != 0) == with_momentum]
+                sel = [(r[0], r[1], r[2]) for r in runs_to_launch if (groups[r[2][0]]["momentum"] != 0) == with_momentum]
                 for lo, hi, chunk in self._step_plan(fs, sel):
                     arr = (_lib.SgdRange * len(chunk))()
                     for k, (b, e, (gi, first)) in enumerate(chunk):
-                        g, r = groups[gi], arr[k]
-                        r.begin, r.end = b - lo, e - lo
-                        r.lr, r.momentum = float(g["lr"]), float(g["momentum"])
-                        r.dampening, r.weight_decay = float(g["dampening"]), float(g["weight_decay"])
-                        r.flags = (
-                            (_lib.SGD_NESTEROV if g["nesterov"] else 0)
-                            | (_lib.SGD_FIRST_STEP if first else 0)
-                            | (_lib.OPT_MAXIMIZE if g.get("maximize") else 0)
-                        )
+                        self._fill_sgd_range(arr[k], b - lo, e - lo, groups[gi], first)
                     self._step_call(
                         _lib.calls.dgs_step_sgd, _lib.calls.dgs_step_sgd_scaled,
                         _ptr(fs.param, lo * psz), _ptr(buf, lo * psz) if with_momentum else None,
@@ -1070,6 +1154,30 @@ class GradSyncEngine:
                         for t in ts:
                             self.optimizer.state[t.param]["momentum_buffer"] = views[t.index]
                 fs.steady = everyone
+
+    @staticmethod
+    def _fill_sgd_range(r: Any, begin: int, end: int, g: Dict[str, Any], first: bool) -> None:
+        r.begin, r.end = begin, end
+        r.lr, r.momentum = float(g["lr"]), float(g["momentum"])
+        r.dampening, r.weight_decay = float(g["dampening"]), float(g["weight_decay"])
+        r.flags = (
+            (_lib.SGD_NESTEROV if g["nesterov"] else 0)
+            | (_lib.SGD_FIRST_STEP if first else 0)
+            | (_lib.OPT_MAXIMIZE if g.get("maximize") else 0)
+        )
+
+    def _fill_adam_range(self, r: Any, begin: int, end: int, g: Dict[str, Any], step: int) -> None:
+        b1, b2 = (float(x) for x in g["betas"])
+        lr = float(g["lr"])
+        r.begin, r.end = begin, end
+        r.lr, r.beta1, r.beta2 = lr, b1, b2
+        r.eps, r.weight_decay = float(g["eps"]), float(g["weight_decay"])
+        r.step_size = lr / (1 - b1 ** step)
+        r.bias_correction2_sqrt = (1 - b2 ** step) ** 0.5
+        use_decoupled = self._fused_kind == "adamw" or bool(g.get("decoupled_weight_decay"))
+        r.flags = (_lib.ADAM_DECOUPLED_WD if use_decoupled else 0) | (_lib.OPT_MAXIMIZE if g.get("maximize") else 0)
+        if g["weight_decay"] == 0:
+            r.flags |= _lib.ADAM_DECOUPLED_WD  # p *= 1 exactly; skips the L2 add
 
     def _ensure_steps(self) -> torch.Tensor:
         n = sum(len(fs.tensors) for fs in self.sets)
@@ -1112,21 +1220,19 @@ class GradSyncEngine:
                 fs.steady = everyone
                 fs.uniform_step = counts[0] if everyone and len(set(counts)) == 1 else None
             psz, wsz = fs.param.element_size(), fs.wire.element_size()
+            if fs.deferred is not None:
+                if self._direct_clip is not None and everyone and len(runs) <= _lib.MAX_RANGES:
+                    arr = (_lib.AdamRange * len(runs))()
+                    for k, (b, e, (gi, step), _) in enumerate(runs):
+                        self._fill_adam_range(arr[k], b, e, groups[gi], step)
+                    self._direct_launch(fs, "dgs_direct_step_adam", runs, arr, [_ptr(m), _ptr(v)])
+                    runs = []
+                else:
+                    norm_ptr, max_norm = self._leave_direct(norm_ptr, max_norm)
             for lo, hi, chunk in self._step_plan(fs, [(r[0], r[1], r[2]) for r in runs]):
                 arr = (_lib.AdamRange * len(chunk))()
                 for k, (b, e, (gi, step)) in enumerate(chunk):
-                    g, r = groups[gi], arr[k]
-                    b1, b2 = (float(x) for x in g["betas"])
-                    lr = float(g["lr"])
-                    r.begin, r.end = b - lo, e - lo
-                    r.lr, r.beta1, r.beta2 = lr, b1, b2
-                    r.eps, r.weight_decay = float(g["eps"]), float(g["weight_decay"])
-                    r.step_size = lr / (1 - b1 ** step)
-                    r.bias_correction2_sqrt = (1 - b2 ** step) ** 0.5
-                    use_decoupled = decoupled or bool(g.get("decoupled_weight_decay"))
-                    r.flags = (_lib.ADAM_DECOUPLED_WD if use_decoupled else 0) | (_lib.OPT_MAXIMIZE if g.get("maximize") else 0)
-                    if g["weight_decay"] == 0:
-                        r.flags |= _lib.ADAM_DECOUPLED_WD  # p *= 1 exactly; skips the L2 add
+                    self._fill_adam_range(arr[k], b - lo, e - lo, groups[gi], step)
                 self._step_call(
                     _lib.calls.dgs_step_adam, _lib.calls.dgs_step_adam_scaled,
                     _ptr(fs.param, lo * psz), _ptr(m, lo * psz), _ptr(v, lo * psz), fs.dtype_code,

@@ -686,7 +686,7 @@ class PyTorchTrialContext(_PyTorchReducerContext):
                 raise errors.InvalidExperimentException("a CheckpointLoadContext only loads trials; use pytorch.init() to train")
             raise errors.InvalidExperimentException("step_optimizer() needs an optimizer returned by wrap_optimizer()")
 
-        present = eng.finish_window()
+        present = eng.finish_window(allow_direct=True)
         parameters = [p for group in optimizer.param_groups for p in group.get("params", [])]
         if scaler is None and self.experimental._auto_amp:
             scaler = self._scaler
@@ -694,6 +694,20 @@ class PyTorchTrialContext(_PyTorchReducerContext):
             scaler = None  # a disabled GradScaler is a pass-through in torch too
         # what the sliced routes (every rank holds and steps 1/N of each bucket) can honour; see GradSyncEngine.route
         sliceable_call = scaler is None and auto_zero_grads and eng.can_fuse()
+        if eng.has_deferred():
+            # one GPU: the gradients of this window are still where autograd left them.  If nothing needs them in memory
+            # (our optimizer kernel steps, no GradScaler, a clip function that provably never looks) the whole tail --
+            # average, norm, clip, step -- is one kernel over them; otherwise they are flattened now, as before.
+            direct, max_norm = sliceable_call, None
+            if direct and clip_grads is not None:
+                max_norm = _plain_clip_max_norm(eng, clip_grads, parameters) if _is_plain_norm_clip(clip_grads) else None
+                direct = max_norm is not None
+            if direct and eng.can_direct(max_norm is not None):
+                eng.direct_step(present, max_norm)
+                eng.reset_window()
+                eng.stepped_in_batch = self._current_batch_idx
+                return
+            eng.flush_deferred()
         if eng.sharded:
             if eng.route == "auto" and not sliceable_call:
                 eng.demote(present)  # back to full gradients on every rank, for good; this step continues below
@@ -835,6 +849,33 @@ def _is_plain_norm_clip(fn: Any) -> bool:
     expected = {"torch": torch, "nn": torch.nn, "utils": torch.nn.utils, "clip_grad": torch.nn.utils.clip_grad, "clip_grad_norm_": real}
     root = code.co_names[0]  # the first name loaded is a global (or builtin) lookup; the rest are attribute walks from it
     return g.get(root) is expected[root]
+
+
+def _plain_clip_max_norm(eng: _gradsync.GradSyncEngine, clip_grads: Callable, parameters: List[Any]) -> Optional[float]:
+    """max_norm of a clip function that _is_plain_norm_clip vouched for, found by running it with torch's
+    clip_grad_norm_ internals replaced by recorders (the parameters carry no .grad at this point, so it has nothing
+    to touch).  None if it asked for anything but one plain L2 clip (another norm_type, error_if_nonfinite, two
+    calls): the caller then takes the general path."""
+    from torch.nn.utils import clip_grad as tcg
+
+    calls: List[Any] = []
+    real_norm, real_clip = tcg._get_total_norm, tcg._clip_grads_with_norm_
+
+    def total_norm(tensors: Any, norm_type: float = 2.0, error_if_nonfinite: bool = False, foreach: Any = None) -> torch.Tensor:
+        calls.append(("norm", float(norm_type), bool(error_if_nonfinite)))
+        return eng._norm[0]  # the kernel writes the norm here; a plain clip function discards the value anyway
+
+    def clip_with_norm(params: Any, max_norm: float, total: torch.Tensor, foreach: Any = None) -> None:
+        calls.append(("clip", float(max_norm)))
+
+    tcg._get_total_norm, tcg._clip_grads_with_norm_ = total_norm, clip_with_norm  # type: ignore
+    try:
+        clip_grads(parameters)
+    finally:
+        tcg._get_total_norm, tcg._clip_grads_with_norm_ = real_norm, real_clip
+    if len(calls) == 2 and calls[0] == ("norm", 2.0, False) and calls[1][0] == "clip":
+        return calls[1][1]
+    return None
 
 
 def _fold_back_replaced_grads(eng: _gradsync.GradSyncEngine, present: List[List[bool]]) -> None:

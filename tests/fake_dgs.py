@@ -227,6 +227,50 @@ class FakeCalls:
         v[0] = float(v[0]) ** 0.5 if float(v[0]) >= 0 else float("nan")
 
 
+    # ---- single-launch step (include/dgs.h section 3b) -------------------------------------------------------------
+    def _direct(self, kind: str, segs, seg_range, n_segs, gdt, acc, scale, p, states, sdt, ranges, n_ranges, clip, max_norm,
+                partials, cap, out_norm, stream) -> None:
+        self.launches += 1
+        self.log.append(("direct_" + kind, n_segs, int(clip)))
+        dt = _TORCH[sdt]
+        isz = torch.empty(0, dtype=dt).element_size()
+        total_sq = 0.0
+        grads = []
+        for k in range(n_segs):
+            sg = segs[k]
+            g = _view(sg.src, gdt, sg.numel).float()
+            if _addr(acc):
+                g = _view(_addr(acc) + 4 * sg.dst_off, _lib.F32, sg.numel) + g
+            g = (g * torch.tensor(scale, dtype=torch.float32)).to(dt)
+            grads.append(g)
+            total_sq += float(g.double().pow(2).sum())
+        norm = torch.zeros(1, dtype=torch.float32)
+        if clip:
+            norm[0] = total_sq ** 0.5
+            _view(out_norm, _lib.F32, 1)[0] = float(norm[0])
+        for k in range(n_segs):
+            sg = segs[k]
+            one = type(ranges[0])()
+            for f, _t in one._fields_:
+                setattr(one, f, getattr(ranges[seg_range[k]], f))
+            one.begin, one.end = 0, sg.numel
+            arr = (type(one) * 1)(one)
+            ptrs = [_addr(x) + isz * sg.dst_off if _addr(x) else None for x in [p] + list(states)]
+            tn = norm.data_ptr() if clip else None
+            if kind == "adam":
+                self.dgs_step_adam(ptrs[0], ptrs[1], ptrs[2], sdt, grads[k].data_ptr(), sdt, sg.numel, arr, 1, tn, max_norm, stream)
+            else:
+                self.dgs_step_sgd(ptrs[0], ptrs[1], sdt, grads[k].data_ptr(), sdt, sg.numel, arr, 1, tn, max_norm, stream)
+            self.launches -= 1
+
+    def dgs_direct_step_adam(self, segs, seg_range, n_segs, gdt, acc, scale, p, m, v, sdt, ranges, n_ranges, clip, max_norm,
+                             partials, cap, out_norm, stream) -> None:
+        self._direct("adam", segs, seg_range, n_segs, gdt, acc, scale, p, [m, v], sdt, ranges, n_ranges, clip, max_norm, partials, cap, out_norm, stream)
+
+    def dgs_direct_step_sgd(self, segs, seg_range, n_segs, gdt, acc, scale, p, buf, sdt, ranges, n_ranges, clip, max_norm,
+                            partials, cap, out_norm, stream) -> None:
+        self._direct("sgd", segs, seg_range, n_segs, gdt, acc, scale, p, [buf], sdt, ranges, n_ranges, clip, max_norm, partials, cap, out_norm, stream)
+
     # ---- peer exchange (include/dgs.h section 6) --------------------------------------------------------------------
     # Remote memory is another PROCESS's host memory here, so a "peer pointer" is a token: (owner rank + 1) << 56 plus
     # the address in the owner's process.  Stores to tokens are queued and delivered when the ranks meet at the next

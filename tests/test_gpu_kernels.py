@@ -450,3 +450,155 @@ def test_step_kernel_timer(lib):
     assert all(1.0 < out[i] < 1000.0 for i in range(3)), list(out)[:3]
     L.calls.dgs_timer_read(out, 16, ctypes.byref(cnt))
     assert cnt.value == 0  # reading clears the log
+
+
+# ---- single-launch step (dgs_direct_step_*): one kernel == flatten -> norm -> step of the entry points above ----------
+def _direct_case(dt, sizes, misalign, read_acc, seed):
+    rng = np.random.default_rng(seed)
+    offs, total = layout(sizes)
+    holders = [dev(rng.standard_normal(n + misalign) * 0.1, dt) for n in sizes]
+    grads = [h[misalign:] for h in holders]  # misalign=1: sources that are not 16-byte aligned
+    acc = dev(rng.standard_normal(total) * 0.1) if read_acc else None
+    p0 = dev(rng.standard_normal(total) * 0.5, dt)
+    s1 = dev(rng.standard_normal(total) * 0.01, dt)
+    s2 = dev(np.abs(rng.standard_normal(total)) * 1e-3, dt)
+    seg_range = (ctypes.c_int32 * len(sizes))(*[i % 3 for i in range(len(sizes))])
+    return offs, total, grads, acc, p0, s1, s2, seg_range
+
+
+@pytest.mark.parametrize("dt", ["float32", "bfloat16"])
+@pytest.mark.parametrize("read_acc", [False, True])
+@pytest.mark.parametrize("clip", [None, 0.05])
+@pytest.mark.parametrize("misalign", [0, 1])
+def test_direct_step_adam_equals_flatten_norm_step(lib, dt, read_acc, clip, misalign):
+    sizes = SIZES + [300000]
+    offs, total, grads, acc, p0, m0, v0, seg_range = _direct_case(dt, sizes, misalign, read_acc, 11)
+    scale = 0.25
+    hp = [dict(lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.1, step=3),
+          dict(lr=5e-4, betas=(0.8, 0.9), eps=1e-6, weight_decay=0.0, step=1),
+          dict(lr=2e-3, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.01, step=7, decoupled=False, maximize=True)]
+    segs = make_segs(grads, offs)
+    # the three-kernel path on copies
+    p, m, v = p0.clone(), m0.clone(), v0.clone()
+    wire = torch.zeros(total, dtype=TD[dt], device="cuda")
+    mode = L.WRITE_WIRE | (L.READ_ACC if read_acc else 0)
+    L.calls.dgs_flatten_accumulate(segs, len(sizes), CODE[dt], ptr(acc) if read_acc else None, ptr(wire), CODE[dt], mode, scale, stream())
+    partials = torch.zeros(max(L.calls.dgs_l2norm_grid(total), 2048), device="cuda")
+    norm = torch.zeros(1, device="cuda")
+    L.calls.dgs_l2norm(ptr(wire), CODE[dt], total, ptr(partials), ptr(norm), stream())
+    specs = [dict(hp[i % 3], begin=o, end=align_up(o + n)) for i, (o, n) in enumerate(zip(offs, sizes)) if n]
+    for k in range(0, len(specs), L.MAX_RANGES):
+        chunk = specs[k:k + L.MAX_RANGES]
+        L.calls.dgs_step_adam(ptr(p), ptr(m), ptr(v), CODE[dt], ptr(wire), CODE[dt], total, adam_ranges(chunk), len(chunk),
+                              ptr(norm) if clip else None, clip or 0.0, stream())
+    # one launch
+    q, qm, qv = p0.clone(), m0.clone(), v0.clone()
+    out_norm = torch.full((1,), -1.0, device="cuda")
+    rows = adam_ranges([dict(h, begin=0, end=0) for h in hp])
+    L.calls.dgs_direct_step_adam(segs, seg_range, len(sizes), CODE[dt], ptr(acc) if read_acc else None, scale, ptr(q), ptr(qm), ptr(qv),
+                                 CODE[dt], rows, 3, 1 if clip else 0, clip or 0.0, ptr(partials), partials.numel(), ptr(out_norm), stream())
+    torch.cuda.synchronize()
+    tol = STEP_TOL[dt]
+    if clip:
+        np.testing.assert_allclose(float(out_norm), float(norm), rtol=2e-6)
+    else:
+        assert float(out_norm) == -1.0  # no clipping asked: the norm is not computed
+    for a, b, what in ((q, p, "param"), (qm, m, "exp_avg"), (qv, v, "exp_avg_sq")):
+        np.testing.assert_allclose(host(a), host(b), err_msg=what, **tol)
+    # elements that no tensor covers (alignment gaps) are never touched by the single launch
+    covered = np.zeros(total, dtype=bool)
+    for o, n in zip(offs, sizes):
+        covered[o:o + n] = True
+    np.testing.assert_array_equal(host(q)[~covered], host(p0)[~covered])
+    np.testing.assert_array_equal(host(qv)[~covered], host(v0)[~covered])
+
+
+@pytest.mark.parametrize("dt", ["float32", "bfloat16"])
+@pytest.mark.parametrize("variant", ["momentum", "first", "nesterov", "plain"])
+@pytest.mark.parametrize("clip", [None, 0.05])
+def test_direct_step_sgd_equals_flatten_norm_step(lib, dt, variant, clip):
+    sizes = SIZES + [200000]
+    offs, total, grads, acc, p0, b0, _, seg_range = _direct_case(dt, sizes, 0, variant == "first", 12)
+    read_acc = acc is not None
+    scale = 0.5
+    mom = 0.0 if variant == "plain" else 0.9
+    hp = [dict(lr=0.1, momentum=mom, weight_decay=5e-4, nesterov=variant == "nesterov", first=variant == "first"),
+          dict(lr=0.05, momentum=mom and 0.8, dampening=0.1 if variant == "momentum" else 0.0, weight_decay=0.0,
+               nesterov=variant == "nesterov", first=variant == "first", maximize=True),
+          dict(lr=0.01, momentum=mom, weight_decay=1e-2, nesterov=variant == "nesterov", first=variant == "first")]
+    segs = make_segs(grads, offs)
+    p, b = p0.clone(), b0.clone()
+    wire = torch.zeros(total, dtype=TD[dt], device="cuda")
+    L.calls.dgs_flatten_accumulate(segs, len(sizes), CODE[dt], ptr(acc) if read_acc else None, ptr(wire), CODE[dt],
+                                   L.WRITE_WIRE | (L.READ_ACC if read_acc else 0), scale, stream())
+    partials = torch.zeros(max(L.calls.dgs_l2norm_grid(total), 2048), device="cuda")
+    norm = torch.zeros(1, device="cuda")
+    L.calls.dgs_l2norm(ptr(wire), CODE[dt], total, ptr(partials), ptr(norm), stream())
+    specs = [dict(hp[i % 3], begin=o, end=align_up(o + n)) for i, (o, n) in enumerate(zip(offs, sizes)) if n]
+    L.calls.dgs_step_sgd(ptr(p), ptr(b) if mom else None, CODE[dt], ptr(wire), CODE[dt], total, sgd_ranges(specs), len(specs),
+                         ptr(norm) if clip else None, clip or 0.0, stream())
+    q, qb = p0.clone(), b0.clone()
+    out_norm = torch.zeros(1, device="cuda")
+    L.calls.dgs_direct_step_sgd(segs, seg_range, len(sizes), CODE[dt], ptr(acc) if read_acc else None, scale, ptr(q),
+                                ptr(qb) if mom else None, CODE[dt], sgd_ranges([dict(h, begin=0, end=0) for h in hp]), 3,
+                                1 if clip else 0, clip or 0.0, ptr(partials), partials.numel(), ptr(out_norm), stream())
+    torch.cuda.synchronize()
+    tol = STEP_TOL[dt]
+    np.testing.assert_allclose(host(q), host(p), err_msg="param", **tol)
+    np.testing.assert_allclose(host(qb), host(b), err_msg="momentum_buffer", **tol)
+    if clip:
+        np.testing.assert_allclose(float(out_norm), float(norm), rtol=2e-6)
+
+
+def test_direct_step_large_set_reloads_gradients_and_small_grid_of_partials(lib):
+    """More tiles than resident CTAs (the gradients are read a second time after the grid barrier instead of staying in
+    registers), and a partials scratch smaller than the grid the GPU could hold (the grid shrinks to fit it)."""
+    n = (1 << 24) + 40  # 64 MiB of fp32: 8 Ki tiles
+    g = torch.randn(n, device="cuda") * 0.01
+    p0, m0, v0 = torch.randn(n, device="cuda"), torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+    segs = make_segs([g], [0])
+    seg_range = (ctypes.c_int32 * 1)(0)
+    rows = adam_ranges([dict(begin=0, end=0, lr=1e-3, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1, step=1)])
+    want = None
+    for cap in (4096, 7):
+        q, qm, qv = p0.clone(), m0.clone(), v0.clone()
+        partials = torch.zeros(cap, device="cuda")
+        out_norm = torch.zeros(1, device="cuda")
+        L.calls.dgs_direct_step_adam(segs, seg_range, 1, L.F32, None, 1.0, ptr(q), ptr(qm), ptr(qv), L.F32, rows, 1, 1, 1.0,
+                                     ptr(partials), cap, ptr(out_norm), stream())
+        torch.cuda.synchronize()
+        np.testing.assert_allclose(float(out_norm), float(g.double().norm()), rtol=2e-6)
+        if want is None:
+            want = (q, qm, qv)
+        else:
+            for a, b in zip((q, qm, qv), want):
+                np.testing.assert_allclose(host(a), host(b), rtol=2e-6, atol=1e-7)
+    coef = min(1.0 / (float(g.double().norm()) + 1e-6), 1.0)
+    np.testing.assert_allclose(host(want[1]), host(g) * np.float32(coef) * np.float32(0.1), rtol=3e-6, atol=1e-9)
+
+
+def test_adam_step_with_tiny_second_moment(lib):
+    """exp_avg_sq near 1e-16 with eps 1e-8: the denominator is eps-dominated and sqrt(v) sits near 1e-8, where an
+    approximate square root / division (the kernels use sqrt.approx and a fast division) could part from torch's
+    IEEE sequence.  Against the float64 formula at the tolerance of the other step tests, relative to the update."""
+    rng = np.random.default_rng(21)
+    n = 8192
+    p0 = rng.standard_normal(n).astype(np.float32) * 0.02
+    g0 = (rng.standard_normal(n) * 1e-8).astype(np.float32)
+    m0 = (rng.standard_normal(n) * 1e-8).astype(np.float32)
+    v0 = (np.abs(rng.standard_normal(n)) * 1e-16).astype(np.float32)
+    v0[:64] = 1e-38  # about the smallest normal fp32
+    v0[64:128] = 1e-41  # subnormal
+    v0[128:192] = 0.0
+    p, m, v, g = dev(p0), dev(m0), dev(v0), dev(g0)
+    spec = dict(begin=0, end=n, lr=3e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.0, step=5)
+    L.calls.dgs_step_adam(ptr(p), ptr(m), ptr(v), L.F32, ptr(g), L.F32, n, adam_ranges([spec]), 1, None, 0.0, stream())
+    torch.cuda.synchronize()
+    b1, b2, t = 0.9, 0.95, 5
+    m64 = m0.astype(np.float64) + (1 - b1) * (g0.astype(np.float64) - m0)
+    v64 = v0.astype(np.float64) * b2 + (1 - b2) * g0.astype(np.float64) ** 2
+    upd = (3e-4 / (1 - b1 ** t)) * m64 / (np.sqrt(v64) / np.sqrt(1 - b2 ** t) + 1e-8)
+    got_upd = p0.astype(np.float64) - host(p).astype(np.float64)
+    # the update itself (not p, whose rounding would hide it): within 1e-5 of its own magnitude, elementwise
+    np.testing.assert_allclose(got_upd, upd, rtol=1e-5, atol=2e-9)  # atol: one ulp of p ~ 0.02
+    np.testing.assert_allclose(host(v), v64, rtol=2e-6, atol=1e-45)

@@ -1263,7 +1263,7 @@ def test_native_host_loop_equals_the_python_loop(monkeypatch):
 
     def engine():
         eng = G.GradSyncEngine.__new__(G.GradSyncEngine)
-        eng.comm, eng.device, eng.scale, eng.unscale = None, torch.device("cpu"), 0.5, 1.0
+        eng.comm, eng.device, eng.scale, eng.unscale, eng.direct, eng.peer = None, torch.device("cpu"), 0.5, 1.0, False, False
         eng.bucket_bytes, eng.first_bucket_bytes = 0, 64
         eng._final_pass, eng._next_launch, eng._launch_order, eng._eager_norm = True, 0, [], False
         fs = G._FlatSet(torch.float32, torch.device("cpu"))
