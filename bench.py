@@ -366,10 +366,10 @@ def gradsync_microbench(ctx: Any, dist: Any, mb: int, dtype: str, agg: int, step
             ev[1].record(st)
         if eng.direct and eng.can_direct(True):
             present = eng.finish_window(allow_direct=True)
-            eng.direct_step(present, 1.0)  # one GPU: flatten + norm + clip + step in one launch
             if ev:
                 ev[2].record(st)
                 ev[3].record(st)
+            eng.direct_step(present, 1.0)  # one GPU: flatten + norm + clip + step in one launch
         else:
             present = eng.finish_window()
             if ev:
@@ -399,7 +399,7 @@ def gradsync_microbench(ctx: Any, dist: Any, mb: int, dtype: str, agg: int, step
     for i in range(2):
         step(i, timed=True)
     DEV.sync()
-    names = ["flatten_all_passes", "finish_window(exchange)", "norm", "step(+param exchange)"]
+    names = ["flatten_all_passes", "finish_window(exchange)", "norm", "step(+param exchange; one GPU, A=1: the single launch)"]
     phases = {nm: round(min(ev[k].elapsed_time(ev[k + 1]) for ev in marks) * 1e3, 1) for k, nm in enumerate(names)}
     hbm_bytes = (MICRO_BYTES if world > 1 else MICRO_BYTES_1GPU)[(dtype, agg)] * n
     t_hbm = hbm_bytes / (peak_gbs * 1e9)

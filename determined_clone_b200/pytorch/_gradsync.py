@@ -511,7 +511,9 @@ class GradSyncEngine:
         if not to_wire and fs.acc is None:
             fs.acc = torch.zeros(fs.total, dtype=torch.float32, device=self.device)
             fs.acc_ptr = _ptr(fs.acc)
-        if to_wire and self.direct and len(tensors) <= _lib.DIRECT_MAX_SEGS and fs.wire_dtype == fs.dtype:
+        # (only without an accumulator: with one, reading acc + g twice costs what writing and re-reading the wire does,
+        # and the three kernels ran closer to the HBM peak -- measured on GPT-2 medium, bf16, A=4: 1.42 ms against 1.28)
+        if to_wire and not state and self.direct and len(tensors) <= _lib.DIRECT_MAX_SEGS and fs.wire_dtype == fs.dtype:
             # leave the gradients where they are (the segment table points at them): step_optimizer decides between the
             # single-launch step and this flatten (flush_deferred)
             fs.deferred = (grads, bool(state))

@@ -503,12 +503,13 @@ def test_direct_step_adam_equals_flatten_norm_step(lib, dt, read_acc, clip, misa
         np.testing.assert_allclose(float(out_norm), float(norm), rtol=2e-6)
     else:
         assert float(out_norm) == -1.0  # no clipping asked: the norm is not computed
-    for a, b, what in ((q, p, "param"), (qm, m, "exp_avg"), (qv, v, "exp_avg_sq")):
-        np.testing.assert_allclose(host(a), host(b), err_msg=what, **tol)
-    # elements that no tensor covers (alignment gaps) are never touched by the single launch
+    # (the ranged step also walks the alignment gaps behind each tensor, where this test put random values and the
+    # engine keeps zeros; the single launch never touches them)
     covered = np.zeros(total, dtype=bool)
     for o, n in zip(offs, sizes):
         covered[o:o + n] = True
+    for a, b, what in ((q, p, "param"), (qm, m, "exp_avg"), (qv, v, "exp_avg_sq")):
+        np.testing.assert_allclose(host(a)[covered], host(b)[covered], err_msg=what, **tol)
     np.testing.assert_array_equal(host(q)[~covered], host(p0)[~covered])
     np.testing.assert_array_equal(host(qv)[~covered], host(v0)[~covered])
 
@@ -544,8 +545,12 @@ def test_direct_step_sgd_equals_flatten_norm_step(lib, dt, variant, clip):
                                 1 if clip else 0, clip or 0.0, ptr(partials), partials.numel(), ptr(out_norm), stream())
     torch.cuda.synchronize()
     tol = STEP_TOL[dt]
-    np.testing.assert_allclose(host(q), host(p), err_msg="param", **tol)
-    np.testing.assert_allclose(host(qb), host(b), err_msg="momentum_buffer", **tol)
+    covered = np.zeros(total, dtype=bool)
+    for o, n in zip(offs, sizes):
+        covered[o:o + n] = True
+    np.testing.assert_allclose(host(q)[covered], host(p)[covered], err_msg="param", **tol)
+    np.testing.assert_allclose(host(qb)[covered], host(b)[covered], err_msg="momentum_buffer", **tol)
+    np.testing.assert_array_equal(host(q)[~covered], host(p0)[~covered])
     if clip:
         np.testing.assert_allclose(float(out_norm), float(norm), rtol=2e-6)
 

@@ -23,7 +23,8 @@ order (A > 1: the same mathematical sum), or initial parameters moved by one ulp
 reference arm the same way.  Where that disagreement already exceeds rtol (a chaotic configuration; Adam's first
 steps on zero-initialised 16-bit biases, where the update is lr * sign(g) and the sign of a near-zero 16-bit
 gradient is rounding noise) no implementation other than a bit-identical one can be within rtol of the reference,
-and the case passes when this path is no further from the reference than 1.5 x the reference is from its own twin.
+and the case passes when this path is no further from the reference than 1.5 x (per-step synced mode; 4 x when
+free-running, where both distances are draws from a chaotic process) the reference is from its own twin.
 Both numbers are always reported.
 
 Error measure per floating tensor: max |ours - ref| / max |ref|  (tensor-relative), and the fraction of elements
@@ -216,8 +217,11 @@ def live_parity(name: str, trial_cls: Any, ours_ctx: Any, device: torch.device, 
         per_step = vals[len(head):len(head) + steps]
         noise_per_step = vals[len(head) + steps:]
 
+        # free-running arms are two draws from the same chaotic process: the margin over the twin is wider there
+        margin = 1.5 if mode == "synced" else 4.0
+
         def within(x: float, floor: float) -> bool:
-            return bool(x <= rtol or (twin and x <= 1.5 * floor))
+            return bool(x <= rtol or (twin and x <= margin * floor))
 
         # 16-bit gradients: the reference accumulates micro-batches in the parameter dtype, so its own result moves by
         # about 2e-2 of the tensor's largest element when the micro-batches arrive in another order (the twin); this
