@@ -68,6 +68,8 @@ def parse(argv: Optional[List[str]] = None) -> argparse.Namespace:
     ap.add_argument("--parity-cases", nargs="*", default=["cifar_resnet18", "resnet50", "gpt2_medium"])
     ap.add_argument("--parity-steps", type=int, default=10)
     ap.add_argument("--micro-mb", type=int, nargs="*", default=[1, 4, 16, 64, 256, 1024, 2048])
+    ap.add_argument("--micro-dtypes", nargs="*", default=["f32", "bf16"], choices=["f32", "bf16"])
+    ap.add_argument("--micro-aggs", type=int, nargs="*", default=[1, 4])
     ap.add_argument("--micro-only", action="store_true", help="run only the grad-sync microbench and print it")
     ap.add_argument("--micro-bucket-mb", type=int, default=0, help="bucket cap for the microbench (0 = one bucket per flat set)")
     ap.add_argument("--micro-steps", type=int, default=10)
@@ -427,8 +429,8 @@ def microbench_sweep(ctx: Any, dist: Any, args: argparse.Namespace, peak: float)
         except _lib.DgsError as e:
             route, note = "allreduce", f"peer route unavailable: {str(e)[:200]}"
     rows = []
-    for dtype in ("f32", "bf16"):
-        for agg in (1, 4):
+    for dtype in args.micro_dtypes:
+        for agg in args.micro_aggs:
             for mb in args.micro_mb:
                 rows.append(gradsync_microbench(ctx, dist, mb, dtype, agg, args.micro_steps, peak, bucket_mb=args.micro_bucket_mb, route=route))
                 DEV.empty_cache()
@@ -436,7 +438,7 @@ def microbench_sweep(ctx: Any, dist: Any, args: argparse.Namespace, peak: float)
     big = max(head, key=lambda r: r["mib"]) if head else None
     at_1g = next((r for r in head if r["mib"] == 1024), big)
     others = []
-    if world > 1 and at_1g is not None:
+    if world > 1 and at_1g is not None and not args.micro_only:
         for other in ("allreduce", "sharded"):
             if other != route:
                 others.append(gradsync_microbench(ctx, dist, at_1g["mib"], "f32", 1, args.micro_steps, peak, bucket_mb=args.micro_bucket_mb, route=other))

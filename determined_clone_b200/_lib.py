@@ -112,6 +112,7 @@ SIGNATURES = {
     "dgs_flatten_push": [ctypes.POINTER(Seg), _i, _i, _vp, ctypes.POINTER(_vp), _i, _i, _f, _i64, _i64, _i, _i, _vp],
     "dgs_peer_reduce": [_vp, _i, _i64, _i, _i, _vp, _vp],
     "dgs_peer_reduce_multi": [_vp, _i, ctypes.POINTER(_i64), ctypes.POINTER(_i64), _i, _i, _i, _vp, _i, _vp],
+    "dgs_peer_scatter": [ctypes.POINTER(_vp), ctypes.POINTER(_i64), ctypes.POINTER(_i64), _i, _i, _i, _vp],
     "dgs_peer_norm_exchange": [ctypes.POINTER(_vp), _i, _i, _i, ctypes.c_uint32, _vp, _i, _vp, ctypes.c_double, _vp],
     "dgs_step_adam_push": [_vp, _vp, _vp, _i, _vp, _i, _i64, ctypes.POINTER(AdamRange), _i, _vp, _f, ctypes.POINTER(_vp), _i, _i, _vp],
     "dgs_step_sgd_push": [_vp, _vp, _i, _vp, _i, _i64, ctypes.POINTER(SgdRange), _i, _vp, _f, ctypes.POINTER(_vp), _i, _i, _vp],

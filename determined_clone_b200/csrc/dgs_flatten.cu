@@ -212,8 +212,8 @@ int launch_flatten(const dgs_seg* segs, int n_segs, float* acc, void* wire, floa
   // 2 vectors per thread per array measured best on B200 for every dtype mix (gpurun_out/sweep_unroll*.txt:
   // bf16->bf16 0.78 -> 1.00 of the copy peak against 4); DGS_FLAT_UNROLL=1|4 re-runs the sweep.
   const int u = flat_unroll();
-  if (u == 4 && push == nullptr) return launch_flatten_u<G, W, RA, WW, 4>(segs, n_segs, acc, wire, scale, st);
-  if (u == 1 && push == nullptr) return launch_flatten_u<G, W, RA, WW, 1>(segs, n_segs, acc, wire, scale, st);
+  if (u == 4) return launch_flatten_u<G, W, RA, WW, 4>(segs, n_segs, acc, wire, scale, st, push);
+  if (u == 1) return launch_flatten_u<G, W, RA, WW, 1>(segs, n_segs, acc, wire, scale, st, push);
   return launch_flatten_u<G, W, RA, WW, 2>(segs, n_segs, acc, wire, scale, st, push);
 }
 

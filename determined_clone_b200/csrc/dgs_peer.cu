@@ -229,6 +229,49 @@ peer_reduce_multi_kernel(W* __restrict__ wire, const __grid_constant__ ReduceTab
     for (int i = gridDim.x + threadIdx.x; i < capacity; i += kThreads) partials[i] = 0.f;
 }
 
+// All-gather by stores: pieces of this rank's buffer (its slices of every bucket) copied to the same offsets of every
+// other rank's buffer.  One CTA moves one 8 KB tile to ONE destination; consecutive CTAs go to different destinations
+// (rotated by rank), so that the CTAs in flight at any moment load every link evenly.
+struct ScatterTable {
+  long long off[DGS_PEER_MAX_BUCKETS];         // byte offset of the piece (multiple of 16)
+  long long bytes[DGS_PEER_MAX_BUCKETS];       // multiple of 16
+  long long tile_start[DGS_PEER_MAX_BUCKETS];
+  int n;
+  long long tiles;
+};
+struct PeerBases {
+  char* p[DGS_PEER_MAX];
+};
+constexpr long long kScatterTile = (long long)kThreads * 16 * 2;
+
+__global__ void __launch_bounds__(kThreads)
+peer_scatter_kernel(const __grid_constant__ PeerBases B, const __grid_constant__ ScatterTable T, int nranks, int rank) {
+  const long long n_visit = T.tiles * (nranks - 1);
+  for (long long i = blockIdx.x; i < n_visit; i += gridDim.x) {
+    const long long t = i / (nranks - 1);
+    const int dest = (int)((i % (nranks - 1) + rank + 1) % nranks);
+    int lo = 0, hi = T.n - 1;
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (T.tile_start[mid] <= t) lo = mid; else hi = mid - 1;
+    }
+    const long long base = T.off[lo] + (t - T.tile_start[lo]) * kScatterTile;
+    const long long end = T.off[lo] + T.bytes[lo];
+    const char* __restrict__ src = B.p[rank];
+    char* __restrict__ dst = B.p[dest];
+    uint4 v[2];
+    long long at[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      at[u] = base + ((long long)u * kThreads + threadIdx.x) * 16;
+      if (at[u] < end) v[u] = *reinterpret_cast<const uint4*>(src + at[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u)
+      if (at[u] < end) *reinterpret_cast<uint4*>(dst + at[u]) = v[u];
+  }
+}
+
 int check_group(const char* who, int nranks, int rank) {
   DGS_CHECK_ARG(nranks >= 2 && nranks <= DGS_PEER_MAX && rank >= 0 && rank < nranks, "%s: rank %d of %d (at most %d ranks)",
                 who, rank, nranks, DGS_PEER_MAX);
@@ -400,6 +443,41 @@ extern "C" int dgs_peer_reduce_multi(void* wire, int dtype, const int64_t* bucke
     case DGS_F16: peer_reduce_multi_kernel<__half><<<(int)grid, kThreads, 0, st>>>((__half*)wire, T, nranks, rank, partials, partials_capacity); break;
     default: return fail(DGS_EINVAL, "dgs_peer_reduce_multi: bad dtype %d", dtype);
   }
+  DGS_LAUNCHED();
+  return DGS_OK;
+}
+
+extern "C" int dgs_peer_scatter(void* const* bases, const int64_t* piece_off, const int64_t* piece_bytes, int n_pieces,
+                                int nranks, int rank, dgs_stream_t stream) {
+  using namespace dgs;
+  if (int rc = check_group("dgs_peer_scatter", nranks, rank)) return rc;
+  DGS_CHECK_ARG(n_pieces >= 0 && n_pieces <= DGS_PEER_MAX_BUCKETS, "dgs_peer_scatter: n_pieces %d outside [0, %d]", n_pieces,
+                DGS_PEER_MAX_BUCKETS);
+  DGS_CHECK_ARG(bases != nullptr && (n_pieces == 0 || (piece_off && piece_bytes)), "dgs_peer_scatter: NULL argument");
+  PeerBases B;
+  for (int r = 0; r < DGS_PEER_MAX; ++r) B.p[r] = nullptr;
+  for (int r = 0; r < nranks; ++r) {
+    DGS_CHECK_ARG(bases[r] != nullptr && aligned16(bases[r]), "dgs_peer_scatter: buffer of rank %d is NULL or misaligned", r);
+    B.p[r] = static_cast<char*>(bases[r]);
+  }
+  ScatterTable T;
+  T.n = 0;
+  T.tiles = 0;
+  for (int i = 0; i < n_pieces; ++i) {
+    DGS_CHECK_ARG(piece_off[i] >= 0 && (piece_off[i] & 15) == 0 && piece_bytes[i] >= 0 && (piece_bytes[i] & 15) == 0,
+                  "dgs_peer_scatter: piece %d: offset %lld / size %lld must be multiples of 16 bytes", i, (long long)piece_off[i],
+                  (long long)piece_bytes[i]);
+    if (piece_bytes[i] == 0) continue;
+    T.off[T.n] = piece_off[i];
+    T.bytes[T.n] = piece_bytes[i];
+    T.tile_start[T.n] = T.tiles;
+    T.tiles += (piece_bytes[i] + kScatterTile - 1) / kScatterTile;
+    ++T.n;
+  }
+  if (T.tiles == 0) return DGS_OK;
+  const long long visit = T.tiles * (nranks - 1);
+  const long long cap = (long long)sm_count() * grid_mult();
+  peer_scatter_kernel<<<(int)(visit < cap ? visit : cap), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(B, T, nranks, rank);
   DGS_LAUNCHED();
   return DGS_OK;
 }

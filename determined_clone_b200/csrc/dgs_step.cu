@@ -36,9 +36,14 @@ struct ParamDst {
 template <bool PUSH, typename P, int VEC>
 __device__ __forceinline__ void store_param(P* __restrict__ local, const ParamDst& D, long long i, const float (&v)[VEC]) {
   if constexpr (PUSH) {
+    // destinations in an order rotated per CTA: the CTAs in flight then do not all address the same link at once
+    const int r0 = (int)(blockIdx.x % (unsigned)D.n);
 #pragma unroll
-    for (int r = 0; r < DGS_PEER_MAX; ++r)
-      if (r < D.n) store_vec<P, VEC>(static_cast<P*>(D.dst[r]) + i, v);
+    for (int k = 0; k < DGS_PEER_MAX; ++k)
+      if (k < D.n) {
+        const int r = (r0 + k < D.n) ? r0 + k : r0 + k - D.n;
+        store_vec<P, VEC>(static_cast<P*>(D.dst[r]) + i, v);
+      }
   } else {
     store_vec<P, VEC>(local + i, v);
   }
@@ -224,8 +229,8 @@ template <typename P, typename G>
 int launch_adam(void* param, void* ea, void* eas, const void* grad, int64_t n, const Table<AdamHp>& T,
                 const float* tn, float max_norm, const float* inv, const ParamDst* push, cudaStream_t st) {
   // one vector per array per thread (4 loads in flight) measured best; DGS_STEP_UNROLL=2|4 re-runs the sweep
-  if (push == nullptr && step_unroll() == 2) return launch_adam_u<P, G, 2>(param, ea, eas, grad, n, T, tn, max_norm, inv, push, st);
-  if (push == nullptr && step_unroll() == 4) return launch_adam_u<P, G, 4>(param, ea, eas, grad, n, T, tn, max_norm, inv, push, st);
+  if (step_unroll() == 2) return launch_adam_u<P, G, 2>(param, ea, eas, grad, n, T, tn, max_norm, inv, push, st);
+  if (step_unroll() == 4) return launch_adam_u<P, G, 4>(param, ea, eas, grad, n, T, tn, max_norm, inv, push, st);
   return launch_adam_u<P, G, 1>(param, ea, eas, grad, n, T, tn, max_norm, inv, push, st);
 }
 

@@ -49,6 +49,9 @@ MIN_BUCKET_BYTES, MAX_BUCKET_BYTES = 25 << 20, 128 << 20
 # Experiment switch, off by default: flat sets smaller than this many MiB become ONE bucket --
 # one allreduce per step instead of a 1 MiB bucket plus 25 MiB ones -- for launch-bound small models, where each
 # NCCL enqueue costs the host more than the lost overlap costs the GPU.
+# Peer route, parameter exchange: the step kernel stores the new parameters to every rank itself ("fused"), or steps the
+# local slice and a copy kernel spreads it ("split").  DGS_PUSH_MODE picks; see DESIGN section 7 for the measurement.
+_PUSH_SPLIT = _os.environ.get("DGS_PUSH_MODE", "fused") == "split"
 ONE_BUCKET_BELOW_BYTES = int(__import__("os").environ.get("DGS_ONE_BUCKET_BELOW_MB", "0")) << 20
 
 
@@ -183,6 +186,7 @@ class _FlatSet:
         # single-launch step can take them (dgs_direct_step_*): (gradient tensors, accumulator already holds earlier passes)
         self.deferred: Optional[Tuple[List[torch.Tensor], bool]] = None
         self.seg_range: Any = None  # (int32)[len(tensors)]: hyper-parameter row of every tensor, for the direct step
+        self.scatter_table: Any = None  # peer route, split parameter exchange: (offsets, sizes, n) of dgs_peer_scatter
         self.reduce_table: Any = None  # peer route: (begins, spans, first norm slot, slots) of dgs_peer_reduce_multi
         self.peer_wire: Any = None  # (void*)[world]: every rank's pointer to its wire buffer of this set (peer route)
         self.segs_all: Any = None  # prebuilt dgs_seg[len(tensors)] for whole-set launches (single GPU)
@@ -1030,7 +1034,7 @@ class GradSyncEngine:
         fn(*args)
 
     def _push_table(self, fs: _FlatSet, entry: str, lo_bytes: int) -> Any:
-        if not self.peer:
+        if not self.peer or _PUSH_SPLIT:
             return None
         return getattr(_lib.calls, entry), self.peers.table(f"param{self.sets.index(fs)}", lo_bytes)  # type: ignore
 
@@ -1076,7 +1080,17 @@ class GradSyncEngine:
         """All-gather the updated parameters, bucket by bucket, in place; the next forward waits for it."""
         assert self.comm is not None
         if self.peer:
-            # the step kernels stored the new parameters to every rank: wait until everyone's stores have landed here
+            if _PUSH_SPLIT:
+                # the step kernels updated this rank's slices in place: copy them to every other rank
+                for si, fs in enumerate(self.sets):
+                    if fs.scatter_table is None:
+                        bs, isz = sorted(fs.buckets, key=lambda x: x.begin), fs.param.element_size()
+                        spans = [(b.end - b.begin) // self.world for b in bs]
+                        fs.scatter_table = ((ctypes.c_int64 * len(bs))(*[(b.begin + self.comm.rank * sp) * isz for b, sp in zip(bs, spans)]),
+                                            (ctypes.c_int64 * len(bs))(*[sp * isz for sp in spans]), len(bs))
+                    offs, sizes, n = fs.scatter_table
+                    _lib.calls.dgs_peer_scatter(self.peers.table(f"param{si}"), offs, sizes, n, self.world, self.comm.rank, _stream())  # type: ignore
+            # the new parameters were stored to every rank: wait until everyone's stores have landed here
             self.peers.barrier(_peer.S_PARAMS, _stream())  # type: ignore
             return
         for fs in self.sets:

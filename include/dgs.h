@@ -384,6 +384,11 @@ int dgs_peer_reduce(void* bucket, int dtype, int64_t span, int nranks, int rank,
 int dgs_peer_reduce_multi(void* wire, int dtype, const int64_t* bucket_begin, const int64_t* bucket_span,
                           int n_buckets, int nranks, int rank, float* partials, int partials_capacity,
                           dgs_stream_t stream);
+/* All-gather by stores: for every piece i, bytes [piece_off[i], +piece_bytes[i]) of bases[rank] are copied to the same
+ * offsets of bases[r] for every other rank r (offsets and sizes multiples of 16).  The alternative to dgs_step_*_push
+ * for the parameter exchange: dgs_step_* on the local slice, then this. */
+int dgs_peer_scatter(void* const* bases, const int64_t* piece_off, const int64_t* piece_bytes, int n_pieces,
+                     int nranks, int rank, dgs_stream_t stream);
 /* out_norm[0] = sqrt(sum over ranks (in rank order) of sum(partials)); implies a barrier */
 int dgs_peer_norm_exchange(void* const* sync_blocks, int nranks, int rank, int slot, uint32_t epoch,
                            const float* partials, int n_partials, float* out_norm, double timeout_s,

@@ -365,6 +365,15 @@ class FakeCalls:
             total += float(one[0])
         _view(partials, _lib.F32, 1)[0] = total
 
+    def dgs_peer_scatter(self, bases: Any, offs: Any, sizes: Any, n: int, nranks: int, rank: int, stream: Any) -> None:
+        self.launches += 1
+        self.log.append(("peer_scatter", n))
+        for i in range(n):
+            mine = _view(_addr(bases[rank]) + offs[i], _U8, sizes[i])
+            for r in range(nranks):
+                if r != rank:
+                    self._store(_addr(bases[r]) + offs[i], _U8, mine)
+
     def dgs_peer_norm_exchange(self, sync: Any, nranks: int, rank: int, slot: int, epoch: int, partials: Any, n_partials: int,
                                out: Any, timeout: float, stream: Any) -> None:
         import torch.distributed as dist
