@@ -229,8 +229,10 @@ template <typename P, typename G>
 int launch_adam(void* param, void* ea, void* eas, const void* grad, int64_t n, const Table<AdamHp>& T,
                 const float* tn, float max_norm, const float* inv, const ParamDst* push, cudaStream_t st) {
   // one vector per array per thread (4 loads in flight) measured best; DGS_STEP_UNROLL=2|4 re-runs the sweep
-  if (step_unroll() == 2) return launch_adam_u<P, G, 2>(param, ea, eas, grad, n, T, tn, max_norm, inv, push, st);
-  if (step_unroll() == 4) return launch_adam_u<P, G, 4>(param, ea, eas, grad, n, T, tn, max_norm, inv, push, st);
+  // the pushing variant: two vectors per thread measured best at 8 GPUs (profiles/r2_sweep_n8_push_variants.txt)
+  const int u = step_unroll() ? step_unroll() : (push != nullptr ? 2 : 1);
+  if (u == 2) return launch_adam_u<P, G, 2>(param, ea, eas, grad, n, T, tn, max_norm, inv, push, st);
+  if (u == 4) return launch_adam_u<P, G, 4>(param, ea, eas, grad, n, T, tn, max_norm, inv, push, st);
   return launch_adam_u<P, G, 1>(param, ea, eas, grad, n, T, tn, max_norm, inv, push, st);
 }
 
@@ -259,8 +261,9 @@ int launch_sgd_u(void* param, void* buf, const void* grad, int64_t n, const Tabl
 template <typename P, typename G>
 int launch_sgd(void* param, void* buf, const void* grad, int64_t n, const Table<SgdHp>& T,
                const float* tn, float max_norm, const float* inv, const ParamDst* push, cudaStream_t st) {
-  if (push == nullptr && step_unroll() == 2) return launch_sgd_u<P, G, 2>(param, buf, grad, n, T, tn, max_norm, inv, push, st);
-  if (push == nullptr && step_unroll() == 4) return launch_sgd_u<P, G, 4>(param, buf, grad, n, T, tn, max_norm, inv, push, st);
+  const int u = step_unroll() ? step_unroll() : (push != nullptr ? 2 : 1);
+  if (u == 2) return launch_sgd_u<P, G, 2>(param, buf, grad, n, T, tn, max_norm, inv, push, st);
+  if (u == 4) return launch_sgd_u<P, G, 4>(param, buf, grad, n, T, tn, max_norm, inv, push, st);
   return launch_sgd_u<P, G, 1>(param, buf, grad, n, T, tn, max_norm, inv, push, st);
 }
 
