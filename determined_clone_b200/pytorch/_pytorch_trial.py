@@ -106,6 +106,62 @@ def _clone_tensors(obj: Any) -> Any:
     return obj
 
 
+class _BatchFeed:
+    """next() of the training iterator, with the host-to-device copy of the FOLLOWING batch started on a side stream
+    as soon as the current one is handed out, so that it overlaps the current batch's forward and backward instead of
+    preceding the next one (the reference copies at the top of _train_batch, _pytorch_trial.py:883-884, on the
+    compute stream).  Only on a CUDA device with automatic to_device; nothing is fetched beyond the last batch the
+    loop will train."""
+
+    def __init__(self, controller: "_PyTorchTrialController", it: Any) -> None:
+        self.c, self.it = controller, it
+        ctx = controller.context
+        self.on = ctx.device.type == "cuda" and ctx.experimental._auto_to_device and torch.cuda.is_available()
+        self.stream = torch.cuda.Stream(device=ctx.device) if self.on else None
+        self.ahead: Any = None  # (host batch, device batch, copy-done event)
+
+    def _pull(self) -> Any:
+        try:
+            return next(self.it)
+        except StopIteration:
+            self.it = iter(self.c.training_loader)
+            return next(self.it)
+
+    def _stage(self) -> None:
+        host = self._pull()
+        with torch.cuda.stream(self.stream):
+            dev = self.c.context.to_device(host)
+            done = torch.cuda.Event()
+            done.record(self.stream)
+        self.ahead = (host, dev, done)
+
+    @staticmethod
+    def _used_on(data: Any, stream: Any) -> None:
+        if isinstance(data, torch.Tensor):
+            if data.is_cuda:
+                data.record_stream(stream)  # allocated on the copy stream, consumed on the compute stream
+        elif isinstance(data, dict):
+            for v in data.values():
+                _BatchFeed._used_on(v, stream)
+        elif isinstance(data, (list, tuple)):
+            for v in data:
+                _BatchFeed._used_on(v, stream)
+
+    def next(self, more_after: bool) -> Any:
+        if not self.on:
+            return self._pull(), None
+        if self.ahead is None:
+            self._stage()
+        host, dev, done = self.ahead
+        self.ahead = None
+        cur = torch.cuda.current_stream()
+        cur.wait_event(done)
+        self._used_on(dev, cur)
+        if more_after:
+            self._stage()
+        return host, dev
+
+
 class _PyTorchTrialController:
     def __init__(
         self,
@@ -272,18 +328,16 @@ class _PyTorchTrialController:
 
     def _train_loop(self, it: Any, pending: List[Dict[str, Any]], previous: Any, samples: int, t0: float) -> None:
         epoch_len = self.context._epoch_len
+        feed = _BatchFeed(self, it)
         while self.batches_trained < self.max_length:
             batch_idx = self.batches_trained
-            try:
-                batch = next(it)
-            except StopIteration:
-                it = iter(self.training_loader)
-                batch = next(it)
+            # `staged`: the batch already on the device (its copy ran on a side stream during the previous batch)
+            batch, staged = feed.next(more_after=self.batches_trained + 1 < self.max_length)
             self.context._current_batch_idx = batch_idx
             epoch_idx = batch_idx // epoch_len if epoch_len else 0
             if self.callbacks and epoch_len and batch_idx % epoch_len == 0:
                 self._on_epoch_start(epoch_idx)
-            metrics = self._train_batch(batch, epoch_idx, batch_idx)
+            metrics = self._train_batch(batch, epoch_idx, batch_idx, staged=staged)
             if self.context.profiler:
                 self.context.profiler.step()
             samples += self.trial.get_batch_length(batch)
@@ -398,9 +452,11 @@ class _PyTorchTrialController:
             return False
         return self.context._should_communicate_and_update()
 
-    def _train_batch(self, batch: TorchData, epoch_idx: int, batch_idx: int) -> Optional[Dict[str, Any]]:
+    def _train_batch(self, batch: TorchData, epoch_idx: int, batch_idx: int, staged: Any = None) -> Optional[Dict[str, Any]]:
         self.context._loss_ids = {}
-        if self.context.experimental._auto_to_device:
+        if staged is not None:
+            batch = staged
+        elif self.context.experimental._auto_to_device:
             batch = self.context.to_device(batch)
         training_metrics = self.trial.train_batch(batch=batch, epoch_idx=epoch_idx, batch_idx=batch_idx)
         if self._should_update_scaler():
