@@ -149,3 +149,27 @@ def test_entrypoint_dispatch_and_launch(tmp_path):
     missing = subprocess.run([sys.executable, "-m", "determined.exec.launch"], cwd=host, capture_output=True, text=True,
                              env={k: v for k, v in env.items() if k != "DET_EXPERIMENT_CONFIG"})
     assert missing.returncode == 2 and "DET_EXPERIMENT_CONFIG" in missing.stderr
+
+
+def test_horovod_launcher_command_line():
+    """determined.launch.horovod, the reference's default launch layer (harness/determined/launch/horovod.py:205-281):
+    same command line; overrides for horovodrun are accepted and dropped (there is no horovodrun here)."""
+    from determined_clone_b200.launch import horovod
+
+    assert horovod.parse_args(["--autohorovod", "--trial", "model_def:MyTrial"]) == (
+        [], ["python3", "-m", "determined.exec.harness", "model_def:MyTrial"], True)
+    assert horovod.parse_args(["--mpi-args=-v", "--", "python3", "train.py", "--lr", "1"]) == (
+        ["--mpi-args=-v"], ["python3", "train.py", "--lr", "1"], False)
+    for bad in (["--trial", "m:T", "extra"], []):
+        with pytest.raises(SystemExit) as e:
+            horovod.parse_args(bad)
+        assert e.value.code == 1
+
+
+def test_experiment_yaml_that_names_the_horovod_launcher_runs_unchanged(tmp_path):
+    """entrypoint: python3 -m determined.launch.horovod --autohorovod --trial model_def:HostOnlyTrial (one slot): the
+    script runs directly, as under the reference's --autohorovod, and produces the reports of the legacy entrypoint."""
+    host = FIX.parent / "host_only"
+    reports = _run_experiment("horovod.yaml", tmp_path, FIX=host, extra_env={"DET_CHECKPOINT_DIR": str(tmp_path / "ckpts")})
+    assert [r["steps_completed"] for r in reports] == [2, 3, 4, 6]
+    assert [b["loss"] for r in reports for b in r["batch_metrics"]] == [1.5, 1.0, 0.5, 0.0, -0.5, -1.0]
