@@ -1224,10 +1224,14 @@ class GradSyncEngine:
                     cur = st.get("step")
                     mine = self._step_views[base + t.index]
                     if cur is not mine:
-                        if cur is not None:
-                            mine.fill_(float(cur))
+                        # no `step` in the optimizer's state: a fresh optimizer, or state that was cleared
+                        # (optimizer.state.clear(), load_state_dict of an empty state) -> torch restarts from step 0
+                        mine.fill_(float(cur) if cur is not None else 0.0)
                         st["step"] = mine
                     if "exp_avg" not in st:
+                        # ... with zero moments: the flat buffers may still hold the old ones
+                        fs.state_views["exp_avg"][t.index].zero_()
+                        fs.state_views["exp_avg_sq"][t.index].zero_()
                         st["exp_avg"] = fs.state_views["exp_avg"][t.index]
                         st["exp_avg_sq"] = fs.state_views["exp_avg_sq"][t.index]
                 steps[base:base + n_t] += torch.tensor(have, dtype=torch.float32)

@@ -627,7 +627,7 @@ class PyTorchTrialContext(_PyTorchReducerContext):
         if clip_grads is not None:
             if not prefolded and self._scaler and self.experimental._auto_amp:
                 self._scaler.unscale_(optimizer)
-            clip_req = _run_clip(eng, clip_grads, parameters, defer=True)
+            clip_req = _run_clip(eng, clip_grads, parameters, defer=auto_zero_grads and _is_plain_norm_clip(clip_grads))
             _fold_back_replaced_grads(eng, present)
 
         if found is None and st["stage"] is OptState.UNSCALED:
@@ -729,7 +729,10 @@ class PyTorchTrialContext(_PyTorchReducerContext):
             if self._scaler and self.experimental._auto_amp:
                 self._scaler.unscale_(optimizer)
             versions = [fs.wire._version for fs in eng.sets]
-            clip_req = _run_clip(eng, clip_grads, parameters, defer=fused and aliased)
+            # The clip is folded into the optimizer kernel only for a function that provably does nothing else (and when
+            # the gradients are dropped afterwards): anything the function did to the views AFTER clip_grad_norm_, or
+            # a user who keeps p.grad, must see clipped values, as in torch -- then the clip is one more pass, now.
+            clip_req = _run_clip(eng, clip_grads, parameters, defer=fused and aliased and auto_zero_grads and _is_plain_norm_clip(clip_grads))
             # exactly clip_grad_norm_ over the optimizer's parameters, nothing edited in place, nothing replaced
             pure_clip = (clip_req.max_norm is not None and versions == [fs.wire._version for fs in eng.sets]
                          and all(t.param.grad is v for fs, have in zip(eng.sets, present)

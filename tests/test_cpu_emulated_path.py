@@ -718,3 +718,32 @@ def test_parameters_moved_out_of_the_flat_buffer_are_noticed(monkeypatch):
     with pytest.raises(det.errors.InvalidExperimentException, match="no longer lives in the optimizer's flat parameter buffer"):
         ctx.step_optimizer(opt)
     ctx.close()
+
+
+def test_cleared_adam_state_restarts_from_step_zero_with_zero_moments(monkeypatch):
+    """optimizer.state.clear() (or load_state_dict of an empty state) between steps: torch starts over -- step 1, zero
+    moments -- and so must the fused step, whose flat exp_avg / exp_avg_sq buffers still hold the old moments."""
+    fake_dgs.install(monkeypatch)
+    torch.manual_seed(3)
+    base = torch.nn.Sequential(torch.nn.Linear(5, 7), torch.nn.Tanh(), torch.nn.Linear(7, 2))
+    x, y = torch.randn(9, 5), torch.randn(9, 2)
+    ctx = pytorch.PyTorchTrialContext(hparams={"global_batch_size": 9})
+    model = ctx.wrap_model(copy.deepcopy(base))
+    opt = ctx.wrap_optimizer(torch.optim.AdamW(model.parameters(), lr=1e-2, weight_decay=0.1))
+    twin = copy.deepcopy(base)
+    twin_opt = torch.optim.AdamW(twin.parameters(), lr=1e-2, weight_decay=0.1)
+    for i in range(6):
+        if i == 3:
+            opt.state.clear()
+            twin_opt.state.clear()
+        ctx._current_batch_idx = i
+        ctx.backward(torch.nn.functional.mse_loss(model(x), y))
+        ctx.step_optimizer(opt)
+        torch.nn.functional.mse_loss(twin(x), y).backward()
+        twin_opt.step()
+        twin_opt.zero_grad()
+        for p, q in zip(model.parameters(), twin.parameters()):
+            assert_close(_np(p), _np(q), "float32", f"step {i}")
+            assert float(opt.state[p]["step"]) == float(twin_opt.state[q]["step"]) == (i % 3) + 1
+            assert_close(_np(opt.state[p]["exp_avg_sq"]), _np(twin_opt.state[q]["exp_avg_sq"]), "float32", f"exp_avg_sq step {i}")
+    ctx.close()
