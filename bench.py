@@ -561,13 +561,23 @@ def measure_workload(args: argparse.Namespace, W: Any, dctx: Any, dist: Any, dev
     if k_ms:
         bpe = W.STEP_BYTES_PER_ELEM
         n_elem = eng.step_elements()
-        achieved = bpe * n_elem / (k_ms * 1e-3) / 1e9
-        cap = NCU_TRAFFIC.get(W.NAME, {})
-        roofline = {"bound": "hbm", "kernel": W.STEP_KERNEL, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+        hbm_bytes = bpe * n_elem
+        cap = NCU_TRAFFIC.get(W.NAME, {}) if world == 1 else {}
+        roofline = {"bound": "hbm", "kernel": eng.step_kernel_name(), "achieved": hbm_bytes / (k_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                     "traffic": cap.get("dram_bytes_per_launch"), "traffic_source": cap.get("source"), "peak_source": peak_src,
-                    "elements": n_elem, "algorithmic_bytes_per_element": bpe, "algorithmic_bytes_per_launch": bpe * n_elem,
+                    "elements": n_elem, "algorithmic_bytes_per_element": bpe, "algorithmic_bytes_per_launch": hbm_bytes,
                     "us_per_launch": k_ms * 1e3, "launches_timed": len(step_kernel_ms), "launches_per_step": per,
                     "note": "median over the timed region of CUDA events recorded inside libdgs around each launch (dgs_timer_read)"}
+        if eng.peer:
+            # the pushing step also stores every new parameter to the N-1 other ranks (the all-gather): at 8 GPUs those
+            # NVLink bytes, not the HBM bytes of the 1/N slice, bound the launch
+            psz = sum(fs.total * fs.param.element_size() for fs in eng.sets)
+            nvl_bytes = (world - 1) / world * psz
+            if nvl_bytes / (NVLINK_GBS * 1e9) > hbm_bytes / (peak * 1e9):
+                roofline.update({"bound": "nvlink", "achieved": nvl_bytes / (k_ms * 1e-3) / 1e9, "peak": NVLINK_GBS,
+                                 "peak_source": "900 GB/s per direction (BASELINE.md section 4)",
+                                 "algorithmic_bytes_per_launch": nvl_bytes, "algorithmic_hbm_bytes_per_launch": hbm_bytes})
+        roofline["frac"] = roofline["achieved"] / roofline["peak"]
 
     out: Dict[str, Any] = {
         "value": value, "ms_per_step": ms_total / steps, "steps": steps, "warmup": warmup, "gpu_launches": launches,

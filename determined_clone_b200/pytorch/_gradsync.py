@@ -963,6 +963,15 @@ class GradSyncEngine:
             return "nccl reduce-scatter + sharded step + all-gather"
         return "nccl allreduce" + (" (auto: peer route after two conforming steps)" if self.route == "auto" and self.peers is not None else "")
 
+    def step_kernel_name(self) -> str:
+        """The kernel that carries the optimizer step on this engine's current route (reported by bench.py)."""
+        kind = {"sgd": "sgd_kernel", "adam": "adam_kernel", "adamw": "adam_kernel"}.get(self._fused_kind or "", "torch optimizer.step()")
+        if self._fused_kind is None:
+            return kind
+        if self.direct and not self.needs_acc:
+            return f"dgs::direct_kernel<{self._fused_kind}> (single launch: gradients read in place, flatten + step)"
+        return f"dgs::{kind}" + (", PUSH (stores the new parameters to every rank)" if self.peer and not _PUSH_SPLIT else "")
+
     def step_elements(self) -> int:
         """Elements one optimizer step of this rank covers (all flat sets; 1/N of them with the sharded step)."""
         return sum(fs.total for fs in self.sets) // (self.world if self.sharded else 1)
