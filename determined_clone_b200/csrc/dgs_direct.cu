@@ -213,12 +213,23 @@ int launch_direct(DirectParams<typename HpOf<KIND>::type>& D, const dgs_seg* seg
     if (occ < 1) return fail(DGS_ECUDA, "dgs_direct_step: the kernel does not fit on an SM");
     per_sm = occ;
   }
-  long long grid = (long long)sm_count() * per_sm;  // a cooperative launch needs every CTA resident
-  if (grid > tiles) grid = tiles;
-  if (clip && grid > partials_capacity) grid = partials_capacity;
   P* pp = static_cast<P*>(param);
   P* p1 = static_cast<P*>(s1);
   P* p2 = static_cast<P*>(s2);
+  if (!clip) {
+    // no norm, no grid barrier: an ordinary launch, one tile per CTA (measured faster than a persistent grid for
+    // streaming read/write kernels on B200, see grid_mult() in dgs_api.cu)
+    const long long cap = (long long)sm_count() * grid_mult();
+    const int grid = (int)(tiles < cap ? tiles : cap);
+    timer_begin(st);
+    kernel<<<grid, kThreads, 0, st>>>(D, acc, scale, pp, p1, p2, 0, max_norm, partials, out_norm);
+    timer_end(st);
+    DGS_LAUNCHED();
+    return DGS_OK;
+  }
+  long long grid = (long long)sm_count() * per_sm;  // a cooperative launch needs every CTA resident
+  if (grid > tiles) grid = tiles;
+  if (grid > partials_capacity) grid = partials_capacity;
   void* args[] = {&D, &acc, &scale, &pp, &p1, &p2, &clip, &max_norm, &partials, &out_norm};
   timer_begin(st);
   DGS_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(kernel), dim3((unsigned)grid), dim3(kThreads), args, 0, st));
