@@ -52,6 +52,7 @@ MIN_BUCKET_BYTES, MAX_BUCKET_BYTES = 25 << 20, 128 << 20
 # Peer route, parameter exchange: the step kernel stores the new parameters to every rank itself ("fused"), or steps the
 # local slice and a copy kernel spreads it ("split").  DGS_PUSH_MODE picks; see DESIGN section 7 for the measurement.
 _PUSH_SPLIT = _os.environ.get("DGS_PUSH_MODE", "fused") == "split"
+_SLICE_LAUNCH = _os.environ.get("DGS_SLICE_LAUNCH", "single")
 ONE_BUCKET_BELOW_BYTES = int(__import__("os").environ.get("DGS_ONE_BUCKET_BELOW_MB", "0")) << 20
 
 
@@ -1097,6 +1098,15 @@ class GradSyncEngine:
             span = (b.end - b.begin) // world
             lo, hi = b.begin + rank * span, b.begin + (rank + 1) * span
             mine += [(max(x, lo), min(y, hi), k) for x, y, k in items if x < hi and y > lo]
+        if _SLICE_LAUNCH == "per_bucket":  # experiment switch: one launch per slice, no tiles outside the slices
+            for b in sorted(fs.buckets, key=lambda x: x.begin):
+                span = (b.end - b.begin) // world
+                lo, hi = b.begin + rank * span, b.begin + (rank + 1) * span
+                part = [r for r in mine if r[0] >= lo and r[1] <= hi]
+                for i in range(0, len(part), _lib.MAX_RANGES):
+                    chunk = part[i:i + _lib.MAX_RANGES]
+                    plan.append((chunk[0][0], chunk[-1][1], chunk))
+            return plan
         for i in range(0, len(mine), _lib.MAX_RANGES):
             chunk = mine[i:i + _lib.MAX_RANGES]
             plan.append((chunk[0][0], chunk[-1][1], chunk))
