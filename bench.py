@@ -302,9 +302,32 @@ def run_reference(args: argparse.Namespace) -> None:
 
 # ---- our arm ------------------------------------------------------------------------------------------
 def _free_port() -> int:
+    """A port for the control plane's listeners, taken BELOW the kernel's ephemeral range (32768+): a port the kernel
+    hands out for bind(0) can be given to any outgoing connection of the other ranks (NCCL / gloo bootstrap) between
+    this probe and the moment the chief binds it -- seen once on an 8-GPU run as 'Address already in use'."""
+    import random
+
+    rng = random.Random(os.getpid() ^ int(time.time() * 1e3))
+    for _ in range(200):
+        port = rng.randrange(20000, 29000)
+        try:
+            with socket.socket() as s:
+                s.bind(("0.0.0.0", port))
+            return port
+        except OSError:
+            continue
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
         return s.getsockname()[1]
+
+
+def _free_ports(n: int) -> List[int]:
+    out: List[int] = []
+    while len(out) < n:
+        port = _free_port()
+        if port not in out:
+            out.append(port)
+    return out
 
 
 def _max_over_ranks(dist: Any, device: Any, vals: List[float]) -> List[float]:
@@ -652,7 +675,7 @@ def run_parity(args: argparse.Namespace, dctx: Any, dist: Any, device: Any, rank
     # the 2-slot fixtures recorded from the unmodified reference (real torch DDP over gloo), on ranks 0 and 1
     if world >= 2 and not DEV.emulated:
         sys.path.insert(0, str(ROOT / "tests"))
-        ports = [_free_port(), _free_port()] if rank == 0 else [0, 0]
+        ports = _free_ports(2) if rank == 0 else [0, 0]
         ports = dctx.broadcast(ports)
         failed = ""
         if rank < 2:
@@ -709,7 +732,7 @@ def run_ours(args: argparse.Namespace) -> int:
 
     # control plane for the trial: the reference's DistributedContext (ZeroMQ through the chief)
     if world > 1:
-        ports = [_free_port(), _free_port()] if rank == 0 else [0, 0]
+        ports = _free_ports(2) if rank == 0 else [0, 0]
         dist.broadcast_object_list(ports, src=0)
         dctx = core.DistributedContext(rank=rank, size=world, local_rank=local_rank, local_size=world, cross_rank=0, cross_size=1,
                                        pub_port=ports[0], pull_port=ports[1])
