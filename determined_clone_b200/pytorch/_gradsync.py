@@ -404,6 +404,13 @@ class GradSyncEngine:
         """Switch between the full-gradient route and the sliced ones; only between windows."""
         self.sharded, self.peer = sliced, peer
         self._partials.zero_()
+        if peer:
+            # On the peer route the rows of a bucket in this rank's wire buffer receive the OTHER ranks' contributions
+            # to this rank's slice; nobody ever writes the alignment gaps of those rows, and the owner sums them into
+            # the norm.  Coming from the allreduce route the same memory holds last step's reduced gradients of other
+            # slices: clear it once (found as a 7e-5 parameter drift against the reference's 2-slot fixture).
+            for fs in self.sets:
+                fs.wire.zero_()
         self._eager_norm = False
         self.last_total_norm = None
 
