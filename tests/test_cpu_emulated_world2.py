@@ -157,6 +157,93 @@ def test_two_rank_scenarios_with_emulated_kernels_and_gloo(tmp_path, name, shard
     assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
 
 
+def _auto_worker(rank: int, size: int, port: int, zmq_ports, name: str, out_dir: str) -> None:
+    """Route auto (the default) with a clip function that is provably nothing but clip_grad_norm_: two optimizer steps on
+    the allreduce route, then the peer route -- on buffers that the allreduce route has used, which is what matters:
+    the rows of a bucket's alignment gaps must not carry last step's gradients into the norm."""
+    for p in (str(ROOT), str(ROOT / "tests"), str(ROOT / "tests" / "golden")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import torch.distributed as dist
+
+    import fake_dgs
+    from golden_io import N_PARAMS, Golden, assert_close
+    from golden_model import GoldenNet, make_data, make_optimizer
+
+    from determined_clone_b200 import core, pytorch
+    from determined_clone_b200.pytorch import _gradsync
+
+    torch.set_num_threads(1)
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=size)
+    fake = fake_dgs.install()
+
+    class SmallBuckets(_gradsync.GradSyncEngine):
+        def __init__(self, *args, **kwargs):
+            kwargs.update(bucket_bytes=1024, first_bucket_bytes=256)
+            super().__init__(*args, **kwargs)
+
+    _gradsync.GradSyncEngine = SmallBuckets
+    dctx = core.DistributedContext(rank=rank, size=size, local_rank=rank, local_size=size, cross_rank=0, cross_size=1,
+                                   pub_port=zmq_ports[0], pull_port=zmq_ports[1])
+    try:
+        g = Golden(name)
+        params_seen = []
+        max_norm = float(g.clip[1])
+
+        class Trial(pytorch.PyTorchTrial):
+            def __init__(self, context):
+                self.context = context
+                model = GoldenNet()
+                with torch.no_grad():
+                    for p, init in zip(model.parameters(), g.init_params()):
+                        p.copy_(torch.from_numpy(init))
+                self.model = context.wrap_model(model)
+                self.plist = list(self.model.parameters())
+                self.opt = context.wrap_optimizer(make_optimizer(self.model, g.hp), average_aggregated_gradients=g.average)
+                x, y = make_data(g.steps * g.agg, g.hp["global_batch_size"])
+                self.ds = torch.utils.data.TensorDataset(x, y)
+
+            def build_training_data_loader(self):
+                return pytorch.DataLoader(self.ds, batch_size=self.context.get_per_slot_batch_size(), shuffle=False)
+
+            def train_batch(self, batch, epoch_idx, batch_idx):
+                x, y = batch
+                loss = torch.nn.functional.mse_loss(self.model(x), y)
+                self.context.backward(loss)
+                self.context.step_optimizer(self.opt, clip_grads=lambda params: torch.nn.utils.clip_grad_norm_(params, max_norm))
+                if (batch_idx + 1) % g.agg == 0:
+                    params_seen.append([_np(p) for p in self.plist])
+                return {"loss": loss}
+
+        pytorch._PyTorchTrialController.pre_execute_hook(17)
+        ctx = pytorch.PyTorchTrialContext(distributed=dctx, hparams=g.hp, slots_per_trial=size, aggregation_frequency=g.agg, trial_seed=17)
+        trial = Trial(ctx)
+        eng = ctx._engines[trial.opt]
+        assert eng.route == "auto" and not eng.sharded and eng.peers is not None
+        pytorch._PyTorchTrialController(trial, ctx, max_length=g.steps * g.agg, reporting_period=g.agg).run()
+        assert eng.peer and eng.sharded, "route auto did not move to the peer kernels"
+        for s in range(g.steps):
+            for i in range(N_PARAMS):
+                assert_close(params_seen[s][i], g.per_step("params", s)[i], "float32", f"{name}: parameter {i} after step {s}")
+        kinds = [e[0] for e in fake.log]
+        n_buckets = sum(len(fs.buckets) for fs in eng.sets)
+        assert n_buckets >= 3
+        assert sum(1 for e in fake.log if e[0] == "allreduce" and e[1] > 1) == 2 * n_buckets  # the first two steps
+        assert kinds.count("peer_norm_exchange") == g.steps - 2
+        ctx.close()
+        open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
+    finally:
+        dctx.close()
+        dist.destroy_process_group()
+
+
+def test_route_auto_moves_to_the_peer_kernels_and_keeps_matching_the_reference(tmp_path):
+    import torch.multiprocessing as mp
+
+    mp.spawn(_auto_worker, args=(2, _free_port(), (_free_port(), _free_port()), "adamw_n2_a4_clip", str(tmp_path)), nprocs=2, join=True)
+    assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
+
+
 def _amp_worker(rank: int, size: int, port: int, zmq_ports, out_dir: str) -> None:
     """tests/test_gpu_amp.py's two-slot case on the CPU: auto-AMP with accumulation and clipping; an inf in ONE rank's
     data must make EVERY rank skip that step (the check runs on the all-reduced gradients), against torch DDP over
