@@ -344,8 +344,9 @@ def _max_over_ranks(dist: Any, device: Any, vals: List[float]) -> List[float]:
 MICRO_BYTES = {  # several GPUs: the averaged gradient has to exist in memory (the wire buffer) to be exchanged
     ("f32", 1): 8 + 4 + 28, ("f32", 4): 8 + 12 + 12 + 12 + 4 + 28, ("bf16", 1): 4 + 2 + 14, ("bf16", 4): 6 + 10 + 10 + 8 + 2 + 14,
 }
-MICRO_BYTES_1GPU = {  # one GPU: gradients read once for the norm and once by the step (dgs_direct_step_*), no wire buffer
-    ("f32", 1): 4 + 28, ("f32", 4): 8 + 12 + 12 + 8 + 8 + 24, ("bf16", 1): 2 + 14, ("bf16", 4): 6 + 10 + 10 + 6 + 6 + 12,
+MICRO_BYTES_1GPU = {  # one GPU, A = 1: gradients read once for the norm and once by the step (dgs_direct_step_*), no
+    # wire buffer; with an accumulator (A > 1) the three-kernel path runs, as on several GPUs
+    ("f32", 1): 4 + 28, ("f32", 4): 8 + 12 + 12 + 12 + 4 + 28, ("bf16", 1): 2 + 14, ("bf16", 4): 6 + 10 + 10 + 8 + 2 + 14,
 }
 
 
