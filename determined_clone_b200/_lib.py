@@ -105,6 +105,7 @@ SIGNATURES = {
     "dgs_nccl_version": [ctypes.POINTER(_i)],
     "dgs_peer_export": [_vp, _vp, ctypes.POINTER(_i64)],
     "dgs_peer_open": [_vp, _i64, ctypes.POINTER(_vp)],
+    "dgs_peer_close": [_vp],
     "dgs_peer_close_all": [],
     "dgs_peer_error": [ctypes.POINTER(_i)],
     "dgs_peer_error_clear": [],

@@ -37,7 +37,11 @@ constexpr int kThreads = 256;
 
 // ---- IPC bookkeeping ----------------------------------------------------------------------------------------------
 std::mutex g_ipc_mutex;
-std::map<std::string, void*> g_opened;  // handle bytes -> mapped base pointer (one open per allocation per process)
+struct Opened {
+  void* base;
+  int refs;
+};
+std::map<std::string, Opened> g_opened;  // handle bytes -> mapped base pointer (one open per allocation per process)
 int* g_err_host = nullptr;              // host-mapped error word, shared by every peer group of the process
 int* g_err_dev = nullptr;
 
@@ -327,21 +331,36 @@ extern "C" int dgs_peer_open(const void* handle64, int64_t offset, void** out_pt
   auto it = g_opened.find(key);
   void* base = nullptr;
   if (it != g_opened.end()) {
-    base = it->second;
+    base = it->second.base;
+    ++it->second.refs;
   } else {
     cudaIpcMemHandle_t h;
     memcpy(&h, handle64, sizeof(h));
     DGS_CUDA(cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
-    g_opened.emplace(key, base);
+    g_opened.emplace(key, Opened{base, 1});
   }
   *out_ptr = static_cast<char*>(base) + offset;
+  return DGS_OK;
+}
+
+extern "C" int dgs_peer_close(const void* handle64) {
+  using namespace dgs;
+  DGS_CHECK_ARG(handle64 != nullptr, "dgs_peer_close: NULL argument");
+  std::lock_guard<std::mutex> lock(g_ipc_mutex);
+  auto it = g_opened.find(std::string(static_cast<const char*>(handle64), DGS_PEER_HANDLE_BYTES));
+  DGS_CHECK_ARG(it != g_opened.end(), "dgs_peer_close: this handle is not open");
+  if (--it->second.refs == 0) {
+    const cudaError_t e = cudaIpcCloseMemHandle(it->second.base);
+    g_opened.erase(it);
+    if (e != cudaSuccess) return fail(DGS_ECUDA, "cudaIpcCloseMemHandle failed: %s", cudaGetErrorString(e));
+  }
   return DGS_OK;
 }
 
 extern "C" int dgs_peer_close_all(void) {
   using namespace dgs;
   std::lock_guard<std::mutex> lock(g_ipc_mutex);
-  for (auto& kv : g_opened) (void)cudaIpcCloseMemHandle(kv.second);
+  for (auto& kv : g_opened) (void)cudaIpcCloseMemHandle(kv.second.base);
   g_opened.clear();
   (void)cudaGetLastError();
   return DGS_OK;

@@ -463,6 +463,9 @@ class GradSyncEngine:
         if self._state_hook is not None:
             self._state_hook.remove()
             self._state_hook = None
+        if self.peers is not None:
+            self.peers.close()  # unmap the other ranks' buffers; the engine is not usable for peer steps afterwards
+            self.peers = None
 
     # ---- backward ---------------------------------------------------------------------------------
     # Gradients are left where autograd puts them (p.grad) and picked up per bucket:

@@ -40,6 +40,8 @@ class PeerGroup:
         except Exception as e:  # noqa: BLE001 -- reported to every rank below
             err = f"rank {rank}: {e}"
         everyone = allgather((err, mine))
+        self._allgather = allgather
+        self._opened: List[bytes] = []  # one entry per successful dgs_peer_open, for close()
         self.base: Dict[str, List[int]] = {}
         if not any(e for e, _ in everyone):
             try:
@@ -52,15 +54,38 @@ class PeerGroup:
                         handle, off = exported[name]
                         out = ctypes.c_void_p()
                         _lib.calls.dgs_peer_open(ctypes.create_string_buffer(handle, _lib.PEER_HANDLE_BYTES), off, ctypes.byref(out))
+                        self._opened.append(handle)
                         ptrs.append(int(out.value))
                     self.base[name] = ptrs
             except Exception as e:  # noqa: BLE001
                 err = f"rank {rank}: {e}"
         errors = [e for e in allgather(err) if e] + [e for e, _ in everyone if e]
         if errors:
+            self._unmap()
             raise _lib.DgsError("peer-memory set-up failed: " + "; ".join(sorted(set(errors))))
         self._tables: Dict[Tuple[str, int], Any] = {}
         self.sync_table = self.table("__sync__")
+
+    def _unmap(self) -> None:
+        for handle in self._opened:
+            try:
+                _lib.calls.dgs_peer_close(ctypes.create_string_buffer(handle, _lib.PEER_HANDLE_BYTES))
+            except _lib.DgsError:
+                pass
+        self._opened = []
+
+    def close(self) -> None:
+        """Unmap the peers' buffers from this process (after this rank's own kernels on them have finished).  Not a
+        collective, so that a rank tearing down after an error cannot hang the others: the buffers this rank EXPORTED stay
+        valid for as long as their tensors live, and every step ends with a barrier behind the peers' last stores into
+        them."""
+        if self.base is None:
+            return
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+        self._unmap()
+        self.base = None  # type: ignore
+        self._tables = {}
 
     def table(self, name: str, byte_off: int = 0) -> Any:
         """(void*)[size]: every rank's pointer to byte `byte_off` of buffer `name`, as mapped in this process."""

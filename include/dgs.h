@@ -362,6 +362,9 @@ int dgs_nccl_version(int* version);
 
 int dgs_peer_export(const void* ptr, void* handle64_out, int64_t* offset_out);
 int dgs_peer_open(const void* handle64, int64_t offset, void** out_ptr);
+/* one dgs_peer_close per dgs_peer_open of the same handle; the mapping goes when the last one is closed.  The caller
+ * makes sure (control plane) that no rank still uses the mapping and that its own kernels on it have finished. */
+int dgs_peer_close(const void* handle64);
 int dgs_peer_close_all(void);
 int dgs_peer_error(int* code_out);
 int dgs_peer_error_clear(void);

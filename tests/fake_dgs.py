@@ -294,6 +294,9 @@ class FakeCalls:
     def dgs_peer_close_all(self) -> None:
         pass
 
+    def dgs_peer_close(self, handle: Any) -> None:
+        self.log.append(("peer_close",))
+
     def dgs_peer_error(self, out: Any) -> None:
         out._obj.value = 0
 
