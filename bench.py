@@ -231,11 +231,17 @@ def run_cpu_port(trial_cls: Any, steps: int, warmup: int, budget_s: float, world
         return float(t)
 
     one = 0.0
-    for _ in range(max(warmup, 1) * agg):
-        t0 = time.perf_counter()
-        torch_port.train_batch_like_reference(ctx, trial, batches[idx % 4], idx)
-        idx += 1
-        one = time.perf_counter() - t0
+    warm_t0 = time.perf_counter()
+    for w in range(max(warmup, 1)):
+        for _ in range(agg):
+            t0 = time.perf_counter()
+            torch_port.train_batch_like_reference(ctx, trial, batches[idx % 4], idx)
+            idx += 1
+            one = time.perf_counter() - t0
+        # the warm-up is bounded like the sample (N CPU ranks of ResNet-50 take tens of seconds per step); every rank
+        # must stop at the same window, so they agree on the clock
+        if agree(time.perf_counter() - warm_t0) > budget_s / 4:
+            break
     # bounded sample: as many of the requested steps as fit the budget (whole aggregation windows; all ranks agree)
     n = max(agg, min(steps, int(budget_s / max(agree(one), 1e-3))) // agg * agg)
     n = int(agree(float(n), "min"))
