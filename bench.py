@@ -286,7 +286,7 @@ def run_reference(args: argparse.Namespace) -> None:
 
         dist.init_process_group("gloo")
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
-    r = run_cpu_port(W, args.steps, args.warmup, budget_s=120.0, world=world, rank=rank, threads=max(cores // world, 1))
+    r = run_cpu_port(W, args.steps, args.warmup, budget_s=90.0, world=world, rank=rank, threads=max(cores // world, 1))
     if rank == 0:
         line = {
             "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": r["steps"],

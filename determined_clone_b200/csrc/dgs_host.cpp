@@ -58,10 +58,18 @@ bool all_have_grads(const std::vector<at::Tensor>& params) {
   return true;
 }
 
+// True if any parameter has a gradient (step_optimizer's check for gradients produced outside context.backward()).
+bool any_has_grad(const std::vector<at::Tensor>& params) {
+  for (const at::Tensor& p : params)
+    if (p.grad().defined()) return true;
+  return false;
+}
+
 }  // namespace
 
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.doc() = "host-side fast path of the grad-sync engine (fills dgs_seg tables from parameter gradients)";
   m.def("take_grads", &take_grads, py::arg("params"), py::arg("table_addr"), py::arg("dtype_code"));
   m.def("all_have_grads", &all_have_grads, py::arg("params"));
+  m.def("any_has_grad", &any_has_grad, py::arg("params"));
 }

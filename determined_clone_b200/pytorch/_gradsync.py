@@ -767,7 +767,11 @@ class GradSyncEngine:
         present: List[List[bool]] = []
         self.last_total_norm = None
         if self.has_deferred():
-            stray = any(t.param.grad is not None for fs in self.sets for t in fs.tensors)  # produced outside context.backward()
+            # gradients produced outside context.backward() since the pending ones were taken
+            if _host is not None and hasattr(_host, "any_has_grad"):
+                stray = any(_host.any_has_grad(fs.params) for fs in self.sets)
+            else:
+                stray = any(t.param.grad is not None for fs in self.sets for t in fs.tensors)
             if allow_direct and not stray and all(fs.deferred is not None for fs in self.sets):
                 # the usual case on one GPU: every gradient of the window is pending, nothing else to finish
                 self._wire_versions = [fs.wire._version for fs in self.sets]
