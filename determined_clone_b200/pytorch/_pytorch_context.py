@@ -840,16 +840,25 @@ def _is_plain_norm_clip(fn: Any) -> bool:
         return False
     if any(isinstance(c, types.CodeType) for c in code.co_consts) or not set(code.co_names) <= _PLAIN_CLIP_NAMES:
         return False
-    if "clip_grad_norm_" not in code.co_names:
+    if "clip_grad_norm_" not in code.co_names and "clip_grad_norm_" not in code.co_freevars:
         return False
-    for cell in fn.__closure__ or ():
+    import dis
+
+    if any(ins.opname in ("FOR_ITER", "GET_ITER", "JUMP_BACKWARD", "YIELD_VALUE") for ins in dis.get_instructions(code)):
+        return False  # a loop (comprehensions are inlined since 3.12): per-parameter calls are not the one global clip
+    expected = {"torch": torch, "nn": torch.nn, "utils": torch.nn.utils, "clip_grad": torch.nn.utils.clip_grad, "clip_grad_norm_": real}
+    # what the function closes over: numbers (the max_norm), or the very objects the allowed names stand for
+    # (`from torch.nn.utils import clip_grad_norm_` inside an enclosing function)
+    for name, cell in zip(code.co_freevars, fn.__closure__ or ()):
         try:
-            if not isinstance(cell.cell_contents, (int, float)):
-                return False
+            value = cell.cell_contents
         except ValueError:
             return False
+        if isinstance(value, bool) or not (isinstance(value, (int, float)) or (name in expected and value is expected[name])):
+            return False
+    if "clip_grad_norm_" in code.co_freevars:
+        return True  # reached through the closure, checked above; the remaining names are attribute walks
     g = fn.__globals__
-    expected = {"torch": torch, "nn": torch.nn, "utils": torch.nn.utils, "clip_grad": torch.nn.utils.clip_grad, "clip_grad_norm_": real}
     root = code.co_names[0]  # the first name loaded is a global (or builtin) lookup; the rest are attribute walks from it
     return g.get(root) is expected[root]
 

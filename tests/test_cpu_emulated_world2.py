@@ -244,6 +244,84 @@ def test_route_auto_moves_to_the_peer_kernels_and_keeps_matching_the_reference(t
     assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
 
 
+def _demote_worker(rank: int, size: int, port: int, zmq_ports, out_dir: str) -> None:
+    """Route auto end to end against live torch DDP over gloo: AdamW + plain clip for a few steps (allreduce, then the
+    peer kernels), then ONE step that the sliced routes cannot honour (auto_zero_grads=False: the caller keeps
+    p.grad, so every rank needs the whole averaged gradient) -- the engine must bring the reduced slices and the
+    other ranks' optimizer state back (demote) in the middle of that step, finish it on the allreduce route and stay
+    there; parameters and Adam state must follow torch through all of it."""
+    for p in (str(ROOT), str(ROOT / "tests"), str(ROOT / "tests" / "golden")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import copy
+
+    import torch.distributed as dist
+
+    import fake_dgs
+    from golden_io import assert_close
+
+    from determined_clone_b200 import core, pytorch
+
+    torch.set_num_threads(1)
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=size)
+    fake = fake_dgs.install()
+    dctx = core.DistributedContext(rank=rank, size=size, local_rank=rank, local_size=size, cross_rank=0, cross_size=1,
+                                   pub_port=zmq_ports[0], pull_port=zmq_ports[1])
+    try:
+        torch.manual_seed(11)
+        base = torch.nn.Sequential(torch.nn.Linear(10, 48), torch.nn.LayerNorm(48), torch.nn.Tanh(), torch.nn.Linear(48, 3))
+        gen = torch.Generator().manual_seed(500 + rank)
+        data = [(torch.randn(8, 10, generator=gen), torch.randn(8, 3, generator=gen)) for _ in range(8)]
+        keep_grads_at, max_norm = 4, 0.3
+
+        ref_model = torch.nn.parallel.DistributedDataParallel(copy.deepcopy(base))
+        ref_opt = torch.optim.AdamW(ref_model.parameters(), lr=1e-2, betas=(0.9, 0.95), weight_decay=0.05)
+        want, want_kept = [], None
+        for i, (x, y) in enumerate(data):
+            torch.nn.functional.mse_loss(ref_model(x), y).backward()
+            torch.nn.utils.clip_grad_norm_(ref_model.parameters(), max_norm)
+            ref_opt.step()
+            if i == keep_grads_at:
+                want_kept = [_np(p.grad) for p in ref_model.parameters()]
+            ref_opt.zero_grad()
+            want.append(([_np(p) for p in ref_model.parameters()], [_np(ref_opt.state[p]["exp_avg_sq"]) for p in ref_model.parameters()]))
+
+        ctx = pytorch.PyTorchTrialContext(distributed=dctx, hparams={"global_batch_size": 16}, slots_per_trial=size)
+        model = ctx.wrap_model(copy.deepcopy(base))
+        opt = ctx.wrap_optimizer(torch.optim.AdamW(model.parameters(), lr=1e-2, betas=(0.9, 0.95), weight_decay=0.05))
+        eng = ctx._engines[opt]
+        routes = []
+        for i, (x, y) in enumerate(data):
+            ctx._current_batch_idx = i
+            ctx.backward(torch.nn.functional.mse_loss(model(x), y))
+            routes.append((eng.sharded, eng.peer))
+            ctx.step_optimizer(opt, clip_grads=lambda ps: torch.nn.utils.clip_grad_norm_(ps, max_norm), auto_zero_grads=i != keep_grads_at)
+            if i == keep_grads_at:
+                # the caller asked to keep the gradients: whole, averaged over the ranks and clipped, as torch leaves them
+                for p, g in zip(model.parameters(), want_kept):
+                    assert_close(_np(p.grad), g, "float32", "kept gradient")
+                opt.zero_grad()
+            state = opt.state_dict()["state"]  # (a collective while the engine is sliced: every rank asks)
+            for j, (p, (wp, wv)) in enumerate(zip(model.parameters(), zip(*want[i]))):
+                assert_close(_np(p), wp, "float32", f"parameter {j} after step {i}")
+                assert_close(_np(state[j]["exp_avg_sq"]), wv, "float32", f"exp_avg_sq {j} after step {i}")
+        # two steps on NCCL allreduce, then the peer kernels, then back for good from the step that kept its gradients
+        assert routes == [(False, False)] * 2 + [(True, True)] * (keep_grads_at - 1) + [(False, False)] * (len(data) - keep_grads_at - 1), routes
+        assert eng.route == "allreduce"
+        ctx.close()
+        open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
+    finally:
+        dctx.close()
+        dist.destroy_process_group()
+
+
+def test_route_auto_returns_to_allreduce_for_a_step_the_sliced_routes_cannot_serve(tmp_path):
+    import torch.multiprocessing as mp
+
+    mp.spawn(_demote_worker, args=(2, _free_port(), (_free_port(), _free_port()), str(tmp_path)), nprocs=2, join=True)
+    assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
+
+
 def _amp_worker(rank: int, size: int, port: int, zmq_ports, out_dir: str) -> None:
     """tests/test_gpu_amp.py's two-slot case on the CPU: auto-AMP with accumulation and clipping; an inf in ONE rank's
     data must make EVERY rank skip that step (the check runs on the all-reduced gradients), against torch DDP over

@@ -1373,3 +1373,45 @@ def test_controller_with_a_core_context_and_train_units(tmp_path):
         pytorch._PyTorchTrialController(trial_inst=trial2, context=ctx2, max_length=1, latest_checkpoint="no-such-uuid").run()
     with cc2 as entered:
         assert entered is cc2 and cc2.preempt.should_preempt() is False
+
+
+def test_plain_norm_clip_detector_is_conservative():
+    """_is_plain_norm_clip decides whether a clip_grads function can be served without ever showing it a gradient (the
+    single-launch step on one GPU, the sliced routes on several): only code that provably does nothing but call
+    torch.nn.utils.clip_grad_norm_ qualifies -- the reference's docstring example among it."""
+    import functools
+
+    from torch.nn.utils import clip_grad_norm_
+
+    from determined_clone_b200.pytorch._pytorch_context import _is_plain_norm_clip as plain
+
+    class T:
+        limit = 1.0
+
+        @staticmethod
+        def a(params):
+            torch.nn.utils.clip_grad_norm_(params, 1.0)
+
+        def b(self, params):
+            clip_grad_norm_(params, 0.5)
+
+        def reads(self, params):
+            self.seen = [p.grad for p in params]
+            clip_grad_norm_(params, 1.0)
+
+        def attr(self, params):
+            clip_grad_norm_(params, self.limit)  # `limit` could be anything: not provable
+
+    def closure(value):
+        return lambda params: torch.nn.utils.clip_grad_norm_(params, value)
+
+    yes = [lambda params: torch.nn.utils.clip_grad_norm_(params, 0.0001),  # reference _pytorch_context.py:851-853
+           T.a, T().a, T().b, functools.partial(clip_grad_norm_, max_norm=1.0), closure(2.0), closure(3)]
+    no = [T().reads, T().attr, closure([1.0]), closure(torch.ones(())), print, functools.partial(print, end=""),
+          lambda params: torch.nn.utils.clip_grad_value_(params, 1.0), lambda params: None,
+          lambda params: [torch.nn.utils.clip_grad_norm_(p, 1.0) for p in params]]
+    assert [plain(f) for f in yes] == [True] * len(yes)
+    assert [plain(f) for f in no] == [False] * len(no)
+    shadow = {"torch": type("fake", (), {"nn": None})}
+    impostor = eval("lambda params: torch.nn.utils.clip_grad_norm_(params, 1.0)", shadow)  # some other `torch`
+    assert plain(impostor) is False
