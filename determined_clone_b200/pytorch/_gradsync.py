@@ -23,6 +23,14 @@ boundary, so a param group is one contiguous element range and a comm bucket is 
 slice.  Buckets are cut from the END of the buffer (gradients arrive roughly in reverse), 1 MiB
 first then 25 MiB, the sizes torch DDP uses.
 
+Two shortcuts replace parts of that sequence where nothing needs the averaged gradient in memory:
+  * one GPU, no accumulation: the final pass's gradients stay where autograd left them and step_optimizer runs
+    dgs_direct_step_* -- scale, norm, clip and optimizer step in ONE kernel (direct_step / flush_deferred);
+  * several GPUs on one NVSwitch box, route "peer" (what route "auto" moves to): dgs_flatten_push stores each value into
+    the wire buffer of the rank that owns its slice, the owner reduces (dgs_peer_reduce_multi), the ranks exchange
+    their sums of squares (dgs_peer_norm_exchange) and dgs_step_*_push steps the own slices and stores the new
+    parameters to every rank -- no NCCL call in a steady-state step (_peer.py, csrc/dgs_peer.cu).
+
 There is no CPU or torch fallback for these steps.  Optimizers other than SGD / Adam / AdamW keep
 their own torch `step()` on gradient views of the wire buffer (still flattened, all-reduced and
 clipped by the kernels).
