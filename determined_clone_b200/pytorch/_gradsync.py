@@ -61,6 +61,11 @@ MIN_BUCKET_BYTES, MAX_BUCKET_BYTES = 25 << 20, 128 << 20
 # local slice and a copy kernel spreads it ("split").  DGS_PUSH_MODE picks; see DESIGN section 7 for the measurement.
 _PUSH_SPLIT = _os.environ.get("DGS_PUSH_MODE", "fused") == "split"
 _SLICE_LAUNCH = _os.environ.get("DGS_SLICE_LAUNCH", "single")
+# Peer route: flat sets whose largest bucket reaches this size reduce every bucket on a side stream as soon as ITS
+# pushes have landed everywhere (barrier + owner reduction per bucket, hidden behind the pushes of the buckets that
+# follow); smaller sets keep ONE barrier and ONE reduction launch at step time (fewer launches matter more there).
+# DGS_PEER_OVERLAP_MB=0 switches the per-bucket mode off.
+_PEER_OVERLAP_MIN = int(_os.environ.get("DGS_PEER_OVERLAP_MB", "32")) << 20
 ONE_BUCKET_BELOW_BYTES = int(__import__("os").environ.get("DGS_ONE_BUCKET_BELOW_MB", "0")) << 20
 
 
@@ -201,6 +206,7 @@ class _FlatSet:
         self.deferred: Optional[Tuple[List[torch.Tensor], bool]] = None
         self.seg_range_for: Any = None  # which run structure seg_range currently describes
         self.seg_range: Any = None  # (int32)[len(tensors)]: hyper-parameter row of every tensor, for the direct step
+        self.peer_overlap = False  # peer route: barrier + owner reduction per bucket on the side stream (large buckets)
         self.scatter_table: Any = None  # peer route, split parameter exchange: (offsets, sizes, n) of dgs_peer_scatter
         self.reduce_table: Any = None  # peer route: (begins, spans, first norm slot, slots) of dgs_peer_reduce_multi
         self.peer_wire: Any = None  # (void*)[world]: every rank's pointer to its wire buffer of this set (peer route)
@@ -288,6 +294,8 @@ class GradSyncEngine:
         self.direct = comm is None and self._fused_kind is not None and _os.environ.get("DGS_DIRECT", "1") != "0"
         self._direct_clip: Optional[Tuple[bool, float]] = None  # set for the duration of direct_step()
         self._all_present: Optional[List[List[bool]]] = None
+        self._peer_stream: Any = None  # side stream of the per-bucket owner reductions (peer route, large buckets)
+        self._peer_side_pending = False
         self.peers: Optional[_peer.PeerGroup] = None
         self.peer_unavailable: Optional[str] = None  # why peer set-up failed, if it did
         self._conforming_steps = 0
@@ -402,6 +410,10 @@ class GradSyncEngine:
             self.peers = _peer.PeerGroup(comm.rank, comm.size, self.device, comm.allgather_obj, buffers, timeout_s=timeout)
             for si, fs in enumerate(self.sets):
                 fs.peer_wire = self.peers.table(f"wire{si}")
+                biggest = max((b.end - b.begin) * fs.wire.element_size() for b in fs.buckets)
+                fs.peer_overlap = _PEER_OVERLAP_MIN > 0 and biggest >= _PEER_OVERLAP_MIN
+            if self.device.type == "cuda" and any(fs.peer_overlap for fs in self.sets):
+                self._peer_stream = torch.cuda.Stream(device=self.device, priority=-1)
         except _lib.DgsError as e:
             self.peers = None
             if required:
@@ -710,7 +722,12 @@ class GradSyncEngine:
             itemsize = fs.wire.element_size()
             base, span = fs.wire.data_ptr() + b.begin * itemsize, b.end - b.begin
             if self.peer:
-                pass  # nothing to issue: the flatten kernel's stores were the transfer; the owner reduces at step time
+                # the flatten kernel's stores were the transfer.  Large buckets: wait (on the side stream) until every
+                # rank's pushes of THIS bucket have landed and reduce it there, while the compute stream goes on pushing
+                # the next buckets; the ranks issue these barriers in the same (agreed) bucket order.  Small sets reduce
+                # everything at step time in one launch (finish_window).
+                if fs.peer_overlap and not b.reduced:
+                    self._peer_reduce_bucket(fs, b)
             elif self.comm is not None and not b.reduced:
                 if self.sharded:
                     self.comm.reduce_scatter_raw(base, span // self.world, fs.wire_code)
@@ -725,6 +742,27 @@ class GradSyncEngine:
                 b.norm_done = True
             b.reduced = True
             self._next_launch += 1
+
+    def _peer_reduce_bucket(self, fs: _FlatSet, b: _Bucket) -> None:
+        assert self.peers is not None and self.comm is not None
+        isz = fs.wire.element_size()
+        side = self._peer_stream
+        if side is not None:
+            pushed = torch.cuda.Event()
+            pushed.record()  # behind this bucket's push on the compute stream
+            side.wait_event(pushed)
+            ctx: Any = torch.cuda.stream(side)
+        else:
+            import contextlib
+
+            ctx = contextlib.nullcontext()  # (CPU emulation: in line)
+        with ctx:
+            stream = _stream()
+            self.peers.barrier(_peer.S_PUSHED, stream)
+            _lib.calls.dgs_peer_reduce(_ptr(fs.wire, b.begin * isz), fs.wire_code, (b.end - b.begin) // self.world, self.world,
+                                       self.comm.rank, _ptr(self._partials, 4 * b.norm_off), stream)
+        b.norm_done = True
+        self._peer_side_pending = side is not None
 
     # ---- step ---------------------------------------------------------------------------------------
     def has_deferred(self) -> bool:
@@ -828,8 +866,15 @@ class GradSyncEngine:
             assert self.peers is not None
             self.peers.check()
             stream = _stream()
-            self.peers.barrier(_peer.S_PUSHED, stream)
-            for fs in self.sets:
+            if self._peer_side_pending:
+                joined = torch.cuda.Event()
+                joined.record(self._peer_stream)
+                torch.cuda.current_stream().wait_event(joined)  # the per-bucket reductions issued during backward
+                self._peer_side_pending = False
+            batched = [fs for fs in self.sets if not fs.peer_overlap]
+            if batched:
+                self.peers.barrier(_peer.S_PUSHED, stream)
+            for fs in batched:
                 if len(fs.buckets) <= _lib.PEER_MAX_BUCKETS:
                     if fs.reduce_table is None:
                         bs = sorted(fs.buckets, key=lambda x: x.begin)

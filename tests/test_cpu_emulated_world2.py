@@ -183,6 +183,7 @@ def _auto_worker(rank: int, size: int, port: int, zmq_ports, name: str, out_dir:
             super().__init__(*args, **kwargs)
 
     _gradsync.GradSyncEngine = SmallBuckets
+    _gradsync._PEER_OVERLAP_MIN = 1  # every flat set takes the per-bucket mode: barrier + owner reduction as each bucket is pushed
     dctx = core.DistributedContext(rank=rank, size=size, local_rank=rank, local_size=size, cross_rank=0, cross_size=1,
                                    pub_port=zmq_ports[0], pull_port=zmq_ports[1])
     try:
@@ -230,6 +231,10 @@ def _auto_worker(rank: int, size: int, port: int, zmq_ports, name: str, out_dir:
         assert n_buckets >= 3
         assert sum(1 for e in fake.log if e[0] == "allreduce" and e[1] > 1) == 2 * n_buckets  # the first two steps
         assert kinds.count("peer_norm_exchange") == g.steps - 2
+        # per-bucket mode: one barrier and one owner reduction per bucket per step (+ the parameter barrier per step)
+        assert all(fs.peer_overlap for fs in eng.sets)
+        assert kinds.count("peer_reduce") == (g.steps - 2) * n_buckets
+        assert kinds.count("peer_barrier") == (g.steps - 2) * (n_buckets + 1)
         ctx.close()
         open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
     finally:
