@@ -71,7 +71,7 @@ def parse(argv: Optional[List[str]] = None) -> argparse.Namespace:
     ap.add_argument("--micro-dtypes", nargs="*", default=["f32", "bf16"], choices=["f32", "bf16"])
     ap.add_argument("--micro-aggs", type=int, nargs="*", default=[1, 4])
     ap.add_argument("--micro-only", action="store_true", help="run only the grad-sync microbench and print it")
-    ap.add_argument("--micro-bucket-mb", type=int, default=0, help="bucket cap for the microbench (0 = the engine's default cut on several GPUs, one bucket on one)")
+    ap.add_argument("--micro-bucket-mb", type=int, default=0, help="bucket cap for the microbench (0 = one bucket per flat set)")
     ap.add_argument("--micro-steps", type=int, default=10)
     ap.add_argument("--cpu-budget-s", type=float, default=20.0)
     return ap.parse_args(argv)
@@ -377,9 +377,7 @@ def gradsync_microbench(ctx: Any, dist: Any, mb: int, dtype: str, agg: int, step
     if route is not None:
         kwargs["route"] = route
     eng = pytorch.GradSyncEngine(opt, dev, ctx._get_comm(), aggregation_frequency=agg, average_aggregated_gradients=True,
-                                 # buckets: the engine's own cut on several GPUs (1 MiB, then 1/8 of the bytes clamped to
-                                 # [25, 128] MiB -- what a model of this size would get); one bucket on one GPU
-                                 bucket_bytes=(bucket_mb << 20) if bucket_mb else (0 if world > 1 else n * isz + 1), **kwargs)
+                                 bucket_bytes=(bucket_mb << 20) if bucket_mb else n * isz + 1, **kwargs)
     grads = [[(torch.randn(n_piece, device=dev) * 1e-2).to(tdt) for _ in range(pieces)] for _ in range(2)]
     clip = pytorch._gradsync.ClipRequest()
     clip.max_norm = 1.0
@@ -476,9 +474,15 @@ def microbench_sweep(ctx: Any, dist: Any, args: argparse.Namespace, peak: float)
                 # (one bucket: the NCCL collectives' best case -- their bus bandwidth grows with the message size)
                 others.append(gradsync_microbench(ctx, dist, at_1g["mib"], "f32", 1, args.micro_steps, peak, bucket_mb=at_1g["mib"], route=other))
                 DEV.empty_cache()
+    bucketed = None
+    if world > 1 and at_1g is not None and at_1g["mib"] >= 256 and not args.micro_only and not args.micro_bucket_mb:
+        # the same point cut into 128 MiB buckets (what a model of this size gets from the engine): on the peer route the
+        # barrier + owner reduction of a bucket then run on a side stream behind the pushes of the following buckets
+        bucketed = gradsync_microbench(ctx, dist, at_1g["mib"], "f32", 1, args.micro_steps, peak, bucket_mb=128, route=route)
+        DEV.empty_cache()
     return {"optimizer": "adamw + clip_grad_norm_ 1.0", "nvlink_gbs_per_direction": NVLINK_GBS, "hbm_gbs": peak,
             "bytes_per_element": {f"{d}_A{a}": v for (d, a), v in (MICRO_BYTES if world > 1 else MICRO_BYTES_1GPU).items()},
-            "headline": at_1g, "same_point_on_the_nccl_routes": others, "note": note, "rows": rows}
+            "headline": at_1g, "same_point_in_128_mib_buckets": bucketed, "same_point_on_the_nccl_routes": others, "note": note, "rows": rows}
 
 
 class _StepTimer:

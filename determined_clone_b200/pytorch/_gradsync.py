@@ -411,7 +411,8 @@ class GradSyncEngine:
             for si, fs in enumerate(self.sets):
                 fs.peer_wire = self.peers.table(f"wire{si}")
                 biggest = max((b.end - b.begin) * fs.wire.element_size() for b in fs.buckets)
-                fs.peer_overlap = _PEER_OVERLAP_MIN > 0 and biggest >= _PEER_OVERLAP_MIN
+                # (with one big bucket behind the 1 MiB first one there is nothing to hide a reduction behind)
+                fs.peer_overlap = _PEER_OVERLAP_MIN > 0 and biggest >= _PEER_OVERLAP_MIN and len(fs.buckets) >= 3
             if self.device.type == "cuda" and any(fs.peer_overlap for fs in self.sets):
                 self._peer_stream = torch.cuda.Stream(device=self.device, priority=-1)
         except _lib.DgsError as e:
