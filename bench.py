@@ -17,7 +17,7 @@ collectives on the communicator's side stream), context.step_optimizer (fused st
             CUDA events recorded inside libdgs immediately around each launch (dgs_timer_*) during the timed
             region, on the launching stream; algorithmic bytes per element as stated in DESIGN.md; `traffic` is
             the ncu --set full capture of that kernel in this workload (profiles/, file named in the object)
-  parity    N >= 2 (and N = 1): the workloads of configs[1..3] for 10 optimizer steps under this path and, beside
+  parity    (after the headline measurement) N >= 2 (and N = 1): the workloads of configs[1..3] for 10 optimizer steps under this path and, beside
             it on the same GPUs and inputs, under torch DDP + torch.optim (the reference's lines,
             workloads/parity.py); at N >= 2 also the 2-slot fixtures recorded from the unmodified reference on
             ranks 0-1.  A mismatch makes the run exit non-zero.
@@ -767,25 +767,42 @@ def run_ours(args: argparse.Namespace) -> int:
                 print(json.dumps({"n_gpus": world, "gradsync_microbench": sweep}), flush=True)
             return 0
 
+        # the headline first; everything after it is additional evidence, and a failure there (recorded under `errors`)
+        # must not void the measurement already taken.  Only a deterministic parity mismatch makes the run exit non-zero.
+        head = measure_workload(args, W, dctx, dist, device, rank, world, local_rank, args.steps, args.warmup, with_e2e=True)
+        errors: List[str] = []
+
+        def optional(what: str, fn: Callable[[], Any]) -> Any:
+            if errors:
+                return None  # after a failure the ranks may no longer be in step: stop adding work
+            try:
+                return fn()
+            except Exception as e:  # noqa: BLE001
+                errors.append(f"{what}: {type(e).__name__}: {str(e)[:300]}")
+                return None
+
         parity = None
         if not args.no_parity:
-            parity = run_parity(args, dctx, dist, device, rank, world)
-            if not parity["deterministic_checks_ok"]:
+            parity = optional("parity", lambda: run_parity(args, dctx, dist, device, rank, world))
+            if parity is not None and not parity["deterministic_checks_ok"]:
                 rc = 3
-
-        head = measure_workload(args, W, dctx, dist, device, rank, world, local_rank, args.steps, args.warmup, with_e2e=True)
 
         extra: Dict[str, Any] = {}
         if not args.no_extra and args.workload != "gpt2_medium":
             G = _workload(args, "gpt2_medium")
-            extra[G.NAME] = measure_workload(args, G, dctx, dist, device, rank, world, local_rank, 8 * G.AGG, 3 * G.AGG, with_e2e=False)
-            extra[G.NAME]["unit"] = "sequences/s (4 x 1024 tokens per slot per micro-batch)"
+            got = optional("configs[3]", lambda: measure_workload(args, G, dctx, dist, device, rank, world, local_rank, 8 * G.AGG, 3 * G.AGG, with_e2e=False))
+            if got is not None:
+                got["unit"] = "sequences/s (4 x 1024 tokens per slot per micro-batch)"
+                extra[G.NAME] = got
 
         micro = None
         if not args.no_microbench:
-            pytorch._PyTorchTrialController.pre_execute_hook(17)
-            ctx = pytorch.PyTorchTrialContext(distributed=dctx, hparams={"global_batch_size": world}, slots_per_trial=world, device=device)
-            micro = microbench_sweep(ctx, dist, args, peak)
+            def sweep() -> Any:
+                pytorch._PyTorchTrialController.pre_execute_hook(17)
+                ctx = pytorch.PyTorchTrialContext(distributed=dctx, hparams={"global_batch_size": world}, slots_per_trial=world, device=device)
+                return microbench_sweep(ctx, dist, args, peak)
+
+            micro = optional("gradsync_microbench", sweep)
 
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
@@ -799,7 +816,7 @@ def run_ours(args: argparse.Namespace) -> int:
                 "dtype": W.DTYPE, "data": "synthetic", "config": head["config"],
                 "roofline": head["roofline"], "cpu_baseline": cpu, "e2e": head.get("e2e"), "gpu_launches": head["gpu_launches"],
                 "clocks": head["clocks"], "grad_sync_us_per_step": head["grad_sync_us_per_step"], "route": head["route"],
-                "parity": parity, "gradsync_microbench": micro, "configs": extra,
+                "parity": parity, "gradsync_microbench": micro, "configs": extra, "errors": errors or None,
             }
             print(json.dumps(line), flush=True)
     finally:
@@ -863,6 +880,9 @@ def main() -> None:
     # sets NCCL_DEBUG=VERSION) out of it; an explicit NCCL_DEBUG=INFO from the caller is respected
     if os.environ.get("NCCL_DEBUG", "VERSION").upper() in ("VERSION", "WARN"):
         os.environ.pop("NCCL_DEBUG", None)  # both levels print the banner
+    # a rank that never arrives at a peer barrier is reported after this long (not a hang, not a GPU fault); the library's
+    # own default of 120 s suits training jobs, a benchmark wants to know sooner
+    os.environ.setdefault("DGS_PEER_TIMEOUT_S", "60")
     args = parse()
     if args.impl == "reference":
         run_reference(args)
