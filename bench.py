@@ -25,6 +25,11 @@ collectives on the communicator's side stream), context.step_optimizer (fused st
             accumulate + collective + clip + AdamW, time per optimizer step against max(HBM, NVLink @ 900 GB/s)
   configs   configs[3] (GPT-2 medium bf16, AdamW, A=4, clip 1.0) measured the same way as the headline
   cpu_baseline  (N=1, rank 0) the torch port of the reference's path on the host cores, bounded sample
+
+Order and time limits: headline (value, roofline, e2e) and cpu_baseline first; parity, configs and the microbench are
+additional evidence -- a failure there is recorded under `errors`, none of them is started later than 560 s into the
+run, and at 780 s the line is printed with whatever is complete (_Deadline; the driver's scaling sweep allows each N
+about 870 s).
 """
 import argparse
 import json
@@ -304,6 +309,63 @@ def run_reference(args: argparse.Namespace) -> None:
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+
+# ---- time limits ----------------------------------------------------------------------------------------
+T0 = time.monotonic()  # the process's own clock; the driver allows each `--gpus N` run about 870 s in its scaling sweep
+
+
+class _Deadline:
+    """Keeps a measurement that has been taken from being lost to whatever comes after it.
+
+    soft (DGS_BENCH_SOFT_S, 560 s after start): no further optional part (parity, configs[3], microbench) is started;
+    rank 0 decides and the ranks follow its decision, so they stay in step.
+    hard (DGS_BENCH_HARD_S, 780 s after start): a timer thread on every rank.  If the headline has been measured by
+    then, rank 0 prints the JSON line with the parts that are complete (the cut is named under `errors`) and every
+    rank leaves with os._exit -- a collective that never returns (a rank that died in an optional part) cannot be
+    waited out.  Before the headline exists there is nothing to print: the run exits non-zero."""
+
+    def __init__(self, rank: int, emit: Callable[[Optional[str]], None]) -> None:
+        self.rank, self.emit = rank, emit
+        self.soft = float(os.environ.get("DGS_BENCH_SOFT_S", "560"))
+        self.hard = float(os.environ.get("DGS_BENCH_HARD_S", "780"))
+        self.phase, self.rc, self.have_headline, self.printed = "start", 0, False, False
+        self.lock = threading.Lock()
+        self._exit: Callable[[int], None] = os._exit
+        self._timer: Optional[threading.Timer] = None
+
+    def arm(self) -> None:
+        self._timer = threading.Timer(max(self.hard - (time.monotonic() - T0), 0.0), self.expire)
+        self._timer.daemon = True
+        self._timer.start()
+
+    def disarm(self) -> None:
+        if self._timer is not None:
+            self._timer.cancel()
+
+    def elapsed(self) -> float:
+        return time.monotonic() - T0
+
+    def print_once(self, cut: Optional[str] = None) -> None:
+        with self.lock:
+            if self.printed:
+                return
+            self.printed = True
+            if self.rank == 0:
+                self.emit(cut)
+
+    def expire(self) -> None:
+        if not self.have_headline:
+            sys.stderr.write(f"bench.py: no headline after {self.elapsed():.0f} s (in: {self.phase}); giving up\n")
+            sys.stderr.flush()
+            self._exit(4)
+            return
+        self.print_once(f"time limit: stopped after {self.elapsed():.0f} s in `{self.phase}`; the parts that were complete are reported")
+        if self.rank != 0:
+            time.sleep(1.0)  # let rank 0 write its line before the launcher sees a worker leave
+        sys.stdout.flush()
+        self._exit(self.rc)
 
 
 # ---- our arm ------------------------------------------------------------------------------------------
@@ -757,7 +819,26 @@ def run_ours(args: argparse.Namespace) -> int:
     else:
         dctx = core.DummyDistributedContext()
     peak, _ = measured_peaks()
-    rc = 0
+    got: Dict[str, Any] = {"head": None, "parity": None, "extra": {}, "micro": None, "cpu": None}
+    errors: List[str] = []
+    cpu_error: Optional[str] = None  # kept apart from `errors`: it does not put the ranks out of step
+
+    def emit(cut: Optional[str]) -> None:
+        head = got["head"]
+        line = {
+            "metric": METRIC, "value": head["value"], "unit": UNIT, "n_gpus": world, "steps": head["steps"], "warmup": head["warmup"],
+            "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": W.DTYPE, "data": "synthetic", "config": head["config"],
+            "roofline": head["roofline"], "cpu_baseline": got["cpu"], "e2e": head.get("e2e"), "gpu_launches": head["gpu_launches"],
+            "clocks": head["clocks"], "grad_sync_us_per_step": head["grad_sync_us_per_step"], "route": head["route"],
+            "parity": got["parity"], "gradsync_microbench": got["micro"], "configs": got["extra"],
+            "errors": (errors + ([cut] if cut else [])) or None,
+        }
+        print(json.dumps(line), flush=True)
+
+    guard = _Deadline(rank, emit)
+    if not DEV.emulated:
+        guard.arm()
     try:
         if args.micro_only:
             pytorch._PyTorchTrialController.pre_execute_hook(17)
@@ -765,66 +846,70 @@ def run_ours(args: argparse.Namespace) -> int:
             sweep = microbench_sweep(ctx, dist, args, peak)
             if rank == 0:
                 print(json.dumps({"n_gpus": world, "gradsync_microbench": sweep}), flush=True)
+            guard.printed = True
             return 0
 
         # the headline first; everything after it is additional evidence, and a failure there (recorded under `errors`)
         # must not void the measurement already taken.  Only a deterministic parity mismatch makes the run exit non-zero.
-        head = measure_workload(args, W, dctx, dist, device, rank, world, local_rank, args.steps, args.warmup, with_e2e=True)
-        errors: List[str] = []
+        guard.phase = "headline"
+        got["head"] = measure_workload(args, W, dctx, dist, device, rank, world, local_rank, args.steps, args.warmup, with_e2e=True)
+        guard.have_headline = True
+
+        if world == 1 and not args.no_cpu_baseline:  # (one rank, bounded: nothing to keep in step)
+            guard.phase = "cpu_baseline"
+            try:
+                r = run_cpu_port(W, steps=20, warmup=1, budget_s=args.cpu_budget_s)
+                got["cpu"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
+            except Exception as e:  # noqa: BLE001
+                cpu_error = f"cpu_baseline: {type(e).__name__}: {str(e)[:300]}"
 
         def optional(what: str, fn: Callable[[], Any]) -> Any:
-            if errors:
-                return None  # after a failure the ranks may no longer be in step: stop adding work
+            guard.phase = f"before {what}"
+            # after a failure anywhere the ranks may no longer be in step: stop adding work, on every rank alike
+            failed = [f"rank {r}: {e[0]}" for r, e in enumerate(dctx.allgather(errors)) if e]
+            if failed:
+                if not errors:
+                    errors.append(f"{what}: not started ({failed[0][:200]})")
+                return None
+            if not dctx.broadcast(guard.elapsed() < guard.soft):  # rank 0's clock decides for everyone
+                errors.append(f"{what}: not started, {guard.soft:.0f} s of the run's time were used")
+                return None
+            guard.phase = what
             try:
                 return fn()
             except Exception as e:  # noqa: BLE001
                 errors.append(f"{what}: {type(e).__name__}: {str(e)[:300]}")
                 return None
 
-        parity = None
         if not args.no_parity:
-            parity = optional("parity", lambda: run_parity(args, dctx, dist, device, rank, world))
-            if parity is not None and not parity["deterministic_checks_ok"]:
-                rc = 3
+            got["parity"] = optional("parity", lambda: run_parity(args, dctx, dist, device, rank, world))
+            if got["parity"] is not None and not got["parity"]["deterministic_checks_ok"]:
+                guard.rc = 3
 
-        extra: Dict[str, Any] = {}
         if not args.no_extra and args.workload != "gpt2_medium":
             G = _workload(args, "gpt2_medium")
-            got = optional("configs[3]", lambda: measure_workload(args, G, dctx, dist, device, rank, world, local_rank, 8 * G.AGG, 3 * G.AGG, with_e2e=False))
-            if got is not None:
-                got["unit"] = "sequences/s (4 x 1024 tokens per slot per micro-batch)"
-                extra[G.NAME] = got
+            sub = optional("configs[3]", lambda: measure_workload(args, G, dctx, dist, device, rank, world, local_rank, 8 * G.AGG, 3 * G.AGG, with_e2e=False))
+            if sub is not None:
+                sub["unit"] = "sequences/s (4 x 1024 tokens per slot per micro-batch)"
+                got["extra"][G.NAME] = sub
 
-        micro = None
         if not args.no_microbench:
             def sweep() -> Any:
                 pytorch._PyTorchTrialController.pre_execute_hook(17)
                 ctx = pytorch.PyTorchTrialContext(distributed=dctx, hparams={"global_batch_size": world}, slots_per_trial=world, device=device)
                 return microbench_sweep(ctx, dist, args, peak)
 
-            micro = optional("gradsync_microbench", sweep)
+            got["micro"] = optional("gradsync_microbench", sweep)
 
-        cpu = None
-        if world == 1 and not args.no_cpu_baseline:
-            r = run_cpu_port(W, steps=20, warmup=1, budget_s=args.cpu_budget_s)
-            cpu = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
-
-        if rank == 0:
-            line = {
-                "metric": METRIC, "value": head["value"], "unit": UNIT, "n_gpus": world, "steps": head["steps"], "warmup": head["warmup"],
-                "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": W.DTYPE, "data": "synthetic", "config": head["config"],
-                "roofline": head["roofline"], "cpu_baseline": cpu, "e2e": head.get("e2e"), "gpu_launches": head["gpu_launches"],
-                "clocks": head["clocks"], "grad_sync_us_per_step": head["grad_sync_us_per_step"], "route": head["route"],
-                "parity": parity, "gradsync_microbench": micro, "configs": extra, "errors": errors or None,
-            }
-            print(json.dumps(line), flush=True)
+        guard.phase = "teardown"
+        guard.print_once(cpu_error)
     finally:
         dctx.close()
         if dist is not None:
             dist.barrier()
             dist.destroy_process_group()
-    return rc
+        guard.disarm()
+    return guard.rc
 
 
 def run_torch_gpu(args: argparse.Namespace) -> None:

@@ -137,3 +137,41 @@ def test_bench_reference_arm_runs_n_gloo_ranks(tmp_path):
     line = json.loads((tmp_path / "ref.json").read_text().strip().splitlines()[-1])
     assert line["impl"] == "reference" and line["n_gpus"] == 2 and line["config"]["global_batch"] == 4
     assert line["cpu_baseline"]["ranks"] == 2 and line["value"] > 0 and line["e2e"]["h2d_bytes_per_step"] == 0
+
+
+def test_time_limits_keep_the_headline(monkeypatch, capsys):
+    """Past the soft limit no optional part is started (the line still carries headline, e2e and cpu baseline,
+    and names what was left out); at the hard limit the timer prints what is complete exactly once and leaves."""
+    sys.path.insert(0, str(ROOT / "tests"))
+    import fake_dgs
+
+    import bench
+
+    fake_dgs.install(monkeypatch)
+    monkeypatch.setattr(bench, "DEV", HostDev())
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+        monkeypatch.delenv(k, raising=False)
+    monkeypatch.setenv("DGS_BENCH_SOFT_S", "0")
+    torch.set_num_threads(2)
+    assert bench.run_ours(bench.parse(ARGV)) == 0
+    line = json.loads(capsys.readouterr().out.strip().splitlines()[-1])
+    assert line["value"] > 0 and line["e2e"]["value"] > 0 and line["cpu_baseline"]["value"] > 0
+    assert line["parity"] is None and line["gradsync_microbench"] is None
+    assert len(line["errors"]) == 1 and line["errors"][0].startswith("parity: not started")
+
+    printed, left = [], []
+    guard = bench._Deadline(0, printed.append)
+    guard._exit = left.append
+    guard.phase = "headline"
+    guard.expire()  # nothing measured yet: nothing to print, non-zero exit
+    assert printed == [] and left == [4]
+    guard.have_headline, guard.phase, guard.rc = True, "gradsync_microbench", 3
+    guard.expire()
+    guard.print_once()  # the normal end of the run after the timer fired: the line is not printed twice
+    assert len(printed) == 1 and "gradsync_microbench" in printed[0] and left == [4, 3]
+    other = bench._Deadline(1, printed.append)  # ranks other than 0 print nothing
+    other._exit = left.append
+    other.have_headline = True
+    monkeypatch.setattr(bench.time, "sleep", lambda s: None)
+    other.expire()
+    assert len(printed) == 1 and left == [4, 3, 0]
