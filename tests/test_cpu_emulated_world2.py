@@ -1,4 +1,4 @@
-"""Two ranks, the N>1 Python logic of the engine -- one hook per bucket, buckets flushed and "all-reduced" while
+"""Two ranks (and one case each with four and eight), the N>1 Python logic of the engine -- one hook per bucket, buckets flushed and "all-reduced" while
 backward runs, the learned launch order, the parameter broadcast from rank 0, norm partials per bucket, the opt-in
 sharded step -- in the CPU suite: two processes, torch.distributed over gloo standing in for NCCL through the
 emulated communicator entry points of tests/fake_dgs.py (test infrastructure), the control plane being the real
@@ -504,3 +504,107 @@ def test_two_rank_module_buffers_follow_rank_zero(tmp_path):
 
     mp.spawn(_bn_worker, args=(2, _free_port(), (_free_port(), _free_port()), str(tmp_path)), nprocs=2, join=True)
     assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
+
+
+def _wide_worker(rank: int, size: int, port: int, zmq_ports, per_bucket: bool, out_dir: str) -> None:
+    """More than two ranks (the fixtures recorded from the reference stop at two slots): the peer route pinned, several
+    buckets, aggregation over two micro-batches, two parameter groups, clipping -- against live torch DDP over gloo on
+    the same ranks and data.  What changes with the world size is the slicing: a bucket is `size` rows of span =
+    bucket / size elements, owner r reduces row block r and steps it, the ranges of a parameter group are cut at the
+    slice borders; with `per_bucket` every bucket is reduced as soon as its pushes have landed."""
+    for p in (str(ROOT), str(ROOT / "tests"), str(ROOT / "tests" / "golden")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import copy
+
+    import torch.distributed as dist
+
+    import fake_dgs
+    from golden_io import assert_close
+
+    from determined_clone_b200 import core, pytorch
+    from determined_clone_b200.pytorch import _gradsync
+
+    torch.set_num_threads(1)
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=size)
+    fake = fake_dgs.install()
+
+    class SmallBuckets(_gradsync.GradSyncEngine):
+        def __init__(self, *args, **kwargs):
+            kwargs.update(bucket_bytes=2048, first_bucket_bytes=512)
+            super().__init__(*args, **kwargs)
+
+    _gradsync.GradSyncEngine = SmallBuckets
+    _gradsync._PEER_OVERLAP_MIN = 1 if per_bucket else 1 << 40
+    dctx = core.DistributedContext(rank=rank, size=size, local_rank=rank, local_size=size, cross_rank=0, cross_size=1,
+                                   pub_port=zmq_ports[0], pull_port=zmq_ports[1])
+    try:
+        torch.manual_seed(23)
+        base = torch.nn.Sequential(torch.nn.Linear(12, 40), torch.nn.LayerNorm(40), torch.nn.Tanh(), torch.nn.Linear(40, 33),
+                                   torch.nn.Tanh(), torch.nn.Linear(33, 5))
+        gen = torch.Generator().manual_seed(700 + rank)
+        agg, steps, max_norm = 2, 5, 0.25
+        data = [(torch.randn(6, 12, generator=gen), torch.randn(6, 5, generator=gen)) for _ in range(agg * steps)]
+
+        def groups(model):
+            decay = [p for p in model.parameters() if p.ndim > 1]
+            rest = [p for p in model.parameters() if p.ndim <= 1]
+            return [{"params": decay, "weight_decay": 0.1}, {"params": rest, "weight_decay": 0.0, "lr": 2e-2}]
+
+        ref_model = torch.nn.parallel.DistributedDataParallel(copy.deepcopy(base))
+        ref_opt = torch.optim.AdamW(groups(ref_model), lr=1e-2, betas=(0.9, 0.95))
+        want = []
+        for i, (x, y) in enumerate(data):  # the reference's lines: no_sync off the boundary, /A, clip, step (_pytorch_context.py:802-924)
+            if (i + 1) % agg:
+                with ref_model.no_sync():
+                    torch.nn.functional.mse_loss(ref_model(x), y).backward()
+                continue
+            torch.nn.functional.mse_loss(ref_model(x), y).backward()
+            for p in ref_model.parameters():
+                p.grad.div_(agg)
+            norm = torch.nn.utils.clip_grad_norm_(ref_model.parameters(), max_norm)
+            ref_opt.step()
+            ref_opt.zero_grad()
+            want.append((float(norm), [_np(p) for p in ref_model.parameters()], [_np(ref_opt.state[p]["exp_avg"]) for p in ref_model.parameters()]))
+
+        ctx = pytorch.PyTorchTrialContext(distributed=dctx, hparams={"global_batch_size": 6 * size}, slots_per_trial=size, aggregation_frequency=agg,
+                                          exp_conf={"optimizations": {"grad_sync_route": "peer"}})
+        model = ctx.wrap_model(copy.deepcopy(base))
+        opt = ctx.wrap_optimizer(torch.optim.AdamW(groups(model), lr=1e-2, betas=(0.9, 0.95)))
+        eng = ctx._engines[opt]
+        assert eng.peer and eng.sharded and eng.world == size
+        n_buckets = sum(len(fs.buckets) for fs in eng.sets)
+        assert n_buckets >= 3 and all(fs.peer_overlap == per_bucket for fs in eng.sets)
+        norms = []
+        index_of = {p: j for j, p in enumerate(p for g in opt.param_groups for p in g["params"])}
+        for i, (x, y) in enumerate(data):
+            ctx._current_batch_idx = i
+            ctx.backward(torch.nn.functional.mse_loss(model(x), y))
+            ctx.step_optimizer(opt, clip_grads=lambda ps: norms.append(torch.nn.utils.clip_grad_norm_(ps, max_norm)))
+            if (i + 1) % agg:
+                continue
+            s = i // agg
+            state = opt.state_dict()["state"]  # (a collective on the sliced routes: every rank asks)
+            assert_close(float(norms[-1]), want[s][0], "float32", f"total norm, step {s}")
+            for j, p in enumerate(model.parameters()):
+                assert_close(_np(p), want[s][1][j], "float32", f"parameter {j} after step {s}")
+                assert_close(_np(state[index_of[p]]["exp_avg"]), want[s][2][j], "float32", f"exp_avg {j} after step {s}")
+        kinds = [e[0] for e in fake.log]
+        assert kinds.count("flatten_push") >= steps * n_buckets and kinds.count("peer_norm_exchange") == steps
+        # per bucket: one barrier + one reduction per bucket; otherwise one barrier and one (multi-bucket) reduction per step
+        assert kinds.count("peer_barrier") == steps * ((n_buckets if per_bucket else 1) + 1)
+        if per_bucket:
+            assert kinds.count("peer_reduce") == steps * n_buckets
+        ctx.close()
+        open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
+    finally:
+        dctx.close()
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("size,per_bucket", [(4, True), (8, False)])
+def test_peer_route_on_four_and_eight_ranks_matches_torch_ddp(tmp_path, size, per_bucket):
+    import torch.multiprocessing as mp
+
+    mp.spawn(_wide_worker, args=(size, _free_port(), (_free_port(), _free_port()), per_bucket, str(tmp_path)), nprocs=size, join=True)
+    assert all((tmp_path / f"ok{r}").exists() for r in range(size))
