@@ -69,16 +69,57 @@ def tolerances(dtype: str) -> Dict[str, float]:
     return dict(rtol=1e-2, atol=2e-4)
 
 
-def assert_close(actual: Any, desired: Any, dtype: str, what: str = "", scale: Any = None, factor: float = 1.0) -> None:
-    """rel 1e-5 (fp32) / 1e-2 (bf16), relative to each element or -- for elements that are the
-    result of cancellation -- to the magnitude of the operands (`scale`, default max |desired|):
-    a bf16 sum of two gradients of size 0.03 carries an absolute error of about one ulp of 0.03
-    however small the sum is.  `factor` widens the tolerance for derived quantities: exp_avg_sq is
-    quadratic in the gradient, so gradients that agree to 1e-2 give second moments that agree to ~2e-2
-    plus their own rounding."""
+def _report(actual: np.ndarray, desired: np.ndarray, dtype: str, what: str, factor: float) -> None:
+    """DGS_TOL_REPORT=<file>: one JSON line per comparison with the worst element under three rules, each as a
+    fraction of what the rule allows (<= 1 passes) -- `tensor`: rtol*(|b| + max|b|), the rule asserted below;
+    `rms`: rtol*(|b| + rms(b)); `elem`: the purely element-wise rule of tolerances() (rtol*|b| + atol).  A diagnostic
+    for choosing tolerances from measured errors; asserts nothing."""
+    import os
+
+    path = os.environ.get("DGS_TOL_REPORT")
+    if not path or actual.shape != desired.shape or not desired.size:
+        return
+    import json
+
+    t = tolerances(dtype)
+    err, mag = np.abs(actual - desired), np.abs(desired)
+    rms = float(np.sqrt(np.mean(desired * desired)))
+    row = {"what": what, "dtype": dtype, "factor": factor, "n": int(desired.size), "max_abs": float(mag.max()), "rms": rms,
+           "tensor": float(np.max(err / (t["rtol"] * (mag + mag.max()) + 1e-300))),
+           "rms_rule": float(np.max(err / (t["rtol"] * (mag + rms) + 1e-300))),
+           "elem": float(np.max(err / (t["rtol"] * mag + t["atol"])))}
+    with open(path, "a") as f:
+        f.write(json.dumps(row) + "\n")
+
+
+def assert_close(actual: Any, desired: Any, dtype: str, what: str = "", scale: Any = None, factor: float = 1.0, rule: Any = None) -> None:
+    """rel 1e-5 (fp32) / 1e-2 (bf16) per element, plus an absolute floor that depends on `rule`:
+
+      "elem"    tolerances(): rtol*|b| + 1e-7 (fp32) / 2e-4 (bf16) -- purely element-wise; for comparisons on identical
+                inputs (the golden replay)
+      "rms"     rtol*(|b| + rms(b)): the floor is 1e-5 of the tensor's typical element (default for fp32)
+      "tensor"  rtol*(|b| + max|b|): the floor is relative to the tensor's largest element (default for bf16: a bf16 sum
+                of two gradients of size 0.03 carries an error of about one ulp of 0.03 however small the sum is)
+
+    A floor is needed because the fixtures were recorded on a CPU and the trial's forward/backward runs on the GPU: an
+    element that is the difference of two O(1) products carries the matmuls' rounding however small it is.  The
+    defaults were chosen from measured errors (DGS_TOL_REPORT, profiles/r2_tolerance_report_gpu.txt: on B200 every
+    fp32 comparison of the 1-slot fixture tests is within 0.21 of the "rms" rule and 0.69 of the "elem" rule, the
+    replay within 0.11 of "elem").  `scale` replaces max|b| in the "tensor" rule; `factor` widens the tolerance for
+    derived quantities."""
     actual = np.asarray(actual, dtype=np.float64)
     desired = np.asarray(desired, dtype=np.float64)
-    rtol = (1e-5 if dtype == "float32" else 1e-2) * factor
-    if scale is None:
-        scale = float(np.max(np.abs(desired))) if desired.size else 0.0
-    np.testing.assert_allclose(actual, desired, rtol=rtol, atol=rtol * float(scale) + 1e-30, err_msg=what)
+    t = tolerances(dtype)
+    rtol = t["rtol"] * factor
+    if rule is None:
+        rule = "rms" if dtype == "float32" and scale is None else "tensor"
+    _report(actual, desired, dtype, what, factor)
+    if rule == "elem":
+        atol = t["atol"] * factor
+    elif rule == "rms":
+        atol = rtol * float(np.sqrt(np.mean(desired * desired))) if desired.size else 0.0
+    else:
+        if scale is None:
+            scale = float(np.max(np.abs(desired))) if desired.size else 0.0
+        atol = rtol * float(scale)
+    np.testing.assert_allclose(actual, desired, rtol=rtol, atol=atol + 1e-30, err_msg=what)

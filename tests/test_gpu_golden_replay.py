@@ -22,6 +22,8 @@ FUSED = [n for n, sc in SCENARIOS.items() if sc["hp"]["optimizer"] in ("sgd", "a
 def test_replay(lib, name):
     g = Golden(name)
     dt = g.dtype
+    # identical inputs (the recorded gradients): fp32 is held to the purely element-wise rule, 1e-5*|x| + 1e-7
+    rule = "elem" if dt == "float32" else None
     init = g.init_params()
     # flat layout in optimizer order, every tensor 128-byte aligned
     offs, off = {}, 0
@@ -63,7 +65,7 @@ def test_replay(lib, name):
         for w in wires[1:]:
             wire = wire + w  # ncclAllReduce(sum) in the wire dtype
         want_avg = flat_of(g.per_step("avg_grads", s))
-        assert_close(host(wire), want_avg, dt, f"{name}: synced gradients, step {s}")
+        assert_close(host(wire), want_avg, dt, f"{name}: synced gradients, step {s}", rule=rule)
 
         clip_ptr, max_norm = None, 0.0
         if g.clip is not None and g.clip[0] == "norm":
@@ -85,10 +87,10 @@ def test_replay(lib, name):
         torch.cuda.synchronize()
 
         if clip_ptr is not None:
-            assert_close(float(norm), g.z["total_norm"][s], dt, f"{name}: total norm, step {s}")
-        assert_close(host(p), flat_of(g.per_step("params", s)), dt, f"{name}: parameters, step {s}")
+            assert_close(float(norm), g.z["total_norm"][s], dt, f"{name}: total norm, step {s}", rule=rule)
+        assert_close(host(p), flat_of(g.per_step("params", s)), dt, f"{name}: parameters, step {s}", rule=rule)
         if kind == "sgd":
-            assert_close(host(s1), flat_of([g.state(s, i, "momentum_buffer") for i in range(N_PARAMS)]), dt, f"{name}: momentum, step {s}")
+            assert_close(host(s1), flat_of([g.state(s, i, "momentum_buffer") for i in range(N_PARAMS)]), dt, f"{name}: momentum, step {s}", rule=rule)
         else:
-            assert_close(host(s1), flat_of([g.state(s, i, "exp_avg") for i in range(N_PARAMS)]), dt, f"{name}: exp_avg, step {s}")
-            assert_close(host(s2), flat_of([g.state(s, i, "exp_avg_sq") for i in range(N_PARAMS)]), dt, f"{name}: exp_avg_sq, step {s}")
+            assert_close(host(s1), flat_of([g.state(s, i, "exp_avg") for i in range(N_PARAMS)]), dt, f"{name}: exp_avg, step {s}", rule=rule)
+            assert_close(host(s2), flat_of([g.state(s, i, "exp_avg_sq") for i in range(N_PARAMS)]), dt, f"{name}: exp_avg_sq, step {s}", rule=rule)

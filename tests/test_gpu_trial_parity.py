@@ -83,29 +83,34 @@ def run_scenario(name: str, distributed=None) -> None:
     # CPU run that produced the fixtures) and already differ by ~1e-2; Adam divides by sqrt(v), so that
     # input noise is amplified a few times in the state and in zero-initialised parameters.  The path's own
     # bf16 parity at 1e-2 is asserted on identical inputs in test_gpu_golden_replay.py.
-    wide = 1.0 if dt == "float32" else 5.0
+    # Measured on B200 (profiles/r2_tolerance_report_gpu.txt): the 1-slot bf16 scenario stays within 1.15x of the plain
+    # rule, so 3x; the 2-slot scenarios only run where two GPUs are (inside bench.py's parity pass) and keep the rule
+    # and the factor they were last measured with.
+    two_slot = g.slots > 1
+    wide = 1.0 if dt == "float32" else (5.0 if two_slot else 3.0)
+    rule = "tensor" if two_slot else None  # None: golden_io's default (fp32: 1e-5*(|x| + rms); bf16: tensor-relative)
     opt_order_to_model = [0, 4, 1, 2, 3, 5]
     for s in range(g.steps):
         want_avg = g.per_step("avg_grads", s)
         for j, i in enumerate(opt_order_to_model):
-            assert_close(rec["avg"][s][j], want_avg[i], dt, f"{name}: synced grad, step {s}, param {i}")
+            assert_close(rec["avg"][s][j], want_avg[i], dt, f"{name}: synced grad, step {s}, param {i}", rule=rule)
         for i in range(N_PARAMS):
-            assert_close(rec["params"][s][i], g.per_step("params", s)[i], dt, f"{name}: parameter {i} after step {s}", factor=wide)
+            assert_close(rec["params"][s][i], g.per_step("params", s)[i], dt, f"{name}: parameter {i} after step {s}", factor=wide, rule=rule)
             st = rec["state"][s][i]
             if g.hp["optimizer"] == "sgd":
-                assert_close(st["momentum_buffer"], g.state(s, i, "momentum_buffer"), dt, f"{name}: momentum {i} step {s}")
+                assert_close(st["momentum_buffer"], g.state(s, i, "momentum_buffer"), dt, f"{name}: momentum {i} step {s}", rule=rule)
             elif g.hp["optimizer"] in ("adam", "adamw"):
-                assert_close(st["exp_avg"], g.state(s, i, "exp_avg"), dt, f"{name}: exp_avg {i} step {s}", factor=wide)
-                assert_close(st["exp_avg_sq"], g.state(s, i, "exp_avg_sq"), dt, f"{name}: exp_avg_sq {i} step {s}", factor=wide)
+                assert_close(st["exp_avg"], g.state(s, i, "exp_avg"), dt, f"{name}: exp_avg {i} step {s}", factor=wide, rule=rule)
+                assert_close(st["exp_avg_sq"], g.state(s, i, "exp_avg_sq"), dt, f"{name}: exp_avg_sq {i} step {s}", factor=wide, rule=rule)
                 assert float(st["step"]) == float(g.state(s, i, "step")) == s + 1  # integer counter: exact
         if g.clip is not None and g.clip[0] == "norm":
-            assert_close(float(rec["norm"][s]), g.z["total_norm"][s], dt, f"{name}: total norm step {s}")
+            assert_close(float(rec["norm"][s]), g.z["total_norm"][s], dt, f"{name}: total norm step {s}", rule=rule)
     if ctx.distributed.rank == 0:
         # chief's reports: batch counters exactly, averaged loss within tolerance
         assert [n for n, _ in reports] == g.z["reported_steps"].tolist()
         for (n, r), want_avg, want_batches in zip(reports, g.z["reported_avg_loss"], g.z["reported_batch_loss"]):
-            assert_close(r["avg_metrics"]["loss"], want_avg, dt, f"{name}: reported avg loss at {n}")
-            assert_close([float(b["loss"]) for b in r["batch_metrics"]], want_batches, dt, f"{name}: per-batch loss at {n}")
+            assert_close(r["avg_metrics"]["loss"], want_avg, dt, f"{name}: reported avg loss at {n}", rule=rule)
+            assert_close([float(b["loss"]) for b in r["batch_metrics"]], want_batches, dt, f"{name}: per-batch loss at {n}", rule=rule)
     ctx.close()
 
 
@@ -252,16 +257,17 @@ def _sharded_rank_main(rank: int, size: int, name: str, ports, route: str = "sha
             assert eng.peer and eng.sharded, f"route auto did not reach the peer kernels: {eng.peer_unavailable}"
         dt = g.dtype
         wide = 1.0 if dt == "float32" else 5.0
+        rule = "tensor"  # 2 slots: the rule these comparisons were last measured with on two GPUs
         for s in range(g.steps):
             for i in range(N_PARAMS):  # every rank ends every step with the full, identical parameters
-                assert_close(rec["params"][s][i], g.per_step("params", s)[i], dt, f"{name}: parameter {i} after step {s}", factor=wide)
+                assert_close(rec["params"][s][i], g.per_step("params", s)[i], dt, f"{name}: parameter {i} after step {s}", factor=wide, rule=rule)
             if g.clip is not None and rec["norm"]:
-                assert_close(float(rec["norm"][s]), g.z["total_norm"][s], dt, f"{name}: total norm step {s}")
+                assert_close(float(rec["norm"][s]), g.z["total_norm"][s], dt, f"{name}: total norm step {s}", rule=rule)
         # optimizer.state_dict() gathers the other ranks' slices: complete and in the reference layout
         sd = trial.opt.state_dict()["state"]
         key = "momentum_buffer" if g.hp["optimizer"] == "sgd" else "exp_avg"
         for j, i in enumerate([0, 4, 1, 2, 3, 5]):  # optimizer order -> model order
-            assert_close(_np(sd[j][key]), g.state(g.steps - 1, i, key), dt, f"{name}: gathered {key} of param {i}", factor=wide)
+            assert_close(_np(sd[j][key]), g.state(g.steps - 1, i, key), dt, f"{name}: gathered {key} of param {i}", factor=wide, rule=rule)
         with pytest.raises(det.errors.InvalidExperimentException, match="sharded_step"):
             ctx._current_batch_idx = g.agg - 1  # a boundary batch
             ctx.backward(trial.model(torch.randn(4, 24, device="cuda").to(trial.plist[0].dtype)).float().sum())
