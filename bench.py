@@ -819,7 +819,7 @@ def run_ours(args: argparse.Namespace) -> int:
     else:
         dctx = core.DummyDistributedContext()
     peak, _ = measured_peaks()
-    got: Dict[str, Any] = {"head": None, "parity": None, "extra": {}, "micro": None, "cpu": None}
+    got: Dict[str, Any] = {"head": None, "parity": None, "extra": {}, "micro": None, "cpu": None, "wall_s": {}}
     errors: List[str] = []
     cpu_error: Optional[str] = None  # kept apart from `errors`: it does not put the ranks out of step
 
@@ -833,6 +833,8 @@ def run_ours(args: argparse.Namespace) -> int:
             "clocks": head["clocks"], "grad_sync_us_per_step": head["grad_sync_us_per_step"], "route": head["route"],
             "parity": got["parity"], "gradsync_microbench": got["micro"], "configs": got["extra"],
             "errors": (errors + ([cut] if cut else [])) or None,
+            # this rank's wall clock, seconds since bench.py was imported, at which each part was complete
+            "wall_s": dict(got["wall_s"], printed=round(time.monotonic() - T0, 1)),
         }
         print(json.dumps(line), flush=True)
 
@@ -854,6 +856,7 @@ def run_ours(args: argparse.Namespace) -> int:
         guard.phase = "headline"
         got["head"] = measure_workload(args, W, dctx, dist, device, rank, world, local_rank, args.steps, args.warmup, with_e2e=True)
         guard.have_headline = True
+        got["wall_s"]["headline"] = round(guard.elapsed(), 1)
 
         if world == 1 and not args.no_cpu_baseline:  # (one rank, bounded: nothing to keep in step)
             guard.phase = "cpu_baseline"
@@ -862,6 +865,7 @@ def run_ours(args: argparse.Namespace) -> int:
                 got["cpu"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
             except Exception as e:  # noqa: BLE001
                 cpu_error = f"cpu_baseline: {type(e).__name__}: {str(e)[:300]}"
+            got["wall_s"]["cpu_baseline"] = round(guard.elapsed(), 1)
 
         def optional(what: str, fn: Callable[[], Any]) -> Any:
             guard.phase = f"before {what}"
@@ -880,6 +884,8 @@ def run_ours(args: argparse.Namespace) -> int:
             except Exception as e:  # noqa: BLE001
                 errors.append(f"{what}: {type(e).__name__}: {str(e)[:300]}")
                 return None
+            finally:
+                got["wall_s"][what] = round(guard.elapsed(), 1)
 
         if not args.no_parity:
             got["parity"] = optional("parity", lambda: run_parity(args, dctx, dist, device, rank, world))

@@ -81,6 +81,8 @@ def test_bench_ours_single_process(monkeypatch, capsys):
     line = json.loads(capsys.readouterr().out.strip().splitlines()[-1])
     _check_line(line)
     assert line["n_gpus"] == 1 and line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["value"] > 0
+    walls = line["wall_s"]  # when each part was complete: headline first, the line last
+    assert list(walls) == ["headline", "cpu_baseline", "parity", "gradsync_microbench", "printed"] and sorted(walls.values()) == list(walls.values())
 
 
 def _free_port():
