@@ -53,6 +53,7 @@ def _worker(rank: int, size: int, port: int, zmq_ports, name: str, sharded, smal
                 kwargs.update(bucket_bytes=1024, first_bucket_bytes=256)
                 super().__init__(*args, **kwargs)
 
+        real_engine = _gradsync.GradSyncEngine
         _gradsync.GradSyncEngine = SmallBuckets
     dctx = core.DistributedContext(rank=rank, size=size, local_rank=rank, local_size=size, cross_rank=0, cross_size=1,
                                    pub_port=zmq_ports[0], pull_port=zmq_ports[1])
@@ -140,21 +141,35 @@ def _worker(rank: int, size: int, port: int, zmq_ports, name: str, sharded, smal
         everyone = dctx.allgather([e[1] for e in per_step])
         assert everyone[0] == everyone[1]
         ctx.close()
-        open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
+        open(os.path.join(out_dir, f"ok{rank}-{name}-{route}-{small_buckets}"), "w").write("ok")
     finally:
         dctx.close()
         dist.destroy_process_group()
+        if small_buckets:
+            _gradsync.GradSyncEngine = real_engine
 
 
-@pytest.mark.parametrize("name,sharded,small_buckets", [
-    ("sgd_n2_a2", False, True), ("adamw_n2_a4_clip", False, False), ("adamw_n2_a4_clip", True, True),
-    ("sgd_n2_a2", "peer", True), ("adamw_n2_a4_clip", "peer", True),
-])
-def test_two_rank_scenarios_with_emulated_kernels_and_gloo(tmp_path, name, sharded, small_buckets):
+SCENARIOS_2 = [("sgd_n2_a2", False, True), ("adamw_n2_a4_clip", False, False), ("adamw_n2_a4_clip", True, True),
+               ("sgd_n2_a2", "peer", True), ("adamw_n2_a4_clip", "peer", True)]
+
+
+def _scenarios_worker(rank: int, size: int, ports, out_dir: str) -> None:
+    """All scenario / route / bucket combinations in ONE pair of processes (each spawn costs ~12 s of interpreter and
+    torch start-up, the scenarios themselves a second or two); every combination gets its own process group, control
+    plane and ports, and leaves its own marker file, so a failure names the combination."""
+    for (name, sharded, small_buckets), (port, zmq_ports) in zip(SCENARIOS_2, ports):
+        _worker(rank, size, port, zmq_ports, name, sharded, small_buckets, out_dir)
+
+
+def test_two_rank_scenarios_with_emulated_kernels_and_gloo(tmp_path):
     import torch.multiprocessing as mp
 
-    mp.spawn(_worker, args=(2, _free_port(), (_free_port(), _free_port()), name, sharded, small_buckets, str(tmp_path)), nprocs=2, join=True)
-    assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
+    ports = [(_free_port(), (_free_port(), _free_port())) for _ in SCENARIOS_2]
+    mp.spawn(_scenarios_worker, args=(2, ports, str(tmp_path)), nprocs=2, join=True)
+    for name, sharded, small_buckets in SCENARIOS_2:
+        route = {False: "allreduce", True: "sharded"}.get(sharded, sharded)
+        for rank in range(2):
+            assert (tmp_path / f"ok{rank}-{name}-{route}-{small_buckets}").exists(), (name, route, small_buckets)
 
 
 def _auto_worker(rank: int, size: int, port: int, zmq_ports, name: str, out_dir: str) -> None:
