@@ -86,7 +86,7 @@ def _native_host_loop():
 def test_single_slot_scenarios_through_the_whole_python_path(monkeypatch, name, native):
     """The reference's recorded runs (10 optimizer steps each) reproduced by this harness with emulated kernels:
     synchronized gradients, clip norm, parameters, optimizer state, step counters, reported metrics.  native: with
-    the C++ host loop (csrc/dgs_host.cpp, what DGS_HOST_EXT=1 selects) taking the gradients instead of Python."""
+    the C++ host loop (csrc/dgs_host.cpp, the default once built) taking the gradients instead of Python."""
     fake = fake_dgs.install(monkeypatch)
     if native:
         from determined_clone_b200.pytorch import _gradsync

@@ -1236,7 +1236,7 @@ def test_lr_scheduler_coupling_matches_rates_recorded_from_the_reference():
 
 
 def test_native_host_loop_equals_the_python_loop(monkeypatch):
-    """csrc/dgs_host.cpp (opt-in with DGS_HOST_EXT=1) against the Python loops it replaces, on CPU tensors: the same
+    """csrc/dgs_host.cpp (used whenever it is built; DGS_HOST_EXT=0 switches it off) against the Python loops it replaces, on CPU tensors: the same
     dgs_seg tables reach dgs_flatten_accumulate, p.grad ends up None, and cases the fast path does not cover (a
     missing gradient, a dtype or layout the kernel cannot read directly) leave everything untouched."""
     import importlib.util
