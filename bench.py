@@ -779,7 +779,13 @@ def run_parity(args: argparse.Namespace, dctx: Any, dist: Any, device: Any, rank
     # reference-recorded fixtures).  Free-running arms and 16-bit cases are judged against the reference's own twin,
     # a statistical bound: they are reported in `ok`, but a chaotic draw must not void a measurement.
     hard = [c for c in cases if c.get("mode") == "fixtures" or (c.get("mode") == "synced" and c.get("dtype") == "f32")]
-    return {"n": world, "ok": all(c["ok"] for c in cases), "deterministic_checks_ok": all(c["ok"] for c in hard), "max_rel": max((c["max_rel"] for c in free), default=None),
+    one_step = [c["max_rel"] for c in hard if "max_rel" in c]
+    return {"n": world, "ok": all(c["ok"] for c in cases), "deterministic_checks_ok": all(c["ok"] for c in hard),
+            # the error of ONE optimizer step on identical inputs, fp32 cases, every route (tensor-relative; rtol 1e-5)
+            "max_rel_one_step_fp32": max(one_step, default=None),
+            # free-running arms after `parity_steps` steps, all cases: includes the chaotic ones, which are judged against
+            # the reference's own twin (cases[].reference_self_noise), not against rtol
+            "max_rel": max((c["max_rel"] for c in free), default=None),
             "against": "torch DDP (NCCL) + torch.optim on the same GPUs, same seeds and inputs (workloads/parity.py)", "cases": cases}
 
 
