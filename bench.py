@@ -29,7 +29,8 @@ collectives on the communicator's side stream), context.step_optimizer (fused st
 Order and time limits: headline (value, roofline, e2e) and cpu_baseline first; parity, configs and the microbench are
 additional evidence -- a failure there is recorded under `errors`, none of them is started later than 560 s into the
 run, and at 780 s the line is printed with whatever is complete (_Deadline; the driver's scaling sweep allows each N
-about 870 s).
+about 870 s).  A part that is cut or fails reports the cases / rows it had finished (`incomplete`).  `wall_s` says when
+each part was complete.
 """
 import argparse
 import json
@@ -506,7 +507,9 @@ def gradsync_microbench(ctx: Any, dist: Any, mb: int, dtype: str, agg: int, step
     return out
 
 
-def microbench_sweep(ctx: Any, dist: Any, args: argparse.Namespace, peak: float) -> Dict[str, Any]:
+def microbench_sweep(ctx: Any, dist: Any, args: argparse.Namespace, peak: float, rows: Optional[List[Dict[str, Any]]] = None) -> Dict[str, Any]:
+    """`rows`: a list the caller keeps; every finished row is appended to it at once, so that a run that is cut short
+    (bench._Deadline) can still report the rows it has."""
     from determined_clone_b200 import _lib
 
     world = ctx.distributed.size
@@ -520,7 +523,7 @@ def microbench_sweep(ctx: Any, dist: Any, args: argparse.Namespace, peak: float)
             gradsync_microbench(ctx, dist, min(args.micro_mb), "f32", 1, 1, peak, route="peer")
         except _lib.DgsError as e:
             route, note = "allreduce", f"peer route unavailable: {str(e)[:200]}"
-    rows = []
+    rows = [] if rows is None else rows
     for dtype in args.micro_dtypes:
         for agg in args.micro_aggs:
             for mb in args.micro_mb:
@@ -718,12 +721,14 @@ def measure_workload(args: argparse.Namespace, W: Any, dctx: Any, dist: Any, dev
     return out
 
 
-def run_parity(args: argparse.Namespace, dctx: Any, dist: Any, device: Any, rank: int, world: int) -> Dict[str, Any]:
-    """See the module docstring.  Returns {"n", "ok", "max_rel", "cases": [...]}."""
+def run_parity(args: argparse.Namespace, dctx: Any, dist: Any, device: Any, rank: int, world: int,
+               cases: Optional[List[Dict[str, Any]]] = None) -> Dict[str, Any]:
+    """See the module docstring.  Returns {"n", "ok", "max_rel", "cases": [...]}.  `cases`: a list the caller keeps, filled
+    as the cases finish (see microbench_sweep)."""
     from determined_clone_b200 import _lib, core, pytorch
     from workloads import parity as P
 
-    cases: List[Dict[str, Any]] = []
+    cases = [] if cases is None else cases
 
     def reduce_max(v: List[float]) -> List[float]:
         return _max_over_ranks(dist, device, v)
@@ -826,6 +831,7 @@ def run_ours(args: argparse.Namespace) -> int:
         dctx = core.DummyDistributedContext()
     peak, _ = measured_peaks()
     got: Dict[str, Any] = {"head": None, "parity": None, "extra": {}, "micro": None, "cpu": None, "wall_s": {}}
+    unfinished: Dict[str, List[Dict[str, Any]]] = {"parity": [], "micro": []}  # cases / rows of a part that is still running
     errors: List[str] = []
     cpu_error: Optional[str] = None  # kept apart from `errors`: it does not put the ranks out of step
 
@@ -837,7 +843,9 @@ def run_ours(args: argparse.Namespace) -> int:
             "dtype": W.DTYPE, "data": "synthetic", "config": head["config"],
             "roofline": head["roofline"], "cpu_baseline": got["cpu"], "e2e": head.get("e2e"), "gpu_launches": head["gpu_launches"],
             "clocks": head["clocks"], "grad_sync_us_per_step": head["grad_sync_us_per_step"], "route": head["route"],
-            "parity": got["parity"], "gradsync_microbench": got["micro"], "configs": got["extra"],
+            "parity": got["parity"] or ({"n": world, "incomplete": True, "cases": unfinished["parity"]} if unfinished["parity"] else None),
+            "gradsync_microbench": got["micro"] or ({"incomplete": True, "rows": unfinished["micro"]} if unfinished["micro"] else None),
+            "configs": got["extra"],
             "errors": (errors + ([cut] if cut else [])) or None,
             # this rank's wall clock, seconds since bench.py was imported, at which each part was complete
             "wall_s": dict(got["wall_s"], printed=round(time.monotonic() - T0, 1)),
@@ -894,7 +902,7 @@ def run_ours(args: argparse.Namespace) -> int:
                 got["wall_s"][what] = round(guard.elapsed(), 1)
 
         if not args.no_parity:
-            got["parity"] = optional("parity", lambda: run_parity(args, dctx, dist, device, rank, world))
+            got["parity"] = optional("parity", lambda: run_parity(args, dctx, dist, device, rank, world, cases=unfinished["parity"]))
             if got["parity"] is not None and not got["parity"]["deterministic_checks_ok"]:
                 guard.rc = 3
 
@@ -909,7 +917,7 @@ def run_ours(args: argparse.Namespace) -> int:
             def sweep() -> Any:
                 pytorch._PyTorchTrialController.pre_execute_hook(17)
                 ctx = pytorch.PyTorchTrialContext(distributed=dctx, hparams={"global_batch_size": world}, slots_per_trial=world, device=device)
-                return microbench_sweep(ctx, dist, args, peak)
+                return microbench_sweep(ctx, dist, args, peak, rows=unfinished["micro"])
 
             got["micro"] = optional("gradsync_microbench", sweep)
 

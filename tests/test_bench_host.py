@@ -161,6 +161,18 @@ def test_time_limits_keep_the_headline(monkeypatch, capsys):
     assert line["parity"] is None and line["gradsync_microbench"] is None
     assert len(line["errors"]) == 1 and line["errors"][0].startswith("parity: not started")
 
+    # a part that fails half-way: what it had finished is reported as incomplete, the failure is named, nothing else starts
+    def broken_parity(args, dctx, dist, device, rank, world, cases=None):
+        cases.append({"case": "first", "ok": True})
+        raise RuntimeError("second case fell over")
+
+    monkeypatch.setenv("DGS_BENCH_SOFT_S", "100000")
+    monkeypatch.setattr(bench, "run_parity", broken_parity)
+    assert bench.run_ours(bench.parse(ARGV + ["--no-cpu-baseline"])) == 0
+    line = json.loads(capsys.readouterr().out.strip().splitlines()[-1])
+    assert line["value"] > 0 and line["parity"] == {"n": 1, "incomplete": True, "cases": [{"case": "first", "ok": True}]}
+    assert line["gradsync_microbench"] is None and line["errors"][0] == "parity: RuntimeError: second case fell over"
+
     printed, left = [], []
     guard = bench._Deadline(0, printed.append)
     guard._exit = left.append
