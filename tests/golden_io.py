@@ -105,7 +105,7 @@ def assert_close(actual: Any, desired: Any, dtype: str, what: str = "", scale: A
     element that is the difference of two O(1) products carries the matmuls' rounding however small it is.  The
     defaults were chosen from measured errors (DGS_TOL_REPORT, profiles/r2_tolerance_report_gpu.txt: on B200 every
     fp32 comparison of the 1-slot fixture tests is within 0.21 of the "rms" rule and 0.69 of the "elem" rule, the
-    replay within 0.11 of "elem").  `scale` replaces max|b| in the "tensor" rule; `factor` widens the tolerance for
+    replay within 0.33 of "elem").  `scale` replaces max|b| in the "tensor" rule; `factor` widens the tolerance for
     derived quantities."""
     actual = np.asarray(actual, dtype=np.float64)
     desired = np.asarray(desired, dtype=np.float64)
